@@ -1,0 +1,157 @@
+#!/usr/bin/env python3
+"""Regenerates tests/golden/: inputs + the outputs of the compiled, UNMODIFIED reference for them.
+
+Run in the build container (needs /root/reference and `make -C oracle ref`):
+    python tests/golden/make_golden.py
+
+What lands in tests/golden/:
+  cases/<name>.bz2      the compressed inputs: (i) the reference's own 11 single-block fixtures
+                        (src/tests/data/*.bz2, data files, copied verbatim), (ii) generated multi-block,
+                        multi-stream, long-run, periodic and damaged files (seeded; python bz2 = libbz2 1.0.8)
+  golden.json           per case: sha256 + size of the decoded data, blockOffsets() of ParallelBZ2Reader (P=4)
+                        and of BZ2Reader, the `ibzip2 -l` magic list, error text / exit status of the CLI,
+                        all produced by oracle/_ref (reference @ 30c04e66)
+Nothing here is read from /root/reference at test time.
+"""
+from __future__ import annotations
+
+import base64
+import bz2
+import hashlib
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+ROOT = HERE.parent.parent
+sys.path.insert(0, str(ROOT / "tests"))
+import _oracle  # noqa: E402
+
+REF_DATA = Path("/root/reference/src/tests/data")
+CASES = HERE / "cases"
+
+
+def text_like(rng: np.random.Generator, n: int) -> bytes:
+    vocab = ["".join(chr(97 + c) for c in rng.integers(0, 26, rng.integers(2, 10))) for _ in range(4096)]
+    ranks = np.minimum(rng.zipf(1.3, n // 3), 4095)
+    words = " ".join(vocab[r] for r in ranks)
+    raw = words.encode()[:n]
+    out = bytearray(raw)
+    out[79::80] = b"\n" * len(out[79::80])
+    return bytes(out)
+
+
+def long_runs(rng: np.random.Generator, n: int) -> bytes:
+    parts = []
+    total = 0
+    special = [3, 4, 5, 255, 256, 258, 259, 260, 1, 2]
+    i = 0
+    while total < n:
+        length = special[i] if i < len(special) else int(np.exp(rng.uniform(0, np.log(1e5))))
+        i += 1
+        parts.append(bytes([int(rng.integers(0, 256))]) * length)
+        total += length
+    return b"".join(parts)[:n]
+
+
+def generated_cases() -> dict[str, bytes]:
+    rng = np.random.default_rng(20261104)
+    ref = {p.stem: p.read_bytes() for p in REF_DATA.glob("*.bz2")}
+    cases: dict[str, bytes] = {}
+
+    # Appendix B multi-stream example: data, tiny, EMPTY stream, data
+    cases["multistream-b64-1B-empty-b64"] = (ref["base64-32KiB"] + ref["1B"] + ref["empty"] + ref["base64-32KiB"])
+    # multi-block, level 1 (100 kB blocks): text-like
+    txt = text_like(rng, 450_000)
+    cases["text-450k-l1"] = bz2.compress(txt, 1)
+    # multi-block mixed entropy (text + random), level 2
+    mixed = b"".join(text_like(rng, 65536) if i % 2 == 0 else rng.bytes(65536) for i in range(6))
+    cases["mixed-384k-l2"] = bz2.compress(mixed, 2)
+    # base64 random, level 1, 3 blocks (config 1 miniature)
+    b64 = base64.encodebytes(rng.bytes(225_000))[:300_000]
+    cases["base64-300k-l1"] = bz2.compress(b64, 1)
+    # long runs (config 4 miniature): RLE1 expansion, RUNA/RUNB heavy
+    runs = long_runs(rng, 3_000_000)
+    cases["longruns-3M-l1"] = bz2.compress(runs, 1)
+    # periodic data (testPythonWrappers.py:476-500 regression sizes, Appendix C-15)
+    for size in [1, 2, 4, 128, 1000, 1024, 100_000, 200_000, 512 * 1024 + 2]:
+        cases[f"A-x{size}-l1"] = bz2.compress(b"A" * size, 1)
+    cases["AB-x150000-l1"] = bz2.compress(b"AB" * 150_000, 1)
+    cases["stripes-257-l3"] = bz2.compress((b"A" * 257 + b"B" * 257) * 400, 3)
+    cases["abracadabra-x3"] = bz2.compress(b"abracadabra" * 3, 9)
+    # all 256 byte values, every RLE1 run length 1..300 of a few bytes
+    edge = b"".join(bytes([b]) * k for k, b in zip(range(1, 301), [0, 255, 4, 65] * 75))
+    cases["rle1-runlengths-1..300"] = bz2.compress(bytes(range(256)) * 3 + edge, 9)
+    # pbzip2-style: many small independent streams, different levels
+    pieces = [text_like(rng, 20_000), rng.bytes(5000), b"", b"x", long_runs(rng, 50_000)]
+    cases["pbzip2-style-5-streams"] = b"".join(bz2.compress(p, lvl) for p, lvl in zip(pieces, [9, 1, 5, 3, 2]))
+    # damaged inputs
+    good = cases["text-450k-l1"]
+    cases["err-trailing-garbage"] = ref["base64-32KiB"] + b"\x00garbage after the end of stream"
+    cases["err-truncated"] = good[: len(good) // 2]
+    flipped = bytearray(good)
+    flipped[len(flipped) // 3] ^= 0x10
+    cases["err-bitflip"] = bytes(flipped)
+    cases["err-not-bzip2"] = b"this is not a bzip2 file at all, not even a little bit\n" * 3
+    cases["err-gap-then-valid"] = ref["1B"] + b"\x00\x00\x00" + ref["1B"]
+    hdr = bytearray(ref["dolorem-ipsum.txt"])
+    hdr[3] = ord("1")  # BZh1 header in front of a block produced at level 9 (Appendix C-1: level digit ignored)
+    cases["level-digit-ignored"] = bytes(hdr)
+    return cases
+
+
+def reference_cli(args: list[str]) -> tuple[int, str, bytes]:
+    p = subprocess.run([str(_oracle.REF_CLI)] + args, capture_output=True)
+    return p.returncode, p.stderr.decode(errors="replace"), p.stdout
+
+
+def main() -> None:
+    assert _oracle.ref_available() and _oracle.REF_CLI.exists(), "run `make -C oracle ref` first"
+    CASES.mkdir(parents=True, exist_ok=True)
+    cases: dict[str, bytes] = {}
+    for p in sorted(REF_DATA.glob("*.bz2")):
+        cases["ref-" + p.stem] = p.read_bytes()
+    cases.update(generated_cases())
+
+    golden = {}
+    for name, blob in sorted(cases.items()):
+        path = CASES / f"{name}.bz2"
+        path.write_bytes(blob)
+        entry: dict = {"compressed_size": len(blob), "compressed_sha256": hashlib.sha256(blob).hexdigest()}
+
+        par = _oracle.ref_decode_file(str(path), parallelization=4, serial_class=False)
+        entry["parallel"] = {"rc": par.rc, "error": par.error, "size": len(par.data),
+                             "sha256": hashlib.sha256(par.data).hexdigest(), "offsets": par.offsets}
+        ser = _oracle.ref_decode_file(str(path), parallelization=1, serial_class=True)
+        entry["serial"] = {"rc": ser.rc, "error": ser.error, "size": len(ser.data),
+                           "sha256": hashlib.sha256(ser.data).hexdigest(), "offsets": ser.offsets}
+
+        rc, err, out = reference_cli(["-l", "-", str(path)])
+        entry["finder"] = [int(x) for x in out.split()] if rc == 0 else None
+        rc, err, out = reference_cli(["-d", "-c", "-P", "4", str(path)])
+        entry["cli_parallel"] = {"rc": rc, "stderr": err.strip(), "stdout_size": len(out),
+                                 "stdout_sha256": hashlib.sha256(out).hexdigest()}
+        rc, err, out = reference_cli(["-d", "-c", "-P", "1", str(path)])
+        entry["cli_serial"] = {"rc": rc, "stderr": err.strip(), "stdout_size": len(out),
+                               "stdout_sha256": hashlib.sha256(out).hexdigest()}
+        # independent cross-check (libbz2) where the file is valid
+        try:
+            raw = bz2.decompress(blob)
+            entry["libbz2_sha256"] = hashlib.sha256(raw).hexdigest()
+        except Exception as e:  # noqa: BLE001
+            entry["libbz2_sha256"] = None
+            entry["libbz2_error"] = type(e).__name__
+        golden[name] = entry
+        print(f"{name:40s} C={len(blob):8d} par rc={par.rc} U={len(par.data):8d} entries={len(par.offsets):3d} "
+              f"ser rc={ser.rc} cliP4 rc={entry['cli_parallel']['rc']} {entry['cli_parallel']['stderr'][:60]!r}")
+
+    (HERE / "golden.json").write_text(json.dumps(golden, indent=1, sort_keys=True) + "\n")
+    total = sum(len(b) for b in cases.values())
+    print(f"{len(cases)} cases, {total} compressed bytes")
+
+
+if __name__ == "__main__":
+    main()
