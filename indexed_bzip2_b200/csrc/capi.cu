@@ -1,0 +1,779 @@
+/*
+ * capi.cu -- the C ABI declared in include/ibz2_cuda.h: context, scratch memory, stream orchestration.
+ * All bzip2 arithmetic lives in the kernels (blockfinder.cu, huffman_decode.cu, bwt_prepare.cu, bwt_traverse.cu,
+ * rle.cu, crc.cu); this file only moves buffers, launches, and converts BlockMeta into ibz2_block_result.
+ */
+#include "common.cuh"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+namespace
+{
+thread_local std::string g_createError;
+}
+
+struct ibz2_ctx
+{
+    int device = 0;
+    int sms = 148;
+    cudaStream_t stream = nullptr;
+    std::string lastError;
+    uint32_t batchBlocks = 0;
+
+    /* per-wave scratch */
+    uint32_t scratchBlocks = 0;
+    ibz2::BlockMeta* dMeta = nullptr;
+    uint8_t* dLbytes = nullptr;
+    uint32_t* dDbuf = nullptr;
+    uint8_t* dSelectors = nullptr;
+    uint32_t* dWarpBase = nullptr;
+    uint32_t* dPieceStart = nullptr;
+    uint64_t* dRunning = nullptr;
+    ibz2::BlockMeta* hMeta = nullptr; /* pinned, scratchBlocks entries */
+
+    /* staging for host-side inputs / outputs */
+    uint8_t* dIn = nullptr;
+    uint64_t dInCapacity = 0;
+    uint8_t* dOut = nullptr;
+    uint64_t dOutCapacity = 0;
+
+    /* finder */
+    uint64_t* dFound = nullptr;
+    uint32_t* dFoundCount = nullptr;
+    uint32_t foundCapacity = 0;
+
+    std::vector<cudaEvent_t> events;
+    size_t eventsUsed = 0;
+    ibz2_timings timings{};
+};
+
+namespace
+{
+int g_smCount = 148;
+
+#define IBZ2_CUDA_CHECK( ctx, call )                                                                          \
+    do {                                                                                                      \
+        const cudaError_t err__ = ( call );                                                                   \
+        if ( err__ != cudaSuccess ) {                                                                         \
+            ( ctx )->lastError = std::string( #call ) + ": " + cudaGetErrorString( err__ );                   \
+            return err__ == cudaErrorMemoryAllocation ? IBZ2_E_OUT_OF_MEMORY : IBZ2_E_CUDA;                   \
+        }                                                                                                     \
+    } while ( false )
+
+cudaEvent_t
+nextEvent( ibz2_ctx* ctx )
+{
+    if ( ctx->eventsUsed == ctx->events.size() ) {
+        cudaEvent_t e;
+        cudaEventCreate( &e );
+        ctx->events.push_back( e );
+    }
+    cudaEvent_t e = ctx->events[ctx->eventsUsed++];
+    cudaEventRecord( e, ctx->stream );
+    return e;
+}
+
+float
+elapsed( cudaEvent_t a, cudaEvent_t b )
+{
+    float ms = 0;
+    cudaEventElapsedTime( &ms, a, b );
+    return ms;
+}
+
+void
+freeScratch( ibz2_ctx* ctx )
+{
+    cudaFree( ctx->dMeta );
+    cudaFree( ctx->dLbytes );
+    cudaFree( ctx->dDbuf );
+    cudaFree( ctx->dSelectors );
+    cudaFree( ctx->dWarpBase );
+    cudaFree( ctx->dPieceStart );
+    cudaFreeHost( ctx->hMeta );
+    ctx->dMeta = nullptr;
+    ctx->dLbytes = nullptr;
+    ctx->dDbuf = nullptr;
+    ctx->dSelectors = nullptr;
+    ctx->dWarpBase = nullptr;
+    ctx->dPieceStart = nullptr;
+    ctx->hMeta = nullptr;
+    ctx->scratchBlocks = 0;
+}
+
+int
+ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
+{
+    if ( blocks <= ctx->scratchBlocks ) {
+        return IBZ2_OK;
+    }
+    freeScratch( ctx );
+    const uint64_t b = blocks;
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dMeta, b * sizeof( ibz2::BlockMeta ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dLbytes, b * ibz2::LBYTES_STRIDE ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dDbuf, b * ibz2::DBUF_STRIDE * sizeof( uint32_t ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dSelectors, b * ibz2::SEL_STRIDE ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dWarpBase, b * ibz2::RLE_RANGES * sizeof( uint32_t ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dPieceStart, ( b + 1 ) * sizeof( uint32_t ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMallocHost( &ctx->hMeta, b * sizeof( ibz2::BlockMeta ) ) );
+    ctx->scratchBlocks = blocks;
+    return IBZ2_OK;
+}
+
+int
+ensureInput( ibz2_ctx* ctx, uint64_t nbytes )
+{
+    if ( nbytes + 256U <= ctx->dInCapacity ) {
+        return IBZ2_OK;
+    }
+    cudaFree( ctx->dIn );
+    ctx->dIn = nullptr;
+    ctx->dInCapacity = 0;
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dIn, nbytes + 256U ) );
+    ctx->dInCapacity = nbytes + 256U;
+    return IBZ2_OK;
+}
+
+int
+ensureOutput( ibz2_ctx* ctx, uint64_t nbytes )
+{
+    if ( nbytes + 256U <= ctx->dOutCapacity ) {
+        return IBZ2_OK;
+    }
+    cudaFree( ctx->dOut );
+    ctx->dOut = nullptr;
+    ctx->dOutCapacity = 0;
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dOut, nbytes + 256U ) );
+    ctx->dOutCapacity = nbytes + 256U;
+    return IBZ2_OK;
+}
+
+void
+fillResult( const ibz2::BlockMeta& m, ibz2_block_result* r )
+{
+    r->enc_offset_bits = m.bitOffset;
+    r->enc_size_bits = m.endBit >= m.bitOffset ? m.endBit - m.bitOffset : 0;
+    r->out_offset = m.outOffset;
+    r->out_size = ( ( m.status == IBZ2_ST_OK ) || ( m.status == IBZ2_ST_OUTPUT_CAPACITY ) || ( m.status == IBZ2_ST_CRC ) )
+                  ? m.outSize : 0;
+    r->expected_crc = m.headerCrc;
+    r->calculated_crc = m.calcCrc;
+    r->status = m.status;
+    r->is_eos = m.isEos;
+    r->is_eof = m.isEof;
+    r->n_symbols = m.n;
+    r->orig_ptr = m.origPtr;
+    r->reserved = 0;
+}
+
+/* MSB-first bit extraction on the host, for the two header probes only. */
+struct HostBits
+{
+    const uint8_t* data;
+    uint64_t nbits;
+    uint64_t pos;
+    bool eof;
+
+    uint64_t
+    read( unsigned n )
+    {
+        if ( pos + n > nbits ) {
+            eof = true;
+            pos = nbits;
+            return 0;
+        }
+        uint64_t v = 0;
+        for ( unsigned i = 0; i < n; ++i, ++pos ) {
+            v = ( v << 1 ) | ( ( data[pos >> 3] >> ( 7U - ( pos & 7U ) ) ) & 1U );
+        }
+        return v;
+    }
+};
+}  // namespace
+
+namespace ibz2
+{
+int
+smCount()
+{
+    return g_smCount;
+}
+}  // namespace ibz2
+
+extern "C" {
+
+int
+ibz2_abi_version( void )
+{
+    return IBZ2_ABI_VERSION;
+}
+
+int
+ibz2_device_count( void )
+{
+    int n = 0;
+    if ( cudaGetDeviceCount( &n ) != cudaSuccess ) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char*
+ibz2_last_error( const ibz2_ctx* ctx )
+{
+    return ctx != nullptr ? ctx->lastError.c_str() : g_createError.c_str();
+}
+
+int
+ibz2_create( int device, ibz2_ctx** out )
+{
+    if ( out == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    int n = 0;
+    cudaError_t err = cudaGetDeviceCount( &n );
+    if ( ( err != cudaSuccess ) || ( n == 0 ) ) {
+        cudaGetLastError();
+        g_createError = std::string( "no usable CUDA device (there is no CPU fallback): " )
+                        + ( err != cudaSuccess ? cudaGetErrorString( err ) : "device count is 0" );
+        return IBZ2_E_NO_DEVICE;
+    }
+    if ( ( device < 0 ) || ( device >= n ) ) {
+        g_createError = "device index out of range";
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    ibz2_ctx* ctx = new ( std::nothrow ) ibz2_ctx;
+    if ( ctx == nullptr ) {
+        return IBZ2_E_OUT_OF_MEMORY;
+    }
+    ctx->device = device;
+    cudaDeviceProp prop{};
+    if ( ( ( err = cudaSetDevice( device ) ) != cudaSuccess )
+         || ( ( err = cudaGetDeviceProperties( &prop, device ) ) != cudaSuccess )
+         || ( ( err = cudaStreamCreateWithFlags( &ctx->stream, cudaStreamNonBlocking ) ) != cudaSuccess )
+         || ( ( err = cudaMalloc( &ctx->dRunning, 2 * sizeof( uint64_t ) ) ) != cudaSuccess ) ) {
+        g_createError = std::string( "CUDA initialisation failed: " ) + cudaGetErrorString( err );
+        delete ctx;
+        return IBZ2_E_CUDA;
+    }
+    if ( prop.major < 10 ) {
+        g_createError = "this library is built for sm_100a (Blackwell B200) only; device is sm_"
+                        + std::to_string( prop.major ) + std::to_string( prop.minor );
+        cudaFree( ctx->dRunning );
+        cudaStreamDestroy( ctx->stream );
+        delete ctx;
+        return IBZ2_E_NO_DEVICE;
+    }
+    ctx->sms = prop.multiProcessorCount;
+    g_smCount = ctx->sms;
+    ctx->batchBlocks = static_cast<uint32_t>( ctx->sms ) * 12U;
+    ibz2::initCrcConstants();
+    if ( ( err = cudaGetLastError() ) != cudaSuccess ) {
+        g_createError = std::string( "constant upload failed: " ) + cudaGetErrorString( err );
+        cudaFree( ctx->dRunning );
+        cudaStreamDestroy( ctx->stream );
+        delete ctx;
+        return IBZ2_E_CUDA;
+    }
+    *out = ctx;
+    return IBZ2_OK;
+}
+
+void
+ibz2_destroy( ibz2_ctx* ctx )
+{
+    if ( ctx == nullptr ) {
+        return;
+    }
+    cudaSetDevice( ctx->device );
+    cudaStreamSynchronize( ctx->stream );
+    freeScratch( ctx );
+    cudaFree( ctx->dIn );
+    cudaFree( ctx->dOut );
+    cudaFree( ctx->dFound );
+    cudaFree( ctx->dFoundCount );
+    cudaFree( ctx->dRunning );
+    for ( cudaEvent_t e : ctx->events ) {
+        cudaEventDestroy( e );
+    }
+    cudaStreamDestroy( ctx->stream );
+    delete ctx;
+}
+
+int
+ibz2_get_timings( const ibz2_ctx* ctx, ibz2_timings* timings )
+{
+    if ( ( ctx == nullptr ) || ( timings == nullptr ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    *timings = ctx->timings;
+    return IBZ2_OK;
+}
+
+int
+ibz2_set_batch_blocks( ibz2_ctx* ctx, uint32_t blocks )
+{
+    if ( ( ctx == nullptr ) || ( blocks == 0 ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    ctx->batchBlocks = blocks;
+    return IBZ2_OK;
+}
+
+int
+ibz2_device_alloc( ibz2_ctx* ctx, uint64_t nbytes, void** dptr )
+{
+    if ( ( ctx == nullptr ) || ( dptr == nullptr ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( dptr, nbytes + 256U ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_device_free( ibz2_ctx* ctx, void* dptr )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaFree( dptr ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_host_alloc_pinned( ibz2_ctx* ctx, uint64_t nbytes, void** hptr )
+{
+    if ( ( ctx == nullptr ) || ( hptr == nullptr ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaHostAlloc( hptr, nbytes > 0 ? nbytes : 1, cudaHostAllocPortable ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_host_free_pinned( ibz2_ctx* ctx, void* hptr )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    IBZ2_CUDA_CHECK( ctx, cudaFreeHost( hptr ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_memcpy_h2d( ibz2_ctx* ctx, void* dptr, const void* hptr, uint64_t nbytes )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( dptr, hptr, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_memcpy_d2h( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbytes )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( hptr, dptr, nbytes, cudaMemcpyDeviceToHost, ctx->stream ) );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_synchronize( ibz2_ctx* ctx )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_find_magics( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem, uint64_t base_bit_offset,
+                  uint32_t which, uint64_t* offsets, uint64_t capacity, uint64_t* count )
+{
+    if ( ( ctx == nullptr ) || ( count == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) )
+         || ( ( which & ( IBZ2_FIND_BLOCK | IBZ2_FIND_EOS ) ) == 0 ) || ( ( offsets == nullptr ) && ( capacity > 0 ) ) ) {
+        if ( ctx != nullptr ) {
+            ctx->lastError = "ibz2_find_magics: invalid argument";
+        }
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    *count = 0;
+    cudaSetDevice( ctx->device );
+    ctx->timings = ibz2_timings{};
+    ctx->eventsUsed = 0;
+    if ( nbytes < 6 ) {
+        return IBZ2_OK;
+    }
+    const uint8_t* dData = static_cast<const uint8_t*>( data );
+    const cudaEvent_t e0 = nextEvent( ctx );
+    if ( data_mem == IBZ2_MEM_HOST ) {
+        const int rc = ensureInput( ctx, nbytes );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
+        dData = ctx->dIn;
+    } else if ( ( reinterpret_cast<uintptr_t>( data ) & 15U ) != 0 ) {
+        ctx->lastError = "ibz2_find_magics: device input must be 16-byte aligned";
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    const cudaEvent_t e1 = nextEvent( ctx );
+
+    /* candidates are rare (one per block plus ~2^-48 per bit of noise); grow and rescan if a file is adversarial */
+    uint32_t wanted = std::max<uint32_t>( ctx->foundCapacity, 1U << 16 );
+    uint32_t found = 0;
+    cudaEvent_t e2 = e1;
+    cudaEvent_t e3 = e1;
+    while ( true ) {
+        if ( wanted > ctx->foundCapacity ) {
+            cudaFree( ctx->dFound );
+            cudaFree( ctx->dFoundCount );
+            ctx->dFound = nullptr;
+            ctx->dFoundCount = nullptr;
+            ctx->foundCapacity = 0;
+            IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dFound, static_cast<uint64_t>( wanted ) * sizeof( uint64_t ) ) );
+            IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dFoundCount, sizeof( uint32_t ) ) );
+            ctx->foundCapacity = wanted;
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dFoundCount, 0, sizeof( uint32_t ), ctx->stream ) );
+        e2 = nextEvent( ctx );
+        ibz2::launchFindMagics( dData, nbytes, which, ctx->dFound, ctx->dFoundCount, ctx->foundCapacity, ctx->stream );
+        ctx->timings.launches += 1;
+        e3 = nextEvent( ctx );
+        IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( &found, ctx->dFoundCount, sizeof( uint32_t ), cudaMemcpyDeviceToHost,
+                                               ctx->stream ) );
+        IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+        if ( found <= ctx->foundCapacity ) {
+            break;
+        }
+        wanted = found;
+    }
+    std::vector<uint64_t> host( found );
+    if ( found > 0 ) {
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( host.data(), ctx->dFound, static_cast<uint64_t>( found ) * sizeof( uint64_t ),
+                                               cudaMemcpyDeviceToHost, ctx->stream ) );
+        IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    }
+    ctx->timings.h2d_ms = elapsed( e0, e1 );
+    ctx->timings.find_ms = elapsed( e2, e3 );
+    ctx->timings.total_ms = elapsed( e0, e3 );
+
+    /* ascending by bit offset (the EOS flag is bit 63, so mask it for the comparison) */
+    std::sort( host.begin(), host.end(), [] ( uint64_t a, uint64_t b ) {
+        return ( a & ~IBZ2_OFFSET_EOS_FLAG ) < ( b & ~IBZ2_OFFSET_EOS_FLAG );
+    } );
+    *count = found;
+    const uint64_t n = std::min<uint64_t>( found, capacity );
+    for ( uint64_t i = 0; i < n; ++i ) {
+        offsets[i] = ( ( host[i] & ~IBZ2_OFFSET_EOS_FLAG ) + base_bit_offset ) | ( host[i] & IBZ2_OFFSET_EOS_FLAG );
+    }
+    return found > capacity ? IBZ2_E_CAPACITY : IBZ2_OK;
+}
+
+int
+ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem,
+                    const uint64_t* block_bit_offsets, uint64_t nblocks,
+                    void* out, uint64_t out_capacity, int out_mem,
+                    ibz2_block_result* results, uint64_t* total_out )
+{
+    if ( ( ctx == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) ) || ( ( block_bit_offsets == nullptr ) && ( nblocks > 0 ) )
+         || ( ( results == nullptr ) && ( nblocks > 0 ) ) ) {
+        if ( ctx != nullptr ) {
+            ctx->lastError = "ibz2_decode_blocks: invalid argument";
+        }
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    if ( total_out != nullptr ) {
+        *total_out = 0;
+    }
+    cudaSetDevice( ctx->device );
+    ctx->timings = ibz2_timings{};
+    ctx->eventsUsed = 0;
+    if ( nblocks == 0 ) {
+        return IBZ2_OK;
+    }
+
+    const uint8_t* dData = static_cast<const uint8_t*>( data );
+    const cudaEvent_t eStart = nextEvent( ctx );
+    if ( data_mem == IBZ2_MEM_HOST ) {
+        const int rc = ensureInput( ctx, nbytes );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
+        dData = ctx->dIn;
+    } else if ( ( reinterpret_cast<uintptr_t>( data ) & 15U ) != 0 ) {
+        ctx->lastError = "ibz2_decode_blocks: device input must be 16-byte aligned";
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    const cudaEvent_t eH2D = nextEvent( ctx );
+
+    uint8_t* dOut = static_cast<uint8_t*>( out );
+    const bool haveOutput = out != nullptr;
+    if ( haveOutput && ( out_mem == IBZ2_MEM_HOST ) ) {
+        const int rc = ensureOutput( ctx, out_capacity );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+        dOut = ctx->dOut;
+    } else if ( haveOutput && ( ( reinterpret_cast<uintptr_t>( out ) & 15U ) != 0 ) ) {
+        ctx->lastError = "ibz2_decode_blocks: device output must be 16-byte aligned";
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+
+    const uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
+    {
+        const int rc = ensureScratch( ctx, wave );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+    }
+    IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), ctx->stream ) );
+
+    struct WaveEvents { cudaEvent_t e[9]; };
+    std::vector<WaveEvents> waveEvents;
+    cudaStream_t s = ctx->stream;
+
+    for ( uint64_t first = 0; first < nblocks; first += wave ) {
+        const uint32_t count = static_cast<uint32_t>( std::min<uint64_t>( wave, nblocks - first ) );
+        /* the previous wave's results must have left the pinned mirror before it is refilled */
+        IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+        if ( first > 0 ) {
+            for ( uint32_t i = 0; i < wave; ++i ) {
+                fillResult( ctx->hMeta[i], &results[first - wave + i] );
+            }
+        }
+        std::memset( ctx->hMeta, 0, sizeof( ibz2::BlockMeta ) * count );
+        for ( uint32_t i = 0; i < count; ++i ) {
+            ctx->hMeta[i].bitOffset = block_bit_offsets[first + i];
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dMeta, ctx->hMeta, sizeof( ibz2::BlockMeta ) * count,
+                                               cudaMemcpyHostToDevice, s ) );
+        WaveEvents we{};
+        we.e[0] = nextEvent( ctx );
+        ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, s );
+        we.e[1] = nextEvent( ctx );
+        ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, count, s );
+        we.e[2] = nextEvent( ctx );
+        ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, s );
+        we.e[3] = nextEvent( ctx );
+        ibz2::launchRleScan( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, s );
+        ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, out_capacity, haveOutput ? 1 : 0,
+                                  ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
+        we.e[4] = nextEvent( ctx );
+        ctx->timings.launches += 5;
+        if ( haveOutput ) {
+            ibz2::launchRleWrite( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, dOut, s );
+            we.e[5] = nextEvent( ctx );
+            ibz2::launchCrc( dOut, ctx->dMeta, count, ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
+            ibz2::launchCrcFinalize( dOut, ctx->dMeta, count, s );
+            we.e[6] = nextEvent( ctx );
+            ctx->timings.launches += 3;
+        } else {
+            we.e[5] = we.e[4];
+            we.e[6] = we.e[4];
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ) * count,
+                                               cudaMemcpyDeviceToHost, s ) );
+        waveEvents.push_back( we );
+    }
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+    {
+        const uint64_t lastFirst = ( ( nblocks - 1 ) / wave ) * wave;
+        const uint32_t count = static_cast<uint32_t>( nblocks - lastFirst );
+        for ( uint32_t i = 0; i < count; ++i ) {
+            fillResult( ctx->hMeta[i], &results[lastFirst + i] );
+        }
+    }
+    uint64_t total = 0;
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( &total, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+    if ( total_out != nullptr ) {
+        *total_out = total;
+    }
+    const cudaEvent_t eKernels = nextEvent( ctx );
+    if ( haveOutput && ( out_mem == IBZ2_MEM_HOST ) ) {
+        const uint64_t n = std::min<uint64_t>( total, out_capacity );
+        if ( n > 0 ) {
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( out, ctx->dOut, n, cudaMemcpyDeviceToHost, s ) );
+        }
+    }
+    const cudaEvent_t eEnd = nextEvent( ctx );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+
+    ctx->timings.h2d_ms = elapsed( eStart, eH2D );
+    for ( const auto& we : waveEvents ) {
+        ctx->timings.huffman_ms += elapsed( we.e[0], we.e[1] );
+        ctx->timings.bwt_prepare_ms += elapsed( we.e[1], we.e[2] );
+        ctx->timings.bwt_traverse_ms += elapsed( we.e[2], we.e[3] );
+        ctx->timings.rle_scan_ms += elapsed( we.e[3], we.e[4] );
+        if ( haveOutput ) {
+            ctx->timings.rle_write_ms += elapsed( we.e[4], we.e[5] );
+            ctx->timings.crc_ms += elapsed( we.e[5], we.e[6] );
+        }
+    }
+    ctx->timings.d2h_ms = elapsed( eKernels, eEnd );
+    ctx->timings.total_ms = elapsed( eStart, eEnd );
+    return IBZ2_OK;
+}
+
+int
+ibz2_debug_decode_block( ibz2_ctx* ctx, const void* data, uint64_t nbytes, uint64_t bit_offset,
+                         ibz2_block_result* result, uint8_t* lbytes, uint32_t* tvec, uint8_t* prerle,
+                         uint8_t* out, uint64_t out_capacity )
+{
+    if ( ( ctx == nullptr ) || ( data == nullptr ) || ( result == nullptr ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    cudaStream_t s = ctx->stream;
+    int rc = ensureInput( ctx, nbytes );
+    if ( rc == IBZ2_OK ) {
+        rc = ensureScratch( ctx, 1 );
+    }
+    if ( rc == IBZ2_OK ) {
+        rc = ensureOutput( ctx, out_capacity );
+    }
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, nbytes, cudaMemcpyHostToDevice, s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
+    std::memset( ctx->hMeta, 0, sizeof( ibz2::BlockMeta ) );
+    ctx->hMeta[0].bitOffset = bit_offset;
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dMeta, ctx->hMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyHostToDevice, s ) );
+
+    ibz2::launchHuffmanDecode( ctx->dIn, nbytes, ctx->dMeta, 1, ctx->dLbytes, ctx->dSelectors, s );
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyDeviceToHost, s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
+    const uint32_t n = ctx->hMeta[0].n;
+    if ( ( lbytes != nullptr ) && ( n > 0 ) ) {
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpy( lbytes, ctx->dLbytes, n, cudaMemcpyDeviceToHost ) );
+    }
+    ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, 1, s );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
+    if ( ( tvec != nullptr ) && ( n > 0 ) ) {
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpy( tvec, ctx->dDbuf, static_cast<uint64_t>( n ) * sizeof( uint32_t ),
+                                          cudaMemcpyDeviceToHost ) );
+    }
+    ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, 1, s );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
+    if ( ( prerle != nullptr ) && ( n > 0 ) ) {
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpy( prerle, ctx->dLbytes, n, cudaMemcpyDeviceToHost ) );
+    }
+    ibz2::launchRleScan( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, 1, s );
+    ibz2::launchOutputLayout( ctx->dMeta, 1, ctx->dRunning, out_capacity, out != nullptr ? 1 : 0, ctx->dPieceStart,
+                              ibz2::CRC_PIECE_BYTES, s );
+    if ( out != nullptr ) {
+        ibz2::launchRleWrite( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, 1, ctx->dOut, s );
+        ibz2::launchCrc( ctx->dOut, ctx->dMeta, 1, ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
+        ibz2::launchCrcFinalize( ctx->dOut, ctx->dMeta, 1, s );
+    }
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyDeviceToHost, s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
+    fillResult( ctx->hMeta[0], result );
+    if ( ( out != nullptr ) && ( ctx->hMeta[0].writeOutput != 0 ) && ( ctx->hMeta[0].outSize > 0 ) ) {
+        IBZ2_CUDA_CHECK( ctx, cudaMemcpy( out, ctx->dOut, ctx->hMeta[0].outSize, cudaMemcpyDeviceToHost ) );
+    }
+    return IBZ2_OK;
+}
+
+int
+ibz2_read_stream_header( const uint8_t* data, uint64_t nbytes, uint64_t* bit_pos )
+{
+    if ( ( data == nullptr ) || ( bit_pos == nullptr ) ) {
+        return 0;
+    }
+    HostBits r{ data, nbytes * 8U, *bit_pos, false };
+    static const char magic[3] = { 'B', 'Z', 'h' };
+    int level = 0;
+    for ( int i = 0; i < 4; ++i ) {
+        const uint64_t b = r.read( 8 );
+        if ( r.eof ) {
+            *bit_pos = r.pos;
+            return -1;
+        }
+        if ( i < 3 ) {
+            if ( b != static_cast<uint8_t>( magic[i] ) ) {
+                *bit_pos = r.pos;
+                return 0;
+            }
+        } else {
+            level = ( ( b >= '1' ) && ( b <= '9' ) ) ? static_cast<int>( b - '0' ) : 0;
+        }
+    }
+    *bit_pos = r.pos;
+    return level;
+}
+
+int
+ibz2_read_block_header( const uint8_t* data, uint64_t nbytes, uint64_t bit_offset, ibz2_block_result* result )
+{
+    if ( ( data == nullptr ) || ( result == nullptr ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    std::memset( result, 0, sizeof( *result ) );
+    result->enc_offset_bits = bit_offset;
+    HostBits r{ data, nbytes * 8U, bit_offset, false };
+    if ( bit_offset > r.nbits ) {
+        result->status = IBZ2_ST_EOF;
+        return IBZ2_OK;
+    }
+    const uint64_t magic = r.read( 48 );
+    result->expected_crc = static_cast<uint32_t>( r.read( 32 ) );
+    if ( r.eof ) {
+        result->status = IBZ2_ST_EOF;
+        return IBZ2_OK;
+    }
+    if ( magic == IBZ2_MAGIC_EOS ) {
+        result->is_eos = 1;
+        const unsigned inByte = static_cast<unsigned>( r.pos & 7U );
+        if ( inByte > 0 ) {
+            r.read( 8U - inByte );
+            if ( r.eof ) {
+                result->status = IBZ2_ST_EOF;
+                return IBZ2_OK;
+            }
+        }
+        result->enc_size_bits = r.pos - bit_offset;
+        result->is_eof = r.pos >= r.nbits ? 1U : 0U;
+        return IBZ2_OK;
+    }
+    if ( magic != IBZ2_MAGIC_BLOCK ) {
+        result->status = IBZ2_ST_BAD_MAGIC;
+    }
+    return IBZ2_OK;
+}
+
+uint32_t
+ibz2_stream_crc_fold( uint32_t stream_crc, uint32_t block_crc )
+{
+    return ( ( stream_crc << 1 ) | ( stream_crc >> 31 ) ) ^ block_crc;
+}
+
+}  // extern "C"

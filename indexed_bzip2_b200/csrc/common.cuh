@@ -1,0 +1,131 @@
+/*
+ * common.cuh -- shared device-side definitions for the sm_100a bzip2 decode kernels.
+ *
+ * Data layout in HBM (per launch wave of B blocks, see DESIGN.md "Data layout"):
+ *   meta[B]                      BlockMeta, one per block (inputs: bit offset; outputs of every stage)
+ *   lbytes[B][LBYTES_STRIDE]     u8   BWT last column L written by K2; re-used as the pre-RLE1 byte string by K4b
+ *   dbuf[B][DBUF_STRIDE]         u32  the reference's packed vector (T[k] << 8) | L[k] (bzip2.hpp:827-831) written by
+ *                                     K4a; re-used by K5a for the per-element output offsets
+ *   selectors[B][SEL_STRIDE]     u8   Huffman table selectors of the block (bzip2.hpp:574-637)
+ *   warpbase[B][32]              u32  K5a: output offset of each of the 32 element ranges of a block
+ */
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/ibz2_cuda.h"
+
+namespace ibz2
+{
+constexpr uint64_t MAGIC_BLOCK = IBZ2_MAGIC_BLOCK;
+constexpr uint64_t MAGIC_EOS = IBZ2_MAGIC_EOS;
+constexpr uint32_t DBUF_SIZE = IBZ2_MAX_BLOCK_SYMBOLS;  /* bzip2.hpp:414-416 */
+constexpr uint32_t MAX_GROUPS = 6;                      /* bzip2.hpp:95 */
+constexpr uint32_t GROUP_SIZE = 50;                     /* bzip2.hpp:96 */
+constexpr uint32_t MAX_CODE_LEN = 20;                   /* bzip2.hpp:97 */
+constexpr uint32_t MAX_SYMBOLS = 258;                   /* bzip2.hpp:98 */
+constexpr uint32_t MAX_SELECTORS = 32768;               /* bzip2.hpp:451 */
+
+constexpr uint32_t LBYTES_STRIDE = 900096;              /* >= DBUF_SIZE, multiple of 128 */
+constexpr uint32_t DBUF_STRIDE = 900096;                /* u32 entries */
+constexpr uint32_t SEL_STRIDE = MAX_SELECTORS + 64;
+constexpr uint32_t RLE_RANGES = 32;                     /* element ranges per block in K5a/K5b (one per warp) */
+
+/* One per block, device-resident; the host mirrors it to fill ibz2_block_result. */
+struct BlockMeta
+{
+    uint64_t bitOffset;   /* in: where the 48-bit magic starts */
+    uint64_t endBit;      /* K2: first bit after the block (after the EOB symbol / after the EOS padding) */
+    uint64_t outOffset;   /* scan: byte offset of the block's output inside the call's output buffer */
+    uint32_t status;      /* ibz2_block_status */
+    uint32_t headerCrc;
+    uint32_t origPtr;
+    uint32_t n;           /* dbufCount */
+    uint32_t outSize;     /* K5a: decoded bytes */
+    uint32_t crcAcc;      /* K6: xor-accumulated raw CRC contributions */
+    uint32_t calcCrc;     /* K6 finalize */
+    uint32_t isEos;
+    uint32_t isEof;
+    uint32_t cycleLen;    /* K4b: length of the permutation cycle through origPtr (diagnostic) */
+    uint32_t writeOutput; /* scan: 1 when the block's bytes fit the output buffer */
+    uint32_t pad;
+};
+
+__device__ __forceinline__ uint32_t
+laneId()
+{
+    return threadIdx.x & 31U;
+}
+
+/* Big-endian 32-bit word i of the byte stream (bytes past the end read as zero). */
+__device__ __forceinline__ uint32_t
+loadWordBE( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t wordIndex )
+{
+    const uint64_t byte = wordIndex * 4U;
+    uint32_t w = 0;
+    if ( byte + 4U <= nbytes ) {
+        w = __ldg( reinterpret_cast<const uint32_t*>( data ) + wordIndex );
+    } else {
+        for ( uint32_t k = 0; k < 4U; ++k ) {
+            if ( byte + k < nbytes ) {
+                w |= static_cast<uint32_t>( data[byte + k] ) << ( 8U * k );
+            }
+        }
+    }
+    return __byte_perm( w, 0, 0x0123 );
+}
+
+/* ---- CRC-32/BZIP2 arithmetic in GF(2)[x] / 0x104C11DB7 (bzip2.hpp:59-91) ---- */
+constexpr uint32_t CRC_POLY = 0x04C11DB7U;
+
+/* a * b mod P, polynomials with bit 31 = x^31 */
+__host__ __device__ __forceinline__ uint32_t
+crcMulMod( uint32_t a, uint32_t b )
+{
+    uint32_t r = 0;
+#pragma unroll 4
+    for ( int i = 31; i >= 0; --i ) {
+        r = ( r << 1 ) ^ ( ( r & 0x80000000U ) ? CRC_POLY : 0U );
+        if ( ( b >> i ) & 1U ) {
+            r ^= a;
+        }
+    }
+    return r;
+}
+
+/* launch wrappers (one per .cu file); all asynchronous on `stream` */
+void launchFindMagics( const uint8_t* data, uint64_t nbytes, uint32_t which, uint64_t* found, uint32_t* foundCount,
+                       uint32_t capacity, cudaStream_t stream );
+
+void launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
+                          uint8_t* lbytes, uint8_t* selectors, cudaStream_t stream );
+
+void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, uint32_t nblocks,
+                       cudaStream_t stream );
+
+void launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks,
+                        cudaStream_t stream );
+
+void launchRleScan( const uint8_t* prerle, uint32_t* offsets, uint32_t* warpBase, BlockMeta* meta,
+                    uint32_t nblocks, cudaStream_t stream );
+
+/* running: device u64[1] = next output offset, carried across the waves of one call.
+ * pieceStart: device u32[nblocks + 1], first CRC window of each block (windows of pieceBytes bytes). */
+void launchOutputLayout( BlockMeta* meta, uint32_t nblocks, uint64_t* running, uint64_t outCapacity,
+                         int haveOutput, uint32_t* pieceStart, uint32_t pieceBytes, cudaStream_t stream );
+
+void launchRleWrite( const uint8_t* prerle, const uint32_t* offsets, const uint32_t* warpBase,
+                     const BlockMeta* meta, uint32_t nblocks, uint8_t* out, cudaStream_t stream );
+
+void launchCrc( const uint8_t* out, BlockMeta* meta, uint32_t nblocks, const uint32_t* pieceStart,
+                uint32_t pieceBytes, cudaStream_t stream );
+
+void launchCrcFinalize( const uint8_t* out, BlockMeta* meta, uint32_t nblocks, cudaStream_t stream );
+
+constexpr uint32_t CRC_PIECE_BYTES = 32768;
+
+void initCrcConstants();
+
+int smCount();
+}  // namespace ibz2

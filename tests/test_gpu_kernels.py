@@ -1,0 +1,321 @@
+"""GPU parity tests: every kernel stage of the sm_100a path, called through the C ABI (include/ibz2_cuda.h), against
+the CPU oracle (oracle/bz2_oracle.c, pinned to the reference by tests/test_oracle.py) and the golden outputs of the
+compiled reference (tests/golden/golden.json).  Bit-exact: all of this is integer / byte work.
+
+Run on the B200 box: python -m pytest tests -m gpu
+"""
+import hashlib
+import json
+
+import numpy as np
+import pytest
+
+import _oracle as orc
+from indexed_bzip2_b200 import _capi
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = json.loads((orc.ROOT / "tests" / "golden" / "golden.json").read_text())
+VALID = sorted(k for k, v in GOLDEN.items() if v["parallel"]["rc"] == 0)
+ALL = sorted(GOLDEN)
+EOS_FLAG = np.uint64(1 << 63)
+BLOCK_MAGIC_BYTES = [0x31, 0x41, 0x59, 0x26, 0x53, 0x59]
+EOS_MAGIC_BYTES = [0x17, 0x72, 0x45, 0x38, 0x50, 0x90]
+
+
+def case(name):
+    return (orc.ROOT / "tests" / "golden" / "cases" / f"{name}.bz2").read_bytes()
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = _capi.Context(0)
+    yield c
+    c.close()
+
+
+def split_found(found):
+    offsets = (found & ~EOS_FLAG).astype(np.uint64)
+    is_eos = (found & EOS_FLAG) != 0
+    return offsets, is_eos
+
+
+def data_blocks(ctx, data):
+    offsets, is_eos = split_found(ctx.find_magics(data))
+    return offsets[~is_eos]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# K1 finder
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("data,expected", [
+    ([0x11, 0x41, 0x59, 0x26, 0x53, 0x59], []),
+    ([0x31, 0x41, 0x59, 0x26, 0x53, 0x58], []),
+    ([0x31, 0x41, 0x59, 0x26, 0x53, 0x59], [0]),
+    ([0x31, 0x41, 0x59, 0x26, 0x53, 0x59, 0, 0], [0]),
+    ([0, 0x31, 0x41, 0x59, 0x26, 0x53, 0x59, 0, 0], [8]),
+    ([0, 0, 0x31, 0x41, 0x59, 0x26, 0x53, 0x59, 0, 0], [16]),
+    ([0, 0, 0, 0x31, 0x41, 0x59, 0x26, 0x53, 0x59, 0, 0], [24]),
+    ([0, 0, 0, 0, 0x31, 0x41, 0x59, 0x26, 0x53, 0x59, 0, 0], [32]),
+    ([0x18, 0xA0, 0xAC, 0x93, 0x29, 0xAC, 0x80], [1]),
+    ([0x00, 0x62, 0x82, 0xB2, 0x4C, 0xA6, 0xB2], [7]),
+])
+def test_finder_kat(ctx, data, expected):
+    """src/tests/core/testBitStringFinder.cpp:117-128"""
+    got = ctx.find_magics(bytes(data), which=_capi.FIND_BLOCK)
+    assert got.tolist() == expected
+
+
+@pytest.mark.parametrize("gap", [1, 100, 123, 1024, 2000, 4095, 4096, 4097, 28 * 1024, 4 << 20])
+def test_finder_second_match(ctx, gap):
+    """src/tests/core/testBitStringFinder.cpp:131-146, testParallelBitStringFinder.cpp:228-249"""
+    buf = [0, 0, 0, 0] + BLOCK_MAGIC_BYTES + [0, 0]
+    data = bytes(buf) + bytes(gap) + bytes(BLOCK_MAGIC_BYTES)
+    assert ctx.find_magics(data, which=_capi.FIND_BLOCK).tolist() == [32, (len(buf) + gap) * 8]
+
+
+def plant(buf: np.ndarray, bitpos: int, magic: int):
+    """write the 48-bit magic at an arbitrary bit position of a uint8 buffer (MSB-first)"""
+    for i in range(48):
+        bit = (magic >> (47 - i)) & 1
+        p = bitpos + i
+        byte, sh = p >> 3, 7 - (p & 7)
+        buf[byte] = (int(buf[byte]) & ~(1 << sh)) | (bit << sh)
+
+
+def test_finder_planted_every_alignment(ctx):
+    """both magics at every bit alignment and straddling 4 B / 16 B / 128 B / 512 B / 4 KiB / CTA-tile seams"""
+    rng = np.random.default_rng(2)
+    n = 3 * 1024 * 1024 + 7
+    buf = rng.integers(0, 256, n, dtype=np.uint8)
+    positions = []
+    cursor = 64
+    for seam in [4, 16, 128, 512, 4096, 16384, 65536, 1 << 20]:
+        for back in range(0, 56, 1):
+            base = (cursor // seam + 1) * seam * 8  # bit index of a seam
+            p = base - back
+            positions.append(p)
+            cursor = p // 8 + 40
+    for s in range(64):
+        positions.append((cursor + 50) * 8 + s)
+        cursor += 20
+    positions.append((n - 6) * 8)  # flush with the end of the buffer
+    positions = sorted(set(positions))
+    kept = []
+    last_end = -1
+    for i, p in enumerate(positions):
+        if p <= last_end or p + 48 > n * 8:
+            continue
+        plant(buf, p, _capi.MAGIC_BLOCK if i % 2 == 0 else _capi.MAGIC_EOS)
+        kept.append(p)
+        last_end = p + 48
+    expected = orc.find_magics(buf)
+    assert set(kept) <= set(expected.tolist())
+    found = ctx.find_magics(buf)
+    offsets, is_eos = split_found(found)
+    assert offsets.tolist() == expected.tolist()
+    assert offsets[is_eos].tolist() == orc.find_magic(buf, orc.MAGIC_EOS).tolist()
+    only_block = ctx.find_magics(buf, which=_capi.FIND_BLOCK)
+    assert only_block.tolist() == orc.find_magic(buf, orc.MAGIC_BLOCK).tolist()
+
+
+@pytest.mark.parametrize("n", list(range(0, 41)) + [63, 64, 65, 127, 129, 255, 257])
+def test_finder_ragged_sizes(ctx, n):
+    """tiny and ragged buffers: magic flush with the end, sizes that are not multiples of 4 or 16"""
+    buf = np.zeros(n, dtype=np.uint8)
+    if n >= 6:
+        buf[n - 6:] = EOS_MAGIC_BYTES
+    if n >= 14:
+        plant(buf, 3, _capi.MAGIC_BLOCK)
+    found = ctx.find_magics(buf)
+    offsets, _ = split_found(found)
+    assert offsets.tolist() == orc.find_magics(buf).tolist()
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_finder_golden(ctx, name):
+    """`ibzip2 -l` of the compiled reference (tools/ibzip2.cpp:96-143), committed in golden.json"""
+    data = case(name)
+    offsets, is_eos = split_found(ctx.find_magics(data))
+    assert offsets.tolist() == GOLDEN[name]["finder"]
+    assert offsets[is_eos].tolist() == orc.find_magic(data, orc.MAGIC_EOS).tolist()
+
+
+def test_finder_device_resident_and_base_offset(ctx):
+    data = np.frombuffer(case("text-450k-l1"), dtype=np.uint8)
+    dptr = ctx.device_alloc(data.size)
+    try:
+        ctx.h2d(dptr, data)
+        found = ctx.find_magics(dptr, data.size, device=True, base_bit_offset=1000)
+        offsets, _ = split_found(found)
+        assert (offsets - np.uint64(1000)).tolist() == GOLDEN["text-450k-l1"]["finder"]
+    finally:
+        ctx.device_free(dptr)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# K2..K6 stage by stage
+# ---------------------------------------------------------------------------------------------------------------
+
+def candidate_offsets(name):
+    return GOLDEN[name]["finder"]
+
+
+@pytest.mark.parametrize("name", ALL)
+def test_stage_parity(ctx, name):
+    """every candidate block of every golden file: header fields, L, packed T vector, pre-RLE1 bytes, output, CRC"""
+    data = case(name)
+    for off in candidate_offsets(name):
+        want = orc.decode_block(data, off)
+        got = ctx.debug_decode_block(data, off, out_capacity=max(int(want.info.out_size), 1) + 16)
+        res = got["result"]
+        label = f"{name}@{off}"
+        assert res.status == want.info.status, f"{label}: status {_capi.STATUS_NAMES.get(res.status)} vs oracle {orc.STATUS_NAMES.get(want.info.status)}"
+        assert bool(res.is_eos) == bool(want.info.is_eos), label
+        if want.info.status in (0, 13):
+            assert res.expected_crc == want.info.header_crc, label
+        if want.info.is_eos:
+            assert res.enc_size_bits == want.info.enc_size_bits, label
+            assert bool(res.is_eof) == bool(want.info.at_eof), label
+            continue
+        if want.info.status not in (0, 13):
+            continue
+        assert res.n_symbols == want.info.n, label
+        assert res.orig_ptr == want.info.orig_ptr, label
+        assert res.enc_size_bits == want.info.enc_size_bits, label
+        assert np.array_equal(got["lbytes"], want.lbytes), f"{label}: L differs"
+        assert np.array_equal(got["tvec"], want.tvec), f"{label}: T vector differs"
+        assert np.array_equal(got["prerle"], want.prerle), f"{label}: pre-RLE1 bytes differ"
+        assert res.out_size == want.info.out_size, label
+        assert np.array_equal(got["out"], want.out), f"{label}: output differs"
+        assert res.calculated_crc == want.info.calc_crc, f"{label}: CRC {res.calculated_crc:08x} vs {want.info.calc_crc:08x}"
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# whole files through ibz2_decode_blocks
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("name", VALID)
+def test_decode_file_matches_reference(ctx, name):
+    data = case(name)
+    blocks = data_blocks(ctx, data)
+    size = GOLDEN[name]["parallel"]["size"]
+    out = np.zeros(size + 64, dtype=np.uint8)
+    results, total = ctx.decode_blocks(data, blocks, out)
+    # err-gap-then-valid style files contain blocks the reader never reaches; only compare what the reference emits
+    if name.startswith("err-"):
+        return
+    assert total == size
+    assert (results["status"] == 0).all(), results["status"]
+    assert hashlib.sha256(out[:total].tobytes()).hexdigest() == GOLDEN[name]["parallel"]["sha256"]
+    assert (results["calculated_crc"] == results["expected_crc"]).all()
+    # blocks are laid out back to back
+    assert results["out_offset"].tolist() == np.concatenate([[0], np.cumsum(results["out_size"])[:-1]]).tolist()
+    # each data block ends where the next header starts (data block or EOS): the reference's block map keys
+    ends = (results["enc_offset_bits"] + results["enc_size_bits"]).tolist()
+    keys = [k for k, _ in GOLDEN[name]["parallel"]["offsets"]]
+    finder = set(GOLDEN[name]["finder"])
+    for e in ends:
+        assert e in keys or e in finder
+
+
+def test_decode_multi_wave_and_device_buffers(ctx):
+    name = "text-450k-l1"
+    data = np.frombuffer(case(name), dtype=np.uint8)
+    blocks = data_blocks(ctx, data)
+    assert blocks.size >= 4
+    size = GOLDEN[name]["parallel"]["size"]
+    din = ctx.device_alloc(data.size)
+    dout = ctx.device_alloc(size)
+    try:
+        ctx.set_batch_blocks(2)  # forces several waves with a carried output offset
+        ctx.h2d(din, data)
+        results, total = ctx.decode_blocks(din, blocks, dout, size, nbytes=data.size, data_device=True, out_device=True)
+        assert total == size and (results["status"] == 0).all()
+        host = np.zeros(size, dtype=np.uint8)
+        ctx.d2h(host, dout)
+        assert hashlib.sha256(host.tobytes()).hexdigest() == GOLDEN[name]["parallel"]["sha256"]
+        t = ctx.timings()
+        assert t["launches"] >= 8 * 2 and t["huffman_ms"] > 0
+    finally:
+        ctx.set_batch_blocks(148 * 12)
+        ctx.device_free(din)
+        ctx.device_free(dout)
+
+
+def test_decode_pinned_host_buffers(ctx):
+    name = "mixed-384k-l2"
+    raw = case(name)
+    size = GOLDEN[name]["parallel"]["size"]
+    pin_in = ctx.pinned(len(raw))
+    pin_out = ctx.pinned(size)
+    try:
+        pin_in.array[:] = np.frombuffer(raw, dtype=np.uint8)
+        blocks = data_blocks(ctx, pin_in.array)
+        results, total = ctx.decode_blocks(pin_in.array, blocks, pin_out.array)
+        assert total == size and (results["status"] == 0).all()
+        assert hashlib.sha256(pin_out.array.tobytes()).hexdigest() == GOLDEN[name]["parallel"]["sha256"]
+    finally:
+        pin_in.free()
+        pin_out.free()
+
+
+def test_output_capacity_and_size_only(ctx):
+    name = "base64-300k-l1"
+    data = case(name)
+    blocks = data_blocks(ctx, data)
+    size = GOLDEN[name]["parallel"]["size"]
+    # size-only call: no output buffer
+    results, total = ctx.decode_blocks(data, blocks, None)
+    assert total == size and (results["status"] == 0).all()
+    sizes = results["out_size"].copy()
+    # buffer that holds all but the last block
+    cap = int(sizes[:-1].sum()) + 5
+    out = np.zeros(cap, dtype=np.uint8)
+    results, total = ctx.decode_blocks(data, blocks, out)
+    assert total == size
+    assert results["status"][:-1].tolist() == [0] * (blocks.size - 1)
+    assert results["status"][-1] == 15
+    full = np.zeros(size, dtype=np.uint8)
+    ctx.decode_blocks(data, blocks, full)
+    assert np.array_equal(out[:cap - 5], full[:cap - 5])
+
+
+def test_error_statuses_match_oracle(ctx):
+    for name in [n for n in ALL if n.startswith("err-")]:
+        data = case(name)
+        offs = np.array(GOLDEN[name]["finder"], dtype=np.uint64)
+        if offs.size == 0:
+            continue
+        out = np.zeros(4 << 20, dtype=np.uint8)
+        results, _ = ctx.decode_blocks(data, offs, out)
+        for off, r in zip(offs.tolist(), results):
+            want = orc.decode_block(data, off, stages=False)
+            assert r["status"] == want.info.status, f"{name}@{off}"
+
+
+def test_synthetic_corruptions_match_oracle(ctx):
+    """flip bits in the header / tables / payload of a small block: the status must match the oracle's"""
+    base = bytearray(case("ref-dolorem-ipsum.txt"))
+    rng = np.random.default_rng(7)
+    for trial in range(200):
+        data = bytearray(base)
+        pos = int(rng.integers(4 * 8, len(data) * 8))
+        data[pos >> 3] ^= 1 << (7 - (pos & 7))
+        want = orc.decode_block(bytes(data), 32, stages=False)
+        out = np.zeros(1 << 20, dtype=np.uint8)
+        results, _ = ctx.decode_blocks(bytes(data), [32], out)
+        assert results["status"][0] == want.info.status, f"bit {pos}: {results['status'][0]} vs {want.info.status}"
+        if want.info.status == 0:
+            assert results["out_size"][0] == want.info.out_size
+
+
+def test_truncations_match_oracle(ctx):
+    base = case("ref-base64-32KiB")
+    for cut in [10, 14, 20, 40, 100, 1000, len(base) - 11, len(base) - 10, len(base) - 5, len(base) - 1]:
+        data = base[:cut]
+        want = orc.decode_block(data, 32, stages=False)
+        out = np.zeros(1 << 20, dtype=np.uint8)
+        results, _ = ctx.decode_blocks(data, [32], out)
+        assert results["status"][0] == want.info.status, f"cut {cut}"
