@@ -1,6 +1,8 @@
 /*
- * K4a -- inverse-BWT preparation: the stable counting-sort scatter that builds the reference's packed vector
- *   dbuf[cum[L[i]]++] = ( i << 8 ) | L[i]
+ * K4a -- inverse-BWT preparation: the stable counting-sort scatter  T[cum[L[i]]++] = i, packed as
+ *   dbuf[k] = ( T[k] << 8 ) | L[T[k]]
+ * (the reference packs ( T[k] << 8 ) | L[k]; carrying the byte of the position the entry points TO saves the
+ * traversal's first hop and needs no second random access here, since L[T[k]] = L[i] is the byte in hand),
  * i.e. BurrowsWheelerTransformData::prepare (indexed_bzip2/bzip2.hpp:810-847) including the 256-bin byte histogram
  * that the reference accumulates during readBlockData (bzip2.hpp:698,759,788).  One CTA per block.
  *

@@ -1,12 +1,13 @@
 /*
  * K4b -- inverse-BWT traversal: the N-step walk  pos = T[pos], emit L[pos]  that starts at T[origPtr]
+ * (with K4a's packing, entry k carries L[T[k]], so the walk reads entry origPtr first: p0 = origPtr)
  * (BurrowsWheelerTransformData::decodeBlock, indexed_bzip2/bzip2.hpp:863-879, without its RLE1 / CRC half).
  *
  * The walk is a dependent-load chain, so it is broken up by list ranking.  One CTA per block:
  *   pass A  every position that is a multiple of SPACING is a "splitter".  Each thread walks from its splitters until
  *           the next splitter, recording the segment's length and successor.  Segment lengths are geometric, so each
  *           lane keeps walking its own list of splitters (no waiting for the slowest lane).  The segment that passes
- *           through the start position p0 = T[origPtr] is remembered (sstar, kstar).
+ *           through the start position p0 is remembered (sstar, kstar).
  *   rank    the successor list of the <= 14063 segments is ranked in shared memory by pointer jumping (Wyllie), with the
  *           list cut at sstar; that gives every segment on p0's cycle its output offset.
  *   pass B  every ranked segment is walked again and its bytes are written to their final positions.
@@ -54,7 +55,10 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
     uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
     const uint32_t tid = threadIdx.x;
     const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
-    const uint32_t p0 = __ldg( dbuf + bm.origPtr ) >> 8;  /* bzip2.hpp:835-838 */
+    /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's ( T[k] << 8 ) | L[k],
+     * so the walk starts at origPtr itself and every load yields the output byte and the next position at once
+     * (the reference first hops to T[origPtr], bzip2.hpp:835-838, and reads L at the position it arrives at). */
+    const uint32_t p0 = bm.origPtr;
 
     if ( tid == 0 ) {
         sh.sstar = -1;
