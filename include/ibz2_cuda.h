@@ -11,6 +11,7 @@
  *                         and tools/ibzip2.cpp:96-143 (findCompressedBlocks, both magics, sorted)
  *   ibz2_decode_blocks    indexed_bzip2/BZ2BlockFetcher.hpp:85-138 (decodeBlock: Block ctor + readBlockData + read
  *                         until eob) i.e. indexed_bzip2/bzip2.hpp:479-910, for a whole batch of block offsets
+ *   ibz2_decode_buffer    indexed_bzip2/ParallelBZ2Reader.hpp:167-269 (finder + fetcher over an in-memory file)
  *   ibz2_read_block_header indexed_bzip2/BZ2BlockFetcher.hpp:64-82 (readBlockHeader: EOS probe), host-side, no GPU
  *   ibz2_read_stream_header indexed_bzip2/bzip2.hpp:114-142 (readBzip2Header), host-side, no GPU
  *   ibz2_stream_crc_fold  indexed_bzip2/BZ2Reader.hpp:481-484 (fold of the per-block CRCs the GPU computed)
@@ -148,6 +149,23 @@ int ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int da
                         const uint64_t* block_bit_offsets, uint64_t nblocks,
                         void* out, uint64_t out_capacity, int out_mem,
                         ibz2_block_result* results, uint64_t* total_out );
+
+/* ---- K1 + K2..K6 in one call: what ParallelBZ2Reader does for a file that is in memory ----
+ * Copies `data` to the GPU once (host input), finds every data-block magic in it, decodes the blocks whose magic
+ * starts in [first_bit, last_bit) (pass 0 and UINT64_MAX for all; a rank of a multi-GPU job passes its share) in
+ * file order and returns their bytes back to back in `out`.  results: HOST array of results_capacity entries;
+ * *nblocks receives the number of blocks decoded (IBZ2_E_CAPACITY if results is too small).
+ * Stands in for the BlockFinder thread + BlockFetcher pool of ParallelBZ2Reader::read
+ * (indexed_bzip2/ParallelBZ2Reader.hpp:167-269, core/BlockFinder.hpp:164-197, core/BlockFetcher.hpp:244-317). */
+int ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem,
+                        uint64_t first_bit, uint64_t last_bit,
+                        void* out, uint64_t out_capacity, int out_mem,
+                        ibz2_block_result* results, uint64_t results_capacity, uint64_t* nblocks,
+                        uint64_t* total_out );
+
+/* CUDA-event stopwatch on the context's stream: brackets any number of calls (device time, not wall clock). */
+int ibz2_timer_start( ibz2_ctx* ctx );
+int ibz2_timer_stop( ibz2_ctx* ctx, float* milliseconds );
 
 /* ---- test/diagnostic hook: stage-level intermediates of ONE block, for parity tests against the oracle ----
  * Any of the host output pointers may be NULL.  lbytes: n_symbols bytes (the BWT last column, bzip2.hpp:759,788);

@@ -66,7 +66,7 @@ EXPORTS = [
     "ibz2_abi_version", "ibz2_device_count", "ibz2_create", "ibz2_destroy", "ibz2_last_error", "ibz2_get_timings",
     "ibz2_set_batch_blocks", "ibz2_device_alloc", "ibz2_device_free", "ibz2_host_alloc_pinned",
     "ibz2_host_free_pinned", "ibz2_memcpy_h2d", "ibz2_memcpy_d2h", "ibz2_synchronize", "ibz2_find_magics",
-    "ibz2_decode_blocks", "ibz2_debug_decode_block", "ibz2_read_stream_header", "ibz2_read_block_header",
+    "ibz2_decode_blocks", "ibz2_decode_buffer", "ibz2_timer_start", "ibz2_timer_stop", "ibz2_debug_decode_block", "ibz2_read_stream_header", "ibz2_read_block_header",
     "ibz2_stream_crc_fold",
 ]
 
@@ -114,6 +114,12 @@ def load_library() -> C.CDLL:
     L.ibz2_find_magics.argtypes = [vp, vp, u64, i32, u64, u32, vp, u64, C.POINTER(u64)]
     L.ibz2_decode_blocks.restype = i32
     L.ibz2_decode_blocks.argtypes = [vp, vp, u64, i32, vp, u64, vp, u64, i32, vp, C.POINTER(u64)]
+    L.ibz2_decode_buffer.restype = i32
+    L.ibz2_decode_buffer.argtypes = [vp, vp, u64, i32, u64, u64, vp, u64, i32, vp, u64, C.POINTER(u64), C.POINTER(u64)]
+    L.ibz2_timer_start.restype = i32
+    L.ibz2_timer_start.argtypes = [vp]
+    L.ibz2_timer_stop.restype = i32
+    L.ibz2_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.ibz2_debug_decode_block.restype = i32
     L.ibz2_debug_decode_block.argtypes = [vp, vp, u64, u64, C.POINTER(BlockResult), vp, vp, vp, vp, u64]
     L.ibz2_read_stream_header.restype = i32
@@ -269,6 +275,41 @@ class Context:
                                                 MEM_DEVICE if out_device else MEM_HOST,
                                                 results.ctypes.data, C.byref(total)))
         return results, int(total.value)
+
+    def decode_buffer(self, data, out=None, out_capacity: int = 0, *, nbytes: int | None = None,
+                      data_device: bool = False, out_device: bool = False, first_bit: int = 0,
+                      last_bit: int = (1 << 64) - 1, max_blocks: int | None = None):
+        """find + decode in one call. Returns (results structured array, total_out)."""
+        if data_device:
+            daddr, n = int(data), int(nbytes)
+        else:
+            a = as_u8(data)
+            daddr, n = a.ctypes.data, a.size if nbytes is None else nbytes
+        if out is None:
+            oaddr, cap = 0, 0
+        elif out_device:
+            oaddr, cap = int(out), int(out_capacity)
+        else:
+            oaddr, cap = out.ctypes.data, out.nbytes if not out_capacity else out_capacity
+        capacity = max_blocks if max_blocks is not None else max(16, n // 64)  # a block takes > 100 bytes
+        while True:
+            results = np.zeros(capacity, dtype=BLOCK_RESULT_DTYPE)
+            nblocks, total = C.c_uint64(), C.c_uint64()
+            rc = self.lib.ibz2_decode_buffer(self.handle, daddr, n, MEM_DEVICE if data_device else MEM_HOST,
+                                             first_bit, last_bit, oaddr, cap, MEM_DEVICE if out_device else MEM_HOST,
+                                             results.ctypes.data, capacity, C.byref(nblocks), C.byref(total))
+            self._check(rc, allow=(4,))
+            if rc == 0:
+                return results[:nblocks.value], int(total.value)
+            capacity = int(nblocks.value)
+
+    def timer_start(self):
+        self._check(self.lib.ibz2_timer_start(self.handle))
+
+    def timer_stop(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.ibz2_timer_stop(self.handle, C.byref(ms)))
+        return float(ms.value)
 
     def debug_decode_block(self, data, bit_offset: int, out_capacity: int = 0):
         """Stage-level intermediates of one block: dict(result, lbytes, tvec, prerle, out)."""

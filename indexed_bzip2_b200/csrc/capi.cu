@@ -48,6 +48,8 @@ struct ibz2_ctx
     uint32_t foundCapacity = 0;
 
     std::vector<cudaEvent_t> events;
+    cudaEvent_t timerStart = nullptr;
+    cudaEvent_t timerStop = nullptr;
     size_t eventsUsed = 0;
     ibz2_timings timings{};
 };
@@ -303,6 +305,10 @@ ibz2_destroy( ibz2_ctx* ctx )
     for ( cudaEvent_t e : ctx->events ) {
         cudaEventDestroy( e );
     }
+    if ( ctx->timerStart != nullptr ) {
+        cudaEventDestroy( ctx->timerStart );
+        cudaEventDestroy( ctx->timerStop );
+    }
     cudaStreamDestroy( ctx->stream );
     delete ctx;
 }
@@ -405,44 +411,40 @@ ibz2_synchronize( ibz2_ctx* ctx )
     return IBZ2_OK;
 }
 
-int
-ibz2_find_magics( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem, uint64_t base_bit_offset,
-                  uint32_t which, uint64_t* offsets, uint64_t capacity, uint64_t* count )
+/* ---------------- internal building blocks of the three decode entry points ---------------- */
+
+/* Makes the compressed bytes available on the device: copies host input into the context's staging buffer. */
+static int
+stageInput( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem, const uint8_t** dData, const char* who )
 {
-    if ( ( ctx == nullptr ) || ( count == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) )
-         || ( ( which & ( IBZ2_FIND_BLOCK | IBZ2_FIND_EOS ) ) == 0 ) || ( ( offsets == nullptr ) && ( capacity > 0 ) ) ) {
-        if ( ctx != nullptr ) {
-            ctx->lastError = "ibz2_find_magics: invalid argument";
-        }
-        return IBZ2_E_INVALID_ARGUMENT;
-    }
-    *count = 0;
-    cudaSetDevice( ctx->device );
-    ctx->timings = ibz2_timings{};
-    ctx->eventsUsed = 0;
-    if ( nbytes < 6 ) {
-        return IBZ2_OK;
-    }
-    const uint8_t* dData = static_cast<const uint8_t*>( data );
-    const cudaEvent_t e0 = nextEvent( ctx );
+    *dData = static_cast<const uint8_t*>( data );
     if ( data_mem == IBZ2_MEM_HOST ) {
         const int rc = ensureInput( ctx, nbytes );
         if ( rc != IBZ2_OK ) {
             return rc;
         }
-        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
-        dData = ctx->dIn;
+        if ( nbytes > 0 ) {
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
+        }
+        *dData = ctx->dIn;
     } else if ( ( reinterpret_cast<uintptr_t>( data ) & 15U ) != 0 ) {
-        ctx->lastError = "ibz2_find_magics: device input must be 16-byte aligned";
+        ctx->lastError = std::string( who ) + ": device input must be 16-byte aligned";
         return IBZ2_E_INVALID_ARGUMENT;
     }
-    const cudaEvent_t e1 = nextEvent( ctx );
+    return IBZ2_OK;
+}
 
+/* K1 on device-resident bytes; `host` receives the matches sorted by bit offset (EOS flag in bit 63). */
+static int
+findOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, uint32_t which, std::vector<uint64_t>& host )
+{
+    host.clear();
+    if ( nbytes < 6 ) {
+        return IBZ2_OK;
+    }
     /* candidates are rare (one per block plus ~2^-48 per bit of noise); grow and rescan if a file is adversarial */
     uint32_t wanted = std::max<uint32_t>( ctx->foundCapacity, 1U << 16 );
     uint32_t found = 0;
-    cudaEvent_t e2 = e1;
-    cudaEvent_t e3 = e1;
     while ( true ) {
         if ( wanted > ctx->foundCapacity ) {
             cudaFree( ctx->dFound );
@@ -455,92 +457,39 @@ ibz2_find_magics( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem
             ctx->foundCapacity = wanted;
         }
         IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dFoundCount, 0, sizeof( uint32_t ), ctx->stream ) );
-        e2 = nextEvent( ctx );
+        const cudaEvent_t e0 = nextEvent( ctx );
         ibz2::launchFindMagics( dData, nbytes, which, ctx->dFound, ctx->dFoundCount, ctx->foundCapacity, ctx->stream );
         ctx->timings.launches += 1;
-        e3 = nextEvent( ctx );
+        const cudaEvent_t e1 = nextEvent( ctx );
         IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
         IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( &found, ctx->dFoundCount, sizeof( uint32_t ), cudaMemcpyDeviceToHost,
                                                ctx->stream ) );
         IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+        ctx->timings.find_ms += elapsed( e0, e1 );
         if ( found <= ctx->foundCapacity ) {
             break;
         }
         wanted = found;
     }
-    std::vector<uint64_t> host( found );
+    host.resize( found );
     if ( found > 0 ) {
         IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( host.data(), ctx->dFound, static_cast<uint64_t>( found ) * sizeof( uint64_t ),
                                                cudaMemcpyDeviceToHost, ctx->stream ) );
         IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
     }
-    ctx->timings.h2d_ms = elapsed( e0, e1 );
-    ctx->timings.find_ms = elapsed( e2, e3 );
-    ctx->timings.total_ms = elapsed( e0, e3 );
-
     /* ascending by bit offset (the EOS flag is bit 63, so mask it for the comparison) */
     std::sort( host.begin(), host.end(), [] ( uint64_t a, uint64_t b ) {
         return ( a & ~IBZ2_OFFSET_EOS_FLAG ) < ( b & ~IBZ2_OFFSET_EOS_FLAG );
     } );
-    *count = found;
-    const uint64_t n = std::min<uint64_t>( found, capacity );
-    for ( uint64_t i = 0; i < n; ++i ) {
-        offsets[i] = ( ( host[i] & ~IBZ2_OFFSET_EOS_FLAG ) + base_bit_offset ) | ( host[i] & IBZ2_OFFSET_EOS_FLAG );
-    }
-    return found > capacity ? IBZ2_E_CAPACITY : IBZ2_OK;
+    return IBZ2_OK;
 }
 
-int
-ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem,
-                    const uint64_t* block_bit_offsets, uint64_t nblocks,
-                    void* out, uint64_t out_capacity, int out_mem,
-                    ibz2_block_result* results, uint64_t* total_out )
+/* K2..K6 over device-resident input, in waves of at most ctx->batchBlocks blocks; dOut may be null (sizes only). */
+static int
+decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint64_t* offsets, uint64_t nblocks,
+                uint8_t* dOut, uint64_t outCapacity, ibz2_block_result* results, uint64_t* totalOut )
 {
-    if ( ( ctx == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) ) || ( ( block_bit_offsets == nullptr ) && ( nblocks > 0 ) )
-         || ( ( results == nullptr ) && ( nblocks > 0 ) ) ) {
-        if ( ctx != nullptr ) {
-            ctx->lastError = "ibz2_decode_blocks: invalid argument";
-        }
-        return IBZ2_E_INVALID_ARGUMENT;
-    }
-    if ( total_out != nullptr ) {
-        *total_out = 0;
-    }
-    cudaSetDevice( ctx->device );
-    ctx->timings = ibz2_timings{};
-    ctx->eventsUsed = 0;
-    if ( nblocks == 0 ) {
-        return IBZ2_OK;
-    }
-
-    const uint8_t* dData = static_cast<const uint8_t*>( data );
-    const cudaEvent_t eStart = nextEvent( ctx );
-    if ( data_mem == IBZ2_MEM_HOST ) {
-        const int rc = ensureInput( ctx, nbytes );
-        if ( rc != IBZ2_OK ) {
-            return rc;
-        }
-        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
-        dData = ctx->dIn;
-    } else if ( ( reinterpret_cast<uintptr_t>( data ) & 15U ) != 0 ) {
-        ctx->lastError = "ibz2_decode_blocks: device input must be 16-byte aligned";
-        return IBZ2_E_INVALID_ARGUMENT;
-    }
-    const cudaEvent_t eH2D = nextEvent( ctx );
-
-    uint8_t* dOut = static_cast<uint8_t*>( out );
-    const bool haveOutput = out != nullptr;
-    if ( haveOutput && ( out_mem == IBZ2_MEM_HOST ) ) {
-        const int rc = ensureOutput( ctx, out_capacity );
-        if ( rc != IBZ2_OK ) {
-            return rc;
-        }
-        dOut = ctx->dOut;
-    } else if ( haveOutput && ( ( reinterpret_cast<uintptr_t>( out ) & 15U ) != 0 ) ) {
-        ctx->lastError = "ibz2_decode_blocks: device output must be 16-byte aligned";
-        return IBZ2_E_INVALID_ARGUMENT;
-    }
-
+    const bool haveOutput = dOut != nullptr;
     const uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
     {
         const int rc = ensureScratch( ctx, wave );
@@ -548,11 +497,11 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
             return rc;
         }
     }
-    IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), ctx->stream ) );
-
-    struct WaveEvents { cudaEvent_t e[9]; };
-    std::vector<WaveEvents> waveEvents;
     cudaStream_t s = ctx->stream;
+    IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
+
+    struct WaveEvents { cudaEvent_t e[7]; };
+    std::vector<WaveEvents> waveEvents;
 
     for ( uint64_t first = 0; first < nblocks; first += wave ) {
         const uint32_t count = static_cast<uint32_t>( std::min<uint64_t>( wave, nblocks - first ) );
@@ -565,7 +514,7 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
         }
         std::memset( ctx->hMeta, 0, sizeof( ibz2::BlockMeta ) * count );
         for ( uint32_t i = 0; i < count; ++i ) {
-            ctx->hMeta[i].bitOffset = block_bit_offsets[first + i];
+            ctx->hMeta[i].bitOffset = offsets[first + i];
         }
         IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dMeta, ctx->hMeta, sizeof( ibz2::BlockMeta ) * count,
                                                cudaMemcpyHostToDevice, s ) );
@@ -578,7 +527,7 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
         ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, s );
         we.e[3] = nextEvent( ctx );
         ibz2::launchRleScan( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, s );
-        ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, out_capacity, haveOutput ? 1 : 0,
+        ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
                                   ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
         we.e[4] = nextEvent( ctx );
         ctx->timings.launches += 5;
@@ -598,6 +547,8 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
                                                cudaMemcpyDeviceToHost, s ) );
         waveEvents.push_back( we );
     }
+    uint64_t total = 0;
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( &total, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
     {
         const uint64_t lastFirst = ( ( nblocks - 1 ) / wave ) * wave;
@@ -606,23 +557,7 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
             fillResult( ctx->hMeta[i], &results[lastFirst + i] );
         }
     }
-    uint64_t total = 0;
-    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( &total, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
-    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
-    if ( total_out != nullptr ) {
-        *total_out = total;
-    }
-    const cudaEvent_t eKernels = nextEvent( ctx );
-    if ( haveOutput && ( out_mem == IBZ2_MEM_HOST ) ) {
-        const uint64_t n = std::min<uint64_t>( total, out_capacity );
-        if ( n > 0 ) {
-            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( out, ctx->dOut, n, cudaMemcpyDeviceToHost, s ) );
-        }
-    }
-    const cudaEvent_t eEnd = nextEvent( ctx );
-    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
-
-    ctx->timings.h2d_ms = elapsed( eStart, eH2D );
+    *totalOut = total;
     for ( const auto& we : waveEvents ) {
         ctx->timings.huffman_ms += elapsed( we.e[0], we.e[1] );
         ctx->timings.bwt_prepare_ms += elapsed( we.e[1], we.e[2] );
@@ -633,8 +568,238 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
             ctx->timings.crc_ms += elapsed( we.e[5], we.e[6] );
         }
     }
-    ctx->timings.d2h_ms = elapsed( eKernels, eEnd );
+    return IBZ2_OK;
+}
+
+/* Resolves the output buffer: device pointer as is, host pointer -> the context's device staging buffer. */
+static int
+stageOutput( ibz2_ctx* ctx, void* out, uint64_t out_capacity, int out_mem, uint8_t** dOut, const char* who )
+{
+    *dOut = static_cast<uint8_t*>( out );
+    if ( out == nullptr ) {
+        return IBZ2_OK;
+    }
+    if ( out_mem == IBZ2_MEM_HOST ) {
+        const int rc = ensureOutput( ctx, out_capacity );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+        *dOut = ctx->dOut;
+    } else if ( ( reinterpret_cast<uintptr_t>( out ) & 15U ) != 0 ) {
+        ctx->lastError = std::string( who ) + ": device output must be 16-byte aligned";
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    return IBZ2_OK;
+}
+
+static int
+copyOutputToHost( ibz2_ctx* ctx, void* out, uint64_t out_capacity, int out_mem, uint64_t total )
+{
+    const cudaEvent_t e0 = nextEvent( ctx );
+    if ( ( out != nullptr ) && ( out_mem == IBZ2_MEM_HOST ) ) {
+        const uint64_t n = std::min<uint64_t>( total, out_capacity );
+        if ( n > 0 ) {
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( out, ctx->dOut, n, cudaMemcpyDeviceToHost, ctx->stream ) );
+        }
+    }
+    const cudaEvent_t e1 = nextEvent( ctx );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    ctx->timings.d2h_ms = elapsed( e0, e1 );
+    return IBZ2_OK;
+}
+
+static void
+beginCall( ibz2_ctx* ctx )
+{
+    cudaSetDevice( ctx->device );
+    ctx->timings = ibz2_timings{};
+    ctx->eventsUsed = 0;
+}
+
+int
+ibz2_find_magics( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem, uint64_t base_bit_offset,
+                  uint32_t which, uint64_t* offsets, uint64_t capacity, uint64_t* count )
+{
+    if ( ( ctx == nullptr ) || ( count == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) )
+         || ( ( which & ( IBZ2_FIND_BLOCK | IBZ2_FIND_EOS ) ) == 0 ) || ( ( offsets == nullptr ) && ( capacity > 0 ) ) ) {
+        if ( ctx != nullptr ) {
+            ctx->lastError = "ibz2_find_magics: invalid argument";
+        }
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    *count = 0;
+    beginCall( ctx );
+    if ( nbytes < 6 ) {
+        return IBZ2_OK;
+    }
+    const cudaEvent_t e0 = nextEvent( ctx );
+    const uint8_t* dData = nullptr;
+    int rc = stageInput( ctx, data, nbytes, data_mem, &dData, "ibz2_find_magics" );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const cudaEvent_t e1 = nextEvent( ctx );
+    std::vector<uint64_t> host;
+    rc = findOnDevice( ctx, dData, nbytes, which, host );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const cudaEvent_t e2 = nextEvent( ctx );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    ctx->timings.h2d_ms = elapsed( e0, e1 );
+    ctx->timings.total_ms = elapsed( e0, e2 );
+
+    *count = host.size();
+    const uint64_t n = std::min<uint64_t>( host.size(), capacity );
+    for ( uint64_t i = 0; i < n; ++i ) {
+        offsets[i] = ( ( host[i] & ~IBZ2_OFFSET_EOS_FLAG ) + base_bit_offset ) | ( host[i] & IBZ2_OFFSET_EOS_FLAG );
+    }
+    return host.size() > capacity ? IBZ2_E_CAPACITY : IBZ2_OK;
+}
+
+int
+ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem,
+                    const uint64_t* block_bit_offsets, uint64_t nblocks,
+                    void* out, uint64_t out_capacity, int out_mem,
+                    ibz2_block_result* results, uint64_t* total_out )
+{
+    if ( ( ctx == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) ) || ( ( block_bit_offsets == nullptr ) && ( nblocks > 0 ) )
+         || ( ( results == nullptr ) && ( nblocks > 0 ) ) ) {
+        if ( ctx != nullptr ) {
+            ctx->lastError = "ibz2_decode_blocks: invalid argument";
+        }
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    if ( total_out != nullptr ) {
+        *total_out = 0;
+    }
+    beginCall( ctx );
+    if ( nblocks == 0 ) {
+        return IBZ2_OK;
+    }
+    const cudaEvent_t eStart = nextEvent( ctx );
+    const uint8_t* dData = nullptr;
+    int rc = stageInput( ctx, data, nbytes, data_mem, &dData, "ibz2_decode_blocks" );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const cudaEvent_t eH2D = nextEvent( ctx );
+    uint8_t* dOut = nullptr;
+    rc = stageOutput( ctx, out, out_capacity, out_mem, &dOut, "ibz2_decode_blocks" );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    uint64_t total = 0;
+    rc = decodeOnDevice( ctx, dData, nbytes, block_bit_offsets, nblocks, dOut, out_capacity, results, &total );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    if ( total_out != nullptr ) {
+        *total_out = total;
+    }
+    rc = copyOutputToHost( ctx, out, out_capacity, out_mem, total );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    ctx->timings.h2d_ms = elapsed( eStart, eH2D );
+    ctx->timings.total_ms = elapsed( eStart, ctx->events[ctx->eventsUsed - 1] );
+    return IBZ2_OK;
+}
+
+int
+ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem,
+                    uint64_t first_bit, uint64_t last_bit,
+                    void* out, uint64_t out_capacity, int out_mem,
+                    ibz2_block_result* results, uint64_t results_capacity, uint64_t* nblocks, uint64_t* total_out )
+{
+    if ( ( ctx == nullptr ) || ( nblocks == nullptr ) || ( ( data == nullptr ) && ( nbytes > 0 ) )
+         || ( ( results == nullptr ) && ( results_capacity > 0 ) ) ) {
+        if ( ctx != nullptr ) {
+            ctx->lastError = "ibz2_decode_buffer: invalid argument";
+        }
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    *nblocks = 0;
+    if ( total_out != nullptr ) {
+        *total_out = 0;
+    }
+    beginCall( ctx );
+    const cudaEvent_t eStart = nextEvent( ctx );
+    const uint8_t* dData = nullptr;
+    int rc = stageInput( ctx, data, nbytes, data_mem, &dData, "ibz2_decode_buffer" );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const cudaEvent_t eH2D = nextEvent( ctx );
+    std::vector<uint64_t> found;
+    rc = findOnDevice( ctx, dData, nbytes, IBZ2_FIND_BLOCK, found );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    std::vector<uint64_t> mine;
+    mine.reserve( found.size() );
+    for ( const uint64_t f : found ) {
+        if ( ( f >= first_bit ) && ( f < last_bit ) ) {
+            mine.push_back( f );
+        }
+    }
+    *nblocks = mine.size();
+    if ( mine.size() > results_capacity ) {
+        ctx->lastError = "ibz2_decode_buffer: results array too small";
+        return IBZ2_E_CAPACITY;
+    }
+    uint64_t total = 0;
+    if ( !mine.empty() ) {
+        uint8_t* dOut = nullptr;
+        rc = stageOutput( ctx, out, out_capacity, out_mem, &dOut, "ibz2_decode_buffer" );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+        rc = decodeOnDevice( ctx, dData, nbytes, mine.data(), mine.size(), dOut, out_capacity, results, &total );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+        rc = copyOutputToHost( ctx, out, out_capacity, out_mem, total );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+    }
+    if ( total_out != nullptr ) {
+        *total_out = total;
+    }
+    const cudaEvent_t eEnd = nextEvent( ctx );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    ctx->timings.h2d_ms = elapsed( eStart, eH2D );
     ctx->timings.total_ms = elapsed( eStart, eEnd );
+    return IBZ2_OK;
+}
+
+int
+ibz2_timer_start( ibz2_ctx* ctx )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    if ( ctx->timerStart == nullptr ) {
+        IBZ2_CUDA_CHECK( ctx, cudaEventCreate( &ctx->timerStart ) );
+        IBZ2_CUDA_CHECK( ctx, cudaEventCreate( &ctx->timerStop ) );
+    }
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+    IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->timerStart, ctx->stream ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_timer_stop( ibz2_ctx* ctx, float* milliseconds )
+{
+    if ( ( ctx == nullptr ) || ( milliseconds == nullptr ) || ( ctx->timerStart == nullptr ) ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->timerStop, ctx->stream ) );
+    IBZ2_CUDA_CHECK( ctx, cudaEventSynchronize( ctx->timerStop ) );
+    IBZ2_CUDA_CHECK( ctx, cudaEventElapsedTime( milliseconds, ctx->timerStart, ctx->timerStop ) );
     return IBZ2_OK;
 }
 
