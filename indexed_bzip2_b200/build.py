@@ -19,7 +19,7 @@ CSRC = PKG / "csrc"
 BUILD = PKG / "build"
 LIB = PKG / "libibz2_cuda.so"
 
-CUDA_SOURCES = ["blockfinder.cu", "huffman_decode.cu", "bwt_prepare.cu", "bwt_traverse.cu", "rle.cu", "crc.cu", "capi.cu"]
+CUDA_SOURCES = ["blockfinder.cu", "huffman_header.cu", "huffman_bits.cu", "huffman_careful.cu", "mtf.cu", "bwt_prepare.cu", "bwt_traverse.cu", "rle.cu", "crc.cu", "capi.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

@@ -31,6 +31,8 @@ struct ibz2_ctx
     uint8_t* dLbytes = nullptr;
     uint32_t* dDbuf = nullptr;
     uint8_t* dSelectors = nullptr;
+    ibz2::BlockTables* dTables = nullptr;
+    uint32_t* dCounter = nullptr;
     uint32_t* dWarpBase = nullptr;
     uint32_t* dPieceStart = nullptr;
     uint64_t* dRunning = nullptr;
@@ -95,6 +97,8 @@ freeScratch( ibz2_ctx* ctx )
     cudaFree( ctx->dLbytes );
     cudaFree( ctx->dDbuf );
     cudaFree( ctx->dSelectors );
+    cudaFree( ctx->dTables );
+    cudaFree( ctx->dCounter );
     cudaFree( ctx->dWarpBase );
     cudaFree( ctx->dPieceStart );
     cudaFreeHost( ctx->hMeta );
@@ -102,6 +106,8 @@ freeScratch( ibz2_ctx* ctx )
     ctx->dLbytes = nullptr;
     ctx->dDbuf = nullptr;
     ctx->dSelectors = nullptr;
+    ctx->dTables = nullptr;
+    ctx->dCounter = nullptr;
     ctx->dWarpBase = nullptr;
     ctx->dPieceStart = nullptr;
     ctx->hMeta = nullptr;
@@ -120,6 +126,8 @@ ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dLbytes, b * ibz2::LBYTES_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dDbuf, b * ibz2::DBUF_STRIDE * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dSelectors, b * ibz2::SEL_STRIDE ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dTables, b * sizeof( ibz2::BlockTables ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dCounter, ( b + 16 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dWarpBase, b * ibz2::RLE_RANGES * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dPieceStart, ( b + 1 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMallocHost( &ctx->hMeta, b * sizeof( ibz2::BlockMeta ) ) );
@@ -520,7 +528,8 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
                                                cudaMemcpyHostToDevice, s ) );
         WaveEvents we{};
         we.e[0] = nextEvent( ctx );
-        ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, s );
+        ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, ctx->dTables,
+                                   ctx->dDbuf, ctx->dCounter, s );
         we.e[1] = nextEvent( ctx );
         ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, count, s );
         we.e[2] = nextEvent( ctx );
@@ -530,7 +539,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
                                   ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
         we.e[4] = nextEvent( ctx );
-        ctx->timings.launches += 5;
+        ctx->timings.launches += 4 + ibz2::HUFFMAN_LAUNCHES;
         if ( haveOutput ) {
             ibz2::launchRleWrite( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, dOut, s );
             we.e[5] = nextEvent( ctx );
@@ -829,7 +838,8 @@ ibz2_debug_decode_block( ibz2_ctx* ctx, const void* data, uint64_t nbytes, uint6
     ctx->hMeta[0].bitOffset = bit_offset;
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dMeta, ctx->hMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyHostToDevice, s ) );
 
-    ibz2::launchHuffmanDecode( ctx->dIn, nbytes, ctx->dMeta, 1, ctx->dLbytes, ctx->dSelectors, s );
+    ibz2::launchHuffmanDecode( ctx->dIn, nbytes, ctx->dMeta, 1, ctx->dLbytes, ctx->dSelectors, ctx->dTables, ctx->dDbuf,
+                               ctx->dCounter, s );
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyDeviceToHost, s ) );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
     IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );

@@ -32,6 +32,9 @@ constexpr uint32_t DBUF_STRIDE = 900096;                /* u32 entries */
 constexpr uint32_t SEL_STRIDE = MAX_SELECTORS + 64;
 constexpr uint32_t RLE_RANGES = 32;                     /* element ranges per block in K5a/K5b (one per warp) */
 
+/* Internal block status between the K2 kernels: "decode this block again with the exact state machine". */
+constexpr uint32_t ST_INTERNAL_CAREFUL = 255;
+
 /* One per block, device-resident; the host mirrors it to fill ibz2_block_result. */
 struct BlockMeta
 {
@@ -49,8 +52,50 @@ struct BlockMeta
     uint32_t isEof;
     uint32_t cycleLen;    /* K4b: length of the permutation cycle through origPtr (diagnostic) */
     uint32_t writeOutput; /* scan: 1 when the block's bytes fit the output buffer */
+    uint32_t nCoded;      /* K2b: Huffman symbols stored for K2c..K2e (run symbols and MTF symbols, without EOB) */
+};
+
+/* ---- K2 intermediates (see huffman_header.cu / huffman_bits.cu / mtf.cu) ----
+ * K2a writes one BlockTables per block; K2b reads it (the LUTs go to shared memory, the rest stays in L1/L2). */
+constexpr int HUFF_LUT_BITS = 9;                       /* direct-lookup width of K2b */
+constexpr int HUFF_LUT_SIZE = 1 << HUFF_LUT_BITS;
+constexpr uint32_t HUFF_LUT_WORDS = MAX_GROUPS * HUFF_LUT_SIZE / 2;   /* u32 words per block: 1536 */
+
+struct alignas( 16 ) BlockTables
+{
+    uint16_t lut[MAX_GROUPS][HUFF_LUT_SIZE];    /* { symbol:11, length:5 }, 0 = code longer than HUFF_LUT_BITS or none */
+    uint16_t perm[MAX_GROUPS][260];             /* symbols sorted by (length, symbol) */
+    uint32_t first[MAX_GROUPS][MAX_CODE_LEN + 2];
+    uint16_t count[MAX_GROUPS][MAX_CODE_LEN + 2];
+    uint16_t offset[MAX_GROUPS][MAX_CODE_LEN + 2];
+    uint32_t maxLen[MAX_GROUPS + 2];
+    uint8_t s2b[256];                           /* symbolToByte (bzip2.hpp:526-571) */
+    uint64_t dataStartBit;                      /* first bit of the Huffman-coded symbols */
+    uint32_t symbolCount;
+    uint32_t selectorsCount;
+    uint32_t groupCount;
     uint32_t pad;
 };
+
+/* The symbol stream of a block is cut into chunks of MTF_CHUNK coded symbols; K2b leaves one checkpoint per chunk. */
+constexpr uint32_t MTF_CHUNK = 1024;
+constexpr uint32_t MTF_CHUNK_SHIFT = 10;
+constexpr uint32_t MAX_CHUNKS = ( DBUF_SIZE + MTF_CHUNK - 1 ) / MTF_CHUNK;   /* 879 */
+struct ChunkCheckpoint
+{
+    uint32_t outOffset;   /* index in L of the first byte the chunk's first symbol produces */
+    uint32_t runShift;    /* number of run symbols directly in front of the chunk (position inside a RUNA/RUNB number) */
+};
+
+/* K2 scratch aliases the block's dbuf slot (3.6 MB), which K4a only overwrites after K2e has consumed it:
+ *   u16 symbols[900096] | u8 symbolic[900096] | u8 lists[MAX_CHUNKS + 1][256] | ChunkCheckpoint[MAX_CHUNKS + 1] */
+constexpr uint64_t K2_SYM16_OFFSET = 0;
+constexpr uint64_t K2_SYM8_OFFSET = static_cast<uint64_t>( LBYTES_STRIDE ) * 2U;
+constexpr uint64_t K2_LISTS_OFFSET = K2_SYM8_OFFSET + LBYTES_STRIDE;
+constexpr uint64_t K2_CKPT_OFFSET = K2_LISTS_OFFSET + static_cast<uint64_t>( MAX_CHUNKS + 1U ) * 256U;
+static_assert( sizeof( BlockTables ) % 16U == 0, "K2b copies the LUTs with 16-byte loads" );
+static_assert( K2_CKPT_OFFSET + ( MAX_CHUNKS + 1U ) * sizeof( ChunkCheckpoint ) <= static_cast<uint64_t>( DBUF_STRIDE ) * 4U,
+               "K2 scratch must fit the dbuf slot" );
 
 __device__ __forceinline__ uint32_t
 laneId()
@@ -98,8 +143,21 @@ crcMulMod( uint32_t a, uint32_t b )
 void launchFindMagics( const uint8_t* data, uint64_t nbytes, uint32_t which, uint64_t* found, uint32_t* foundCount,
                        uint32_t capacity, cudaStream_t stream );
 
+/* K2a..K2e; tables: BlockTables[nblocks]; scratch: the dbuf slots; counter: device u32[2 + nblocks] work counters / hand-over list. */
 void launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
-                          uint8_t* lbytes, uint8_t* selectors, cudaStream_t stream );
+                          uint8_t* lbytes, uint8_t* selectors, BlockTables* tables, uint32_t* scratch,
+                          uint32_t* counter, cudaStream_t stream );
+constexpr uint32_t HUFFMAN_LAUNCHES = 6;
+
+void launchHuffmanHeader( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
+                          uint8_t* selectors, BlockTables* tables, cudaStream_t stream );
+void launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
+                        const uint8_t* selectors, const BlockTables* tables, uint32_t* scratch, uint32_t* counter,
+                        cudaStream_t stream );
+void launchHuffmanCareful( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* lbytes,
+                           uint8_t* selectors, cudaStream_t stream );
+void launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_t* scratch, uint8_t* lbytes,
+                cudaStream_t stream );
 
 void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, uint32_t nblocks,
                        cudaStream_t stream );

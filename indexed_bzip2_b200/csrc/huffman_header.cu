@@ -1,19 +1,14 @@
 /*
- * K2 -- block header, Huffman tables and the Huffman / RUNA-RUNB / move-to-front symbol loop, one warp per bzip2 block.
- * Replaces Block::readBlockHeader / readSymbolMaps / readSelectors / readTrees / readBlockData
- * (indexed_bzip2/bzip2.hpp:479-807) and the canonical Huffman coding construction + decode
- * (huffman/HuffmanCodingBase.hpp:46-187, HuffmanCodingSymbolsPerLength.hpp:43-124,
- * HuffmanCodingShortBitsCached.hpp:39-150).
+ * K2a -- block header, symbol map, selectors and Huffman tables, one warp per bzip2 block.
+ * Replaces Block::readBlockHeader / readSymbolMaps / readSelectors / readTrees (indexed_bzip2/bzip2.hpp:479-685) and the
+ * canonical Huffman coding construction (huffman/HuffmanCodingBase.hpp:46-187, HuffmanCodingSymbolsPerLength.hpp:43-124,
+ * HuffmanCodingShortBitsCached.hpp:39-91).
  *
- * Execution model: the bit stream of a block is inherently serial, so all 32 lanes of the warp run the SAME decode
- * redundantly (warp-uniform control flow, no divergence) and the lanes are used as a distributed register file:
- *   - the input window: each lane holds one 32-bit word of the current and of the next 128-byte line of the
- *     compressed stream (coalesced loads, prefetched one line ahead); the next word is fetched with one shuffle;
- *   - the move-to-front list: entry i lives in lane i % 32, register i / 32; a move-to-front is two shuffles and a
- *     select per touched register instead of a memmove (bzip2.hpp:781-785);
- *   - run expansion and the output staging buffer are filled by all lanes, and L is written to HBM in 128-byte lines.
- * Per-table decode LUTs (2^LUT_BITS entries of {symbol:11, length:5}) sit in shared memory; longer codes fall back to
- * the canonical first-code / count comparison, which is exactly what the reference's decodeLong does.
+ * The header fields are bit-serial, so all 32 lanes of the warp run the SAME parse (warp-uniform control flow) and
+ * the lanes serve as a distributed register file for the input window (each lane holds one 32-bit word of the current
+ * and of the next 128-byte line, fetched with one shuffle).  The per-length symbol counting, the (length, symbol) sort
+ * and the LUT fill are lane-parallel.  The result goes to the block's BlockTables in HBM: K2b (huffman_bits.cu) copies
+ * the 9-bit LUTs into shared memory and decodes the symbol stream with one LANE per block.
  */
 #include "common.cuh"
 
@@ -21,7 +16,7 @@ namespace ibz2
 {
 namespace
 {
-constexpr int LUT_BITS = 10;
+constexpr int LUT_BITS = HUFF_LUT_BITS;
 constexpr int LUT_SIZE = 1 << LUT_BITS;
 constexpr int WARPS_PER_CTA = 4;
 constexpr uint32_t FULL = 0xFFFFFFFFU;
@@ -36,7 +31,6 @@ struct WarpShared
     uint32_t maxLen[MAX_GROUPS + 2];
     uint8_t lens[264];
     uint8_t s2b[256];
-    uint8_t stage[256];
 };
 
 /* MSB-first bit cursor shared by the warp (semantics of BitReader<true, uint64_t>, core/BitReader.hpp:190-290). */
@@ -124,36 +118,6 @@ struct WarpBits
     }
 };
 
-/* Move entry ii of the lane-distributed list to the front and return it (bzip2.hpp:781-785). */
-__device__ __forceinline__ uint32_t
-moveToFront( uint32_t ( &m )[8], uint32_t ii, uint32_t lane )
-{
-    const uint32_t R = ii >> 5;
-    const uint32_t c = ii & 31U;
-    if ( R == 0 ) {
-        const uint32_t v = __shfl_sync( FULL, m[0], c );
-        const uint32_t up = __shfl_up_sync( FULL, m[0], 1 );
-        m[0] = ( lane == 0 ) ? v : ( ( lane <= c ) ? up : m[0] );
-        return v;
-    }
-    uint32_t sel = m[1];
-#pragma unroll
-    for ( int r = 2; r < 8; ++r ) {
-        sel = ( R == static_cast<uint32_t>( r ) ) ? m[r] : sel;
-    }
-    const uint32_t v = __shfl_sync( FULL, sel, c );
-#pragma unroll
-    for ( int r = 7; r >= 0; --r ) {
-        if ( static_cast<uint32_t>( r ) <= R ) {
-            const uint32_t up = __shfl_up_sync( FULL, m[r], 1 );
-            const uint32_t carry = ( r == 0 ) ? v : __shfl_sync( FULL, m[r > 0 ? r - 1 : 0], 31 );
-            const bool affected = ( static_cast<uint32_t>( r ) < R ) || ( lane <= c );
-            m[r] = ( lane == 0 ) ? carry : ( affected ? up : m[r] );
-        }
-    }
-    return v;
-}
-
 /* Canonical code of one table from its lengths in ws.lens[0..nsym) (bzip2.hpp:680-683 -> HuffmanCodingBase.hpp:165-187).
  * Returns false for an over-subscribed length set (Error::INVALID_CODE_LENGTHS); incomplete sets are accepted. */
 __device__ __forceinline__ bool
@@ -236,8 +200,8 @@ buildTable( WarpShared& ws, uint32_t g, uint32_t nsym, uint32_t lane )
 }
 
 __global__ void __launch_bounds__( WARPS_PER_CTA * 32 )
-huffmanDecodeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta,
-                     uint32_t nblocks, uint8_t* __restrict__ lbytesAll, uint8_t* selectorsAll )
+huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta,
+                     uint32_t nblocks, uint8_t* selectorsAll, BlockTables* __restrict__ tablesAll )
 {
     extern __shared__ __align__( 16 ) uint8_t sharedRaw[];
     const uint32_t warp = threadIdx.x >> 5;
@@ -248,7 +212,7 @@ huffmanDecodeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
     }
     WarpShared& ws = reinterpret_cast<WarpShared*>( sharedRaw )[warp];
     BlockMeta& bm = meta[block];
-    uint8_t* const lbytes = lbytesAll + static_cast<uint64_t>( block ) * LBYTES_STRIDE;
+    BlockTables& bt = tablesAll[block];
     uint8_t* const selectors = selectorsAll + static_cast<uint64_t>( block ) * SEL_STRIDE;
     const uint64_t nbits = nbytes * 8U;
     const uint64_t startBit = bm.bitOffset;
@@ -256,7 +220,6 @@ huffmanDecodeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
     uint32_t status = IBZ2_ST_OK;
     uint32_t headerCrc = 0;
     uint32_t origPtr = 0;
-    uint32_t cnt = 0;       /* dbufCount */
     uint32_t isEos = 0;
     uint32_t isEof = 0;
     uint64_t endBit = startBit;
@@ -432,140 +395,36 @@ huffmanDecodeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
             break;
         }
 
-        /* readBlockData (bzip2.hpp:691-807) */
-        uint32_t m[8];
+        /* hand the tables to K2b */
         __syncwarp();
-#pragma unroll
-        for ( int r = 0; r < 8; ++r ) {
-            const uint32_t idx = 32U * r + lane;
-            m[r] = idx < symbolCount ? ws.s2b[idx] : 0U;
-        }
-        uint32_t* const stageWords = reinterpret_cast<uint32_t*>( ws.stage );
-        uint32_t* const outWords = reinterpret_cast<uint32_t*>( lbytes );
-
-        uint32_t hh = 0;
-        uint32_t runPos = 0;
-        uint32_t groupLeft = 0;
-        uint32_t selIdx = 0;
-        uint32_t selChunk = 0;
-        uint32_t table = 0;
-        uint32_t tableMaxLen = 0;
-
-        while ( true ) {
-            if ( groupLeft == 0 ) {
-                if ( selIdx >= selectorsCount ) {
-                    status = IBZ2_ST_SELECTOR_OVERRUN;
-                    break;
-                }
-                if ( ( selIdx & 31U ) == 0 ) {
-                    selChunk = selectors[selIdx + lane];
-                    if ( br.tell() > nbits ) {
-                        status = IBZ2_ST_EOF;
-                        break;
-                    }
-                }
-                table = __shfl_sync( FULL, selChunk, selIdx & 31U );
-                tableMaxLen = ws.maxLen[table];
-                ++selIdx;
-                groupLeft = GROUP_SIZE;
+        {
+            const uint32_t* src = reinterpret_cast<const uint32_t*>( &ws.lut[0][0] );
+            uint32_t* dst = reinterpret_cast<uint32_t*>( &bt.lut[0][0] );
+            for ( uint32_t i = lane; i < groupCount * ( LUT_SIZE / 2U ); i += 32U ) {
+                dst[i] = src[i];
             }
-            --groupLeft;
-
-            br.ensure();
-            uint32_t e = ws.lut[table][br.peek( LUT_BITS )];
-            uint32_t len = e & 31U;
-            uint32_t sym = e >> 5;
-            if ( e == 0 ) {
-                /* code longer than LUT_BITS or no code at all (HuffmanCodingShortBitsCached.hpp:117-150) */
-                bool found = false;
-                for ( len = LUT_BITS + 1; len <= tableMaxLen; ++len ) {
-                    const uint32_t cd = br.peek( static_cast<int>( len ) );
-                    const uint32_t f = ws.first[table][len];
-                    if ( ( cd >= f ) && ( cd - f < ws.count[table][len] ) ) {
-                        sym = ws.perm[table][ws.offset[table][len] + ( cd - f )];
-                        found = true;
-                        break;
-                    }
+            for ( uint32_t g = 0; g < groupCount; ++g ) {
+                for ( uint32_t i = lane; i < nsym; i += 32U ) {
+                    bt.perm[g][i] = ws.perm[g][i];
                 }
-                if ( !found ) {
-                    status = ( br.tell() + tableMaxLen + 1U > nbits ) ? IBZ2_ST_EOF : IBZ2_ST_INVALID_CODE;
-                    break;
+                if ( lane < MAX_CODE_LEN + 2U ) {
+                    bt.first[g][lane] = ws.first[g][lane];
+                    bt.count[g][lane] = ws.count[g][lane];
+                    bt.offset[g][lane] = ws.offset[g][lane];
                 }
             }
-            br.skip( static_cast<int>( len ) );
-
-            if ( sym <= 1U ) {
-                /* RUNA / RUNB (bzip2.hpp:726-743) */
-                if ( runPos == 0 ) {
-                    runPos = 1;
-                    hh = 0;
-                }
-                hh += runPos << sym;
-                runPos <<= 1;
-                continue;
+            if ( lane < groupCount ) {
+                bt.maxLen[lane] = ws.maxLen[lane];
             }
-            if ( runPos != 0 ) {
-                /* flush the pending run of the byte at the front of the list (bzip2.hpp:749-763) */
-                runPos = 0;
-                if ( static_cast<uint64_t>( cnt ) + hh > DBUF_SIZE ) {
-                    status = IBZ2_ST_DBUF_OVERFLOW;
-                    break;
-                }
-                const uint32_t uc = __shfl_sync( FULL, m[0], 0 );
-                while ( hh > 0 ) {
-                    if ( ( ( cnt & 127U ) == 0 ) && ( hh >= 128U ) ) {
-                        outWords[( cnt >> 2 ) + lane] = uc * 0x01010101U;
-                        cnt += 128U;
-                        hh -= 128U;
-                        continue;
-                    }
-                    const uint32_t space = 128U - ( cnt & 127U );
-                    const uint32_t n = hh < space ? hh : space;
-                    for ( uint32_t i = lane; i < n; i += 32U ) {
-                        ws.stage[( cnt & 255U ) + i] = static_cast<uint8_t>( uc );
-                    }
-                    cnt += n;
-                    hh -= n;
-                    if ( ( cnt & 127U ) == 0 ) {
-                        __syncwarp();
-                        outWords[( ( cnt - 128U ) >> 2 ) + lane] = stageWords[( ( ( cnt - 128U ) & 255U ) >> 2 ) + lane];
-                        __syncwarp();
-                    }
-                }
+            for ( uint32_t i = lane; i < 256U; i += 32U ) {
+                bt.s2b[i] = i < symbolCount ? ws.s2b[i] : static_cast<uint8_t>( i );
             }
-            if ( sym > symbolCount ) {
-                break;  /* end of block (bzip2.hpp:766-768) */
-            }
-            if ( cnt >= DBUF_SIZE ) {
-                status = IBZ2_ST_DBUF_OVERFLOW;
-                break;
-            }
-            const uint32_t uc = moveToFront( m, sym - 1U, lane );
             if ( lane == 0 ) {
-                ws.stage[cnt & 255U] = static_cast<uint8_t>( uc );
+                bt.dataStartBit = br.tell();
+                bt.symbolCount = symbolCount;
+                bt.selectorsCount = selectorsCount;
+                bt.groupCount = groupCount;
             }
-            ++cnt;
-            if ( ( cnt & 127U ) == 0 ) {
-                __syncwarp();
-                outWords[( ( cnt - 128U ) >> 2 ) + lane] = stageWords[( ( ( cnt - 128U ) & 255U ) >> 2 ) + lane];
-                __syncwarp();
-            }
-        }
-        if ( status != IBZ2_ST_OK ) {
-            break;
-        }
-        if ( ( cnt & 127U ) != 0 ) {
-            __syncwarp();
-            outWords[( ( cnt & ~127U ) >> 2 ) + lane] = stageWords[( ( ( cnt & ~127U ) & 255U ) >> 2 ) + lane];
-        }
-        endBit = br.tell();
-        if ( endBit > nbits ) {
-            status = IBZ2_ST_EOF;
-            break;
-        }
-        if ( origPtr >= cnt ) {
-            status = IBZ2_ST_ORIGPTR;  /* bzip2.hpp:794-798 */
-            break;
         }
     } while ( false );
 
@@ -576,7 +435,8 @@ huffmanDecodeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         bm.status = status;
         bm.headerCrc = headerCrc;
         bm.origPtr = origPtr;
-        bm.n = ( status == IBZ2_ST_OK ) ? cnt : 0U;
+        bm.n = 0;
+        bm.nCoded = 0;
         bm.endBit = endBit;
         bm.isEos = isEos;
         bm.isEof = isEof;
@@ -591,14 +451,13 @@ huffmanDecodeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
 }  // namespace
 
 void
-launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
-                     uint8_t* lbytes, uint8_t* selectors, cudaStream_t stream )
+launchHuffmanHeader( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* selectors,
+                     BlockTables* tables, cudaStream_t stream )
 {
     const size_t shared = sizeof( WarpShared ) * WARPS_PER_CTA;
-    cudaFuncSetAttribute( huffmanDecodeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaFuncSetAttribute( huffmanHeaderKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                           static_cast<int>( shared ) );
     const uint32_t ctas = ( nblocks + WARPS_PER_CTA - 1 ) / WARPS_PER_CTA;
-    huffmanDecodeKernel<<<ctas, WARPS_PER_CTA * 32, shared, stream>>>( data, nbytes, meta, nblocks, lbytes,
-                                                                       selectors );
+    huffmanHeaderKernel<<<ctas, WARPS_PER_CTA * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables );
 }
 }  // namespace ibz2

@@ -1,0 +1,441 @@
+/*
+ * K2c..K2e -- move-to-front and RUNA/RUNB expansion of Block::readBlockData (indexed_bzip2/bzip2.hpp:726-790), i.e. the
+ * half of the symbol loop that K2b (huffman_bits.cu) leaves out, with chunk-level parallelism inside every block.
+ *
+ * Move-to-front looks serial (the list depends on every earlier symbol), but a chunk of symbols can be decoded against
+ * an UNKNOWN start list symbolically: start from the identity list, so that every output is "the entry that was at
+ * position p of the chunk's start list", and the list left behind is a permutation of start positions.  Permutations
+ * compose, so a cheap serial pass over the chunk permutations recovers every chunk's real start list.
+ *   K2c  mtfChunkKernel   one LANE per chunk of MTF_CHUNK symbols: symbolic move-to-front on a private list held in
+ *                         the lane's own shared-memory bank (word w of lane t at [w][t]; the first four entries stay
+ *                         in a register); writes one symbolic byte per symbol and the chunk's final permutation.
+ *   K2d  mtfListsKernel   one WARP per block: start list of chunk j+1 = start list of chunk j o permutation j, seeded
+ *                         with symbolToByte; overwrites every permutation with the chunk's start list in place.
+ *   K2e  mtfExpandKernel  one WARP per chunk: symbolic byte -> real byte through the start list, RUNA/RUNB symbol at
+ *                         position k of its number -> ( symbol + 1 ) << k copies (the 32-bit sum of bzip2.hpp:742 is the
+ *                         sum of these shares), exclusive scan from the chunk checkpoint, bytes staged in shared memory
+ *                         and written to L in 128-byte rows.
+ * Algorithmic HBM traffic per block: 2 B/symbol read twice, 1 B/symbol written and read, 256 B per chunk twice,
+ * N bytes of L written.
+ */
+#include "common.cuh"
+
+namespace ibz2
+{
+namespace
+{
+constexpr uint32_t FULL = 0xFFFFFFFFU;
+constexpr int MTFC_THREADS = 128;
+constexpr uint32_t MAX_RUN_DIGITS = 20;   /* 2^20 - 1 > 900000: a longer RUNA/RUNB number overflows the block or wraps */
+constexpr uint32_t LONG_RUN_FLAG = 0x80000000U;
+
+__device__ __forceinline__ const uint8_t*
+k2Scratch( const uint32_t* scratchAll, uint32_t block )
+{
+    return reinterpret_cast<const uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE );
+}
+
+__device__ __forceinline__ uint8_t*
+k2Scratch( uint32_t* scratchAll, uint32_t block )
+{
+    return reinterpret_cast<uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE );
+}
+
+/* ---------------------------------------------------------------- K2c ---------------------------------------- */
+__global__ void __launch_bounds__( MTFC_THREADS )
+mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scratchAll )
+{
+    __shared__ uint32_t lists[64][MTFC_THREADS];   /* [word][thread]: thread t only ever touches bank t % 32 */
+
+    const uint32_t block = blockIdx.y;
+    const BlockMeta& bm = meta[block];
+    if ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) {
+        return;
+    }
+    const uint32_t nCoded = bm.nCoded;
+    const uint32_t chunk = blockIdx.x * MTFC_THREADS + threadIdx.x;
+    const uint32_t begin = chunk << MTF_CHUNK_SHIFT;
+    if ( begin >= nCoded ) {
+        return;
+    }
+    const uint32_t count = min( MTF_CHUNK, nCoded - begin );
+    uint8_t* const scratch = k2Scratch( scratchAll, block );
+    const uint16_t* const sym16 = reinterpret_cast<const uint16_t*>( scratch + K2_SYM16_OFFSET ) + begin;
+    uint32_t* const sym8 = reinterpret_cast<uint32_t*>( scratch + K2_SYM8_OFFSET + begin );
+    uint32_t* const listOut = reinterpret_cast<uint32_t*>( scratch + K2_LISTS_OFFSET + static_cast<uint64_t>( chunk ) * 256U );
+    ChunkCheckpoint* const ckpt = reinterpret_cast<ChunkCheckpoint*>( scratch + K2_CKPT_OFFSET ) + chunk;
+
+    /* digits of a RUNA/RUNB number directly in front of the chunk (bzip2.hpp:726-743: runPos = 1 << digits) */
+    uint32_t runDigits = 0;
+    while ( ( runDigits <= MAX_RUN_DIGITS ) && ( runDigits < begin ) && ( sym16[-1 - static_cast<int>( runDigits )] <= 1U ) ) {
+        ++runDigits;
+    }
+    const uint32_t runShift = runDigits;
+    bool longRun = runDigits > MAX_RUN_DIGITS;
+    uint32_t produced = 0;   /* bytes of L the chunk's symbols stand for */
+
+    uint32_t* const my = &lists[0][threadIdx.x];
+    constexpr uint32_t STRIDE = MTFC_THREADS;
+#pragma unroll
+    for ( uint32_t w = 1; w < 64U; ++w ) {
+        my[w * STRIDE] = 0x03020100U + 0x04040404U * w;
+    }
+    uint32_t r0 = 0x03020100U;   /* list entries 0..3 */
+
+    for ( uint32_t base = 0; base < count; base += 8U ) {
+        /* 8 symbols per 16-byte load; `begin` is a multiple of 1024 symbols, so the loads are aligned */
+        const uint4 v = *reinterpret_cast<const uint4*>( sym16 + base );
+        const uint32_t packed[4] = { v.x, v.y, v.z, v.w };
+        uint32_t out[2] = { 0, 0 };
+#pragma unroll
+        for ( uint32_t k = 0; k < 8U; ++k ) {
+            const uint32_t sym = ( packed[k >> 1] >> ( 16U * ( k & 1U ) ) ) & 0xFFFFU;
+            uint32_t o = r0 & 0xFFU;
+            if ( base + k < count ) {
+                const bool isRun = sym <= 1U;
+                produced += isRun ? ( ( sym + 1U ) << min( runDigits, MAX_RUN_DIGITS ) ) : 1U;
+                runDigits = isRun ? runDigits + 1U : 0U;
+                longRun = longRun || ( runDigits > MAX_RUN_DIGITS );
+            }
+            if ( ( sym >= 2U ) && ( base + k < count ) ) {
+                const uint32_t idx = sym - 1U;   /* 1..255 */
+                if ( idx < 4U ) {
+                    const uint32_t sh = 8U * idx;
+                    o = ( r0 >> sh ) & 0xFFU;
+                    const uint32_t keep = ( idx == 3U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );
+                    r0 = ( r0 & keep ) | ( ( ( r0 << 8 ) | o ) & ~keep );
+                } else {
+                    const uint32_t W = idx >> 2;
+                    const uint32_t sh = 8U * ( idx & 3U );
+                    const uint32_t last = my[W * STRIDE];
+                    o = ( last >> sh ) & 0xFFU;
+                    uint32_t carry = r0 >> 24;
+                    r0 = ( r0 << 8 ) | o;
+#pragma unroll 4
+                    for ( uint32_t w = 1; w < W; ++w ) {
+                        const uint32_t x = my[w * STRIDE];
+                        my[w * STRIDE] = ( x << 8 ) | carry;
+                        carry = x >> 24;
+                    }
+                    const uint32_t keep = ( sh == 24U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );
+                    my[W * STRIDE] = ( last & keep ) | ( ( ( last << 8 ) | carry ) & ~keep );
+                }
+            }
+            out[k >> 2] |= o << ( 8U * ( k & 3U ) );
+        }
+        sym8[( base >> 2 ) + 0U] = out[0];
+        sym8[( base >> 2 ) + 1U] = out[1];
+    }
+
+    *ckpt = ChunkCheckpoint{ produced, runShift | ( longRun ? LONG_RUN_FLAG : 0U ) };
+    listOut[0] = r0;
+#pragma unroll 8
+    for ( uint32_t w = 1; w < 64U; ++w ) {
+        listOut[w] = my[w * STRIDE];
+    }
+}
+
+/* ---------------------------------------------------------------- K2d ---------------------------------------- */
+constexpr int MTFL_WARPS = 4;
+
+__global__ void __launch_bounds__( MTFL_WARPS * 32 )
+mtfListsKernel( BlockMeta* __restrict__ meta, uint32_t nblocks, const BlockTables* __restrict__ tablesAll,
+                uint32_t* __restrict__ scratchAll )
+{
+    __shared__ __align__( 16 ) uint8_t startList[MTFL_WARPS][256];
+
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31U;
+    const uint32_t block = blockIdx.x * MTFL_WARPS + warp;
+    if ( block >= nblocks ) {
+        return;
+    }
+    BlockMeta& bm = meta[block];
+    if ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) {
+        return;
+    }
+    const uint32_t chunks = ( bm.nCoded + MTF_CHUNK - 1U ) >> MTF_CHUNK_SHIFT;
+    ChunkCheckpoint* const ckpt = reinterpret_cast<ChunkCheckpoint*>( k2Scratch( scratchAll, block ) + K2_CKPT_OFFSET );
+    uint64_t produced = 0;
+    uint32_t flags = 0;
+    uint2* const lists = reinterpret_cast<uint2*>( k2Scratch( scratchAll, block ) + K2_LISTS_OFFSET );
+    uint8_t* const cur = startList[warp];
+    uint2* const curWords = reinterpret_cast<uint2*>( cur );
+
+    /* list position p holds byte symbolToByte[p] at block start (bzip2.hpp:699 + :786) */
+    curWords[lane] = reinterpret_cast<const uint2*>( tablesAll[block].s2b )[lane];
+    __syncwarp();
+
+    uint2 perm = chunks > 0 ? lists[lane] : make_uint2( 0, 0 );
+    for ( uint32_t j = 0; j < chunks; ++j ) {
+        const uint2 nextPerm = ( j + 1U < chunks ) ? lists[static_cast<uint64_t>( j + 1U ) * 32U + lane] : make_uint2( 0, 0 );
+        const uint2 mine = curWords[lane];
+        uint2 composed;
+        composed.x = static_cast<uint32_t>( cur[perm.x & 0xFFU] ) | ( static_cast<uint32_t>( cur[( perm.x >> 8 ) & 0xFFU] ) << 8 )
+                     | ( static_cast<uint32_t>( cur[( perm.x >> 16 ) & 0xFFU] ) << 16 )
+                     | ( static_cast<uint32_t>( cur[perm.x >> 24] ) << 24 );
+        composed.y = static_cast<uint32_t>( cur[perm.y & 0xFFU] ) | ( static_cast<uint32_t>( cur[( perm.y >> 8 ) & 0xFFU] ) << 8 )
+                     | ( static_cast<uint32_t>( cur[( perm.y >> 16 ) & 0xFFU] ) << 16 )
+                     | ( static_cast<uint32_t>( cur[perm.y >> 24] ) << 24 );
+        lists[static_cast<uint64_t>( j ) * 32U + lane] = mine;   /* the chunk's start list replaces its permutation */
+        {
+            /* chunk byte counts -> where each chunk's bytes start in L (every lane keeps the same running sum) */
+            const ChunkCheckpoint ck = ckpt[j];
+            flags |= ck.runShift;
+            if ( lane == 0 ) {
+                ckpt[j] = ChunkCheckpoint{ static_cast<uint32_t>( min( produced, static_cast<uint64_t>( 0xFFFFFFFFU ) ) ),
+                                           ck.runShift & ~LONG_RUN_FLAG };
+            }
+            produced += ck.outOffset;
+        }
+        __syncwarp();
+        curWords[lane] = composed;
+        __syncwarp();
+        perm = nextPerm;
+    }
+    if ( lane == 0 ) {
+        if ( ( ( flags & LONG_RUN_FLAG ) != 0 ) || ( produced > DBUF_SIZE ) ) {
+            bm.status = ST_INTERNAL_CAREFUL;   /* bzip2.hpp:751-756 / :776-780 or a wrapped run number: the exact decoder decides */
+        } else if ( bm.origPtr >= produced ) {
+            bm.status = IBZ2_ST_ORIGPTR;       /* bzip2.hpp:794-798 */
+            bm.endBit = bm.bitOffset;
+        } else {
+            bm.n = static_cast<uint32_t>( produced );
+        }
+    }
+}
+
+/* ---------------------------------------------------------------- K2e ---------------------------------------- */
+constexpr int MTFE_WARPS = 4;
+constexpr uint32_t STAGE_BYTES = 4096;
+constexpr uint32_t PER_LANE = MTF_CHUNK / 32U;   /* 32 symbols per lane */
+
+struct ExpandShared
+{
+    uint16_t sym16[MTF_CHUNK];
+    uint8_t sym8[MTF_CHUNK];
+    uint8_t list[256];
+    uint8_t stage[STAGE_BYTES + 16];
+};
+
+__device__ __forceinline__ uint32_t
+runShare( uint32_t sym, uint32_t k )
+{
+    return k < 32U ? ( ( sym + 1U ) << k ) : 0U;
+}
+
+__global__ void __launch_bounds__( MTFE_WARPS * 32 )
+mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict__ scratchAll,
+                 uint8_t* __restrict__ lbytesAll )
+{
+    __shared__ __align__( 16 ) ExpandShared shared[MTFE_WARPS];
+
+    const uint32_t block = blockIdx.y;
+    const BlockMeta& bm = meta[block];
+    if ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) {
+        return;
+    }
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31U;
+    const uint32_t nCoded = bm.nCoded;
+    const uint32_t n = bm.n;
+    const uint32_t chunk = blockIdx.x * MTFE_WARPS + warp;
+    const uint32_t begin = chunk << MTF_CHUNK_SHIFT;
+    if ( begin >= nCoded ) {
+        return;
+    }
+    const uint32_t count = min( MTF_CHUNK, nCoded - begin );
+    ExpandShared& sh = shared[warp];
+    const uint8_t* const scratch = k2Scratch( scratchAll, block );
+    uint8_t* const lbytes = lbytesAll + static_cast<uint64_t>( block ) * LBYTES_STRIDE;
+
+    /* stage the chunk: 2 KB of symbols, 1 KB of symbolic bytes, the start list */
+    {
+        const uint4* s16 = reinterpret_cast<const uint4*>( scratch + K2_SYM16_OFFSET + static_cast<uint64_t>( begin ) * 2U );
+        const uint4* s8 = reinterpret_cast<const uint4*>( scratch + K2_SYM8_OFFSET + begin );
+        const uint2* ls = reinterpret_cast<const uint2*>( scratch + K2_LISTS_OFFSET + static_cast<uint64_t>( chunk ) * 256U );
+        uint4* d16 = reinterpret_cast<uint4*>( sh.sym16 );
+        uint4* d8 = reinterpret_cast<uint4*>( sh.sym8 );
+#pragma unroll
+        for ( uint32_t i = 0; i < 4U; ++i ) {
+            d16[i * 32U + lane] = s16[i * 32U + lane];
+        }
+#pragma unroll
+        for ( uint32_t i = 0; i < 2U; ++i ) {
+            d8[i * 32U + lane] = s8[i * 32U + lane];
+        }
+        reinterpret_cast<uint2*>( sh.list )[lane] = ls[lane];
+    }
+    const ChunkCheckpoint ck = reinterpret_cast<const ChunkCheckpoint*>( scratch + K2_CKPT_OFFSET )[chunk];
+    __syncwarp();
+
+    /* lane l owns symbols [32 l, 32 l + 32) of the chunk */
+    const uint32_t first = lane * PER_LANE;
+    const uint32_t mine = first >= count ? 0U : min( PER_LANE, count - first );
+
+    /* position inside a RUNA/RUNB number at the lane's first symbol */
+    uint32_t trailing = 0;
+    bool allRun = true;
+    for ( uint32_t i = 0; i < mine; ++i ) {
+        const bool isRun = sh.sym16[first + i] <= 1U;
+        trailing = isRun ? trailing + 1U : 0U;
+        allRun = allRun && isRun;
+    }
+    const uint32_t allRunMask = __ballot_sync( FULL, allRun );
+    uint32_t k0;
+    {
+        /* nearest lane below that contains a non-run symbol */
+        const uint32_t below = ~allRunMask & ( ( 1U << lane ) - 1U );
+        const uint32_t src = below == 0 ? 0U : 31U - static_cast<uint32_t>( __clz( static_cast<int>( below ) ) );
+        const uint32_t t = __shfl_sync( FULL, trailing, src );
+        k0 = below == 0 ? ck.runShift + PER_LANE * lane : t + PER_LANE * ( lane - 1U - src );
+    }
+
+    /* bytes produced by the lane's symbols */
+    uint32_t total = 0;
+    {
+        uint32_t k = k0;
+        for ( uint32_t i = 0; i < mine; ++i ) {
+            const uint32_t sym = sh.sym16[first + i];
+            if ( sym <= 1U ) {
+                total += runShare( sym, k );
+                ++k;
+            } else {
+                total += 1U;
+                k = 0;
+            }
+        }
+    }
+    uint32_t incl = total;
+#pragma unroll
+    for ( int d = 1; d < 32; d <<= 1 ) {
+        const uint32_t up = __shfl_up_sync( FULL, incl, d );
+        if ( lane >= static_cast<uint32_t>( d ) ) {
+            incl += up;
+        }
+    }
+    const uint32_t chunkTotal = __shfl_sync( FULL, incl, 31 );
+    const uint32_t chunkBase = ck.outOffset;
+    uint32_t pos = incl - total;   /* relative to chunkBase */
+
+    if ( chunkTotal <= STAGE_BYTES ) {
+        /* common case: assemble the chunk's bytes in shared memory, then write 128-byte rows */
+        uint32_t k = k0;
+        for ( uint32_t i = 0; i < mine; ++i ) {
+            const uint32_t sym = sh.sym16[first + i];
+            const uint8_t byte = sh.list[sh.sym8[first + i]];
+            uint32_t c = 1;
+            if ( sym <= 1U ) {
+                c = runShare( sym, k );
+                ++k;
+            } else {
+                k = 0;
+            }
+            for ( uint32_t r = 0; r < c; ++r ) {
+                sh.stage[pos + r] = byte;
+            }
+            pos += c;
+        }
+        __syncwarp();
+        const uint32_t limit = chunkBase < n ? min( chunkTotal, n - chunkBase ) : 0U;
+        uint8_t* const dst = lbytes + chunkBase;
+        const uint32_t head = min( limit, ( 4U - ( chunkBase & 3U ) ) & 3U );
+        if ( lane < head ) {
+            dst[lane] = sh.stage[lane];
+        }
+        const uint32_t words = ( limit - head ) >> 2;
+        const uint32_t* const stageWords = reinterpret_cast<const uint32_t*>( sh.stage );
+        uint32_t* const dstWords = reinterpret_cast<uint32_t*>( dst + head );
+        for ( uint32_t w = lane; w < words; w += 32U ) {
+            /* stage bytes head + 4 w .. + 3: unaligned in shared memory whenever head != 0 */
+            const uint32_t lo = stageWords[w];
+            const uint32_t hi = stageWords[w + 1U];
+            dstWords[w] = __funnelshift_r( lo, hi, 8U * head );
+        }
+        const uint32_t tail = head + 4U * words;
+        if ( tail + lane < limit ) {
+            dst[tail + lane] = sh.stage[tail + lane];
+        }
+    } else {
+        /* long runs: short shares are stored by their lane, long ones by the whole warp */
+        uint32_t k = k0;
+        for ( uint32_t i = 0; i < PER_LANE; ++i ) {
+            uint32_t c = 0;
+            uint32_t byte = 0;
+            if ( i < mine ) {
+                const uint32_t sym = sh.sym16[first + i];
+                byte = sh.list[sh.sym8[first + i]];
+                c = 1;
+                if ( sym <= 1U ) {
+                    c = runShare( sym, k );
+                    ++k;
+                } else {
+                    k = 0;
+                }
+            }
+            const uint32_t at = chunkBase + pos;
+            pos += c;
+            const bool isLong = c >= 64U;
+            if ( !isLong ) {
+                for ( uint32_t r = 0; r < c; ++r ) {
+                    if ( at + r < n ) {
+                        lbytes[at + r] = static_cast<uint8_t>( byte );
+                    }
+                }
+            }
+            uint32_t pending = __ballot_sync( FULL, isLong );
+            while ( pending != 0 ) {
+                const uint32_t src = static_cast<uint32_t>( __ffs( static_cast<int>( pending ) ) ) - 1U;
+                pending &= pending - 1U;
+                const uint32_t a = __shfl_sync( FULL, at, src );
+                const uint32_t cc = __shfl_sync( FULL, c, src );
+                const uint32_t bb = __shfl_sync( FULL, byte, src );
+                const uint32_t end = ( a < n ) ? a + min( cc, n - a ) : a;
+                /* byte stores up to a 4-byte boundary, then words, then the tail */
+                const uint32_t alignedBegin = min( end, ( a + 3U ) & ~3U );
+                const uint32_t alignedEnd = alignedBegin + ( ( end - alignedBegin ) & ~3U );
+                if ( a + lane < alignedBegin ) {
+                    lbytes[a + lane] = static_cast<uint8_t>( bb );
+                }
+                uint32_t* const words = reinterpret_cast<uint32_t*>( lbytes );
+                for ( uint32_t w = ( alignedBegin >> 2 ) + lane; w < ( alignedEnd >> 2 ); w += 32U ) {
+                    words[w] = bb * 0x01010101U;
+                }
+                if ( alignedEnd + lane < end ) {
+                    lbytes[alignedEnd + lane] = static_cast<uint8_t>( bb );
+                }
+            }
+        }
+    }
+}
+}  // namespace
+
+void
+launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_t* scratch, uint8_t* lbytes,
+           cudaStream_t stream )
+{
+    if ( nblocks == 0 ) {
+        return;
+    }
+    {
+        const dim3 grid( ( MAX_CHUNKS + MTFC_THREADS - 1U ) / MTFC_THREADS, nblocks );
+        mtfChunkKernel<<<grid, MTFC_THREADS, 0, stream>>>( meta, scratch );
+    }
+    mtfListsKernel<<<( nblocks + MTFL_WARPS - 1U ) / MTFL_WARPS, MTFL_WARPS * 32, 0, stream>>>( meta, nblocks, tables,
+                                                                                             scratch );
+    {
+        const dim3 grid( ( MAX_CHUNKS + MTFE_WARPS - 1U ) / MTFE_WARPS, nblocks );
+        mtfExpandKernel<<<grid, MTFE_WARPS * 32, 0, stream>>>( meta, scratch, lbytes );
+    }
+}
+
+void
+launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* lbytes,
+                     uint8_t* selectors, BlockTables* tables, uint32_t* scratch, uint32_t* counter, cudaStream_t stream )
+{
+    launchHuffmanHeader( data, nbytes, meta, nblocks, selectors, tables, stream );
+    launchHuffmanBits( data, nbytes, meta, nblocks, selectors, tables, scratch, counter, stream );
+    launchMtf( meta, nblocks, tables, scratch, lbytes, stream );
+    launchHuffmanCareful( data, nbytes, meta, nblocks, lbytes, selectors, stream );
+}
+}  // namespace ibz2
