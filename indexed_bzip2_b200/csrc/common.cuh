@@ -69,6 +69,8 @@ struct alignas( 16 ) BlockTables
     uint16_t count[MAX_GROUPS][MAX_CODE_LEN + 2];
     uint16_t offset[MAX_GROUPS][MAX_CODE_LEN + 2];
     uint32_t maxLen[MAX_GROUPS + 2];
+    uint64_t limit[MAX_GROUPS][MAX_CODE_LEN + 2];   /* ( first + count ) << ( 32 - len ): codes of <= len bits are below it */
+    int32_t base[MAX_GROUPS][MAX_CODE_LEN + 2];     /* offset - first: perm index of a code of len bits = code + base */
     uint8_t s2b[256];                           /* symbolToByte (bzip2.hpp:526-571) */
     uint64_t dataStartBit;                      /* first bit of the Huffman-coded symbols */
     uint32_t symbolCount;

@@ -36,7 +36,13 @@ static_assert( BITS_SLOTS == 32, "the LUT rows are 32 decoders wide" );
 constexpr uint32_t LUT_ROW_BYTES = BITS_SLOTS * 2U;               /* one u16 per decoder */
 constexpr uint32_t LUT_ENTRIES = MAX_GROUPS * HUFF_LUT_SIZE;      /* 3072 rows */
 constexpr uint32_t SYM_LIMIT = DBUF_SIZE;                         /* a clean block has at most this many symbols */
-constexpr uint32_t GROUP_MAX_WORDS = ( GROUP_SIZE * MAX_CODE_LEN + 31U ) / 32U + 2U;
+constexpr uint32_t GROUP_MAX_WORDS = ( GROUP_SIZE * MAX_CODE_LEN + 31U ) / 32U + 4U + 96U;   /* + prefetch distance */
+
+__device__ __forceinline__ void
+prefetchL1( const void* p )
+{
+    asm volatile( "prefetch.global.L1 [%0];" ::"l"( p ) );
+}
 
 struct Decoder
 {
@@ -69,19 +75,23 @@ consume( Decoder& d, uint32_t len )
 }
 
 /* Code longer than the LUT width, or no code at all (HuffmanCodingShortBitsCached.hpp:117-150).  Needs 20 valid bits.
- * Returns ( symbol << 5 ) | length like a LUT entry, 0 when the bits match no code. */
+ * The caller has established that no code of at most HUFF_LUT_BITS bits matches.  Canonical codes grow with their
+ * length when left-aligned, so the length is the number of per-length limits the window has reached; the loads are
+ * independent of each other (one L1 line).  Returns ( symbol << 5 ) | length like a LUT entry, 0 for "no code". */
 __device__ __noinline__ uint32_t
 decodeLong( const BlockTables* __restrict__ bt, uint32_t table, uint32_t hi )
 {
-    const uint32_t tableMaxLen = bt->maxLen[table];
-    for ( uint32_t len = HUFF_LUT_BITS + 1; len <= tableMaxLen; ++len ) {
-        const uint32_t cd = hi >> ( 32U - len );
-        const uint32_t f = bt->first[table][len];
-        if ( ( cd >= f ) && ( cd - f < bt->count[table][len] ) ) {
-            return ( static_cast<uint32_t>( bt->perm[table][bt->offset[table][len] + ( cd - f )] ) << 5 ) | len;
-        }
+    const uint64_t* const limit = bt->limit[table];
+    uint32_t len = HUFF_LUT_BITS + 1;
+#pragma unroll
+    for ( uint32_t l = HUFF_LUT_BITS + 1; l <= MAX_CODE_LEN; ++l ) {
+        len += ( static_cast<uint64_t>( hi ) >= limit[l] ) ? 1U : 0U;
     }
-    return 0;
+    if ( len > MAX_CODE_LEN ) {
+        return 0;
+    }
+    const uint32_t idx = ( hi >> ( 32U - len ) ) + static_cast<uint32_t>( bt->base[table][len] );
+    return ( static_cast<uint32_t>( bt->perm[table][idx] ) << 5 ) | len;
 }
 
 __global__ void __launch_bounds__( BITS_WARPS * 32, 1 )
@@ -176,19 +186,37 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             uint32_t* const pairOut = reinterpret_cast<uint32_t*>( symOut + nsym );   /* nsym is a multiple of 50 */
 
             if ( d.wordIdx + GROUP_MAX_WORDS < fullWords ) {
-                /* ---- hot loop: two symbols per iteration, no file-end checks ---- */
+                /* ---- hot loop: two symbols per iteration, no file-end checks ----
+                 * Two raw words are kept in flight behind the window so that a load has two refills to land. */
                 const uint32_t* wp = dataWords + d.wordIdx;
+                uint32_t raw0 = __byte_perm( d.nextW, 0, 0x0123 );   /* back to memory order: swapped when used */
+                uint32_t raw1 = __ldg( wp + 1 );
                 uint32_t g = 0;
-#pragma unroll 1
+                uint32_t eobTail = 0;   /* bits consumed after the end-of-block symbol */
+#pragma unroll 5
                 for ( ; g < GROUP_SIZE / 2U; ++g ) {
-                    if ( d.nb <= 32 ) {
-                        d.hi |= d.nb == 32 ? 0U : ( d.nextW >> d.nb );
-                        d.lo = d.nb == 0 ? 0U : ( d.nextW << ( 32 - d.nb ) );
-                        d.nb += 32;
-                        ++wp;
-                        d.nextW = __byte_perm( __ldg( wp ), 0, 0x0123 );
-                    }
+                    /* The first lookup only needs the top 9 bits, which are valid before the refill (at least 15 bits
+                     * are left after a pair), so it is issued first and the refill fills its latency. */
                     uint32_t e0 = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_ROW_BYTES );
+                    {
+                        /* refill, written as selects so that it is predicated, not branched around: the load then
+                         * lands in raw1's own register and nothing waits for it before the next refill */
+                        const bool rf = d.nb <= 32;
+                        const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
+                        const uint32_t addHi = __funnelshift_rc( x, 0U, static_cast<uint32_t>( d.nb ) );
+                        const uint32_t newLo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - d.nb ) );
+                        d.hi |= rf ? addHi : 0U;
+                        d.lo = rf ? newLo : d.lo;
+                        d.nb += rf ? 32 : 0;
+                        raw0 = rf ? raw1 : raw0;
+                        wp += rf ? 1 : 0;
+                        if ( rf ) {
+                            raw1 = __ldg( wp + 1 );
+                            if ( ( reinterpret_cast<uintptr_t>( wp ) & 127U ) == 0 ) {
+                                prefetchL1( wp + 64 );   /* stays inside the file: see GROUP_MAX_WORDS */
+                            }
+                        }
+                    }
                     if ( e0 == 0 ) {
                         e0 = decodeLong( bt, table, d.hi );
                         if ( e0 == 0 ) {
@@ -197,42 +225,64 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                         }
                         consume( d, e0 & 31U );
                         if ( d.nb <= 32 ) {
-                            d.hi |= d.nb == 32 ? 0U : ( d.nextW >> d.nb );
-                            d.lo = d.nb == 0 ? 0U : ( d.nextW << ( 32 - d.nb ) );
+                            const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
+                            d.hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( d.nb ) );
+                            d.lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - d.nb ) );
                             d.nb += 32;
+                            raw0 = raw1;
+                            raw1 = __ldg( wp + 2 );
                             ++wp;
-                            d.nextW = __byte_perm( __ldg( wp ), 0, 0x0123 );
                         }
                     } else {
                         consume( d, e0 & 31U );
                     }
                     const uint32_t sym0 = e0 >> 5;
-                    if ( sym0 > symbolCount ) {
-                        outcome = 1;
-                        nsym += 2U * g;
-                        break;
-                    }
                     uint32_t e1 = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_ROW_BYTES );
                     if ( e1 == 0 ) {
-                        e1 = decodeLong( bt, table, d.hi );
-                        if ( e1 == 0 ) {
-                            outcome = 2;
-                            break;
+                        if ( sym0 > symbolCount ) {
+                            e1 = ( symbolCount + 2U ) << 5;   /* whatever follows the end-of-block symbol is not ours */
+                        } else {
+                            e1 = decodeLong( bt, table, d.hi );
+                            if ( e1 == 0 ) {
+                                outcome = 2;
+                                break;
+                            }
                         }
+                        consume( d, e1 & 31U );
+                        if ( d.nb <= 32 ) {
+                            /* a long code can leave fewer than the 9 bits the next pair looks up before refilling */
+                            const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
+                            d.hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( d.nb ) );
+                            d.lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - d.nb ) );
+                            d.nb += 32;
+                            raw0 = raw1;
+                            raw1 = __ldg( wp + 2 );
+                            ++wp;
+                        }
+                    } else {
+                        consume( d, e1 & 31U );
                     }
-                    consume( d, e1 & 31U );
                     const uint32_t sym1 = e1 >> 5;
-                    if ( sym1 > symbolCount ) {
-                        reinterpret_cast<uint16_t*>( pairOut + g )[0] = static_cast<uint16_t>( sym0 );
+                    pairOut[g] = sym0 | ( sym1 << 16 );
+                    if ( max( sym0, sym1 ) > symbolCount ) {
+                        /* end of block (bzip2.hpp:766-768) */
                         outcome = 1;
-                        nsym += 2U * g + 1U;
+                        if ( sym0 > symbolCount ) {
+                            nsym += 2U * g;
+                            eobTail = e1 & 31U;
+                        } else {
+                            nsym += 2U * g + 1U;
+                        }
                         break;
                     }
-                    pairOut[g] = sym0 | ( sym1 << 16 );
                 }
+                /* the window holds wp[-2], wp[-1]; raw0 = wp[0]: hand the position back in file terms */
                 d.wordIdx = static_cast<uint64_t>( wp - dataWords );
+                d.nextW = __byte_perm( raw0, 0, 0x0123 );
                 if ( outcome == 0 ) {
                     nsym += GROUP_SIZE;
+                } else if ( eobTail != 0 ) {
+                    d.nb += static_cast<int>( eobTail );   /* only the bit position is used from here on */
                 }
             } else {
                 /* ---- the last groups before the end of the file: same loop with checked loads ---- */

@@ -411,6 +411,10 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
                     bt.first[g][lane] = ws.first[g][lane];
                     bt.count[g][lane] = ws.count[g][lane];
                     bt.offset[g][lane] = ws.offset[g][lane];
+                    /* left-aligned end of the codes of at most `lane` bits, and perm index = code + base (K2b decodeLong) */
+                    const bool real = ( lane >= 1U ) && ( lane <= MAX_CODE_LEN );
+                    bt.limit[g][lane] = real ? static_cast<uint64_t>( ws.first[g][lane] + ws.count[g][lane] ) << ( 32U - lane ) : 0U;
+                    bt.base[g][lane] = real ? static_cast<int32_t>( ws.offset[g][lane] ) - static_cast<int32_t>( ws.first[g][lane] ) : 0;
                 }
             }
             if ( lane < groupCount ) {
