@@ -6,12 +6,15 @@
  * i.e. BurrowsWheelerTransformData::prepare (indexed_bzip2/bzip2.hpp:810-847) including the 256-bin byte histogram
  * that the reference accumulates during readBlockData (bzip2.hpp:698,759,788).  One CTA per block.
  *
- * Stability is what makes the scatter order-dependent; it is obtained without atomics by giving each of the 256
- * threads a contiguous slice of L and a private 256-bin counter row in shared memory:
- *   phase 1  every thread histograms its slice (u16 counters, thread-major rows -> bank = bin/2, conflict-light);
- *   phase 2  thread b turns column b into exclusive prefixes: u16 within groups of 16 threads plus a u32 base per
- *            group and bin (a slice holds <= 3520 symbols, 16 slices < 65536);
- *   phase 3  every thread replays its slice and scatters ( i << 8 ) | byte to base + running count.
+ * A direct scatter writes 4 bytes at a time into 256 slowly advancing streams per block; with hundreds of blocks in
+ * flight the half-written 32-byte sectors fall out of L2 and every store turns into a DRAM read-modify-write (measured:
+ * 64 B of DRAM traffic per 4-byte entry).  So the scatter is staged through shared memory, tile by tile:
+ *   pass 1  histogram of the whole block (warp-aggregated with match.any, so runs of equal bytes cost one add per row)
+ *           -> exclusive scan -> running[b] = where the next entry of byte b goes;
+ *   pass 2  for every tile of TILE symbols, in order: stable local counting sort into shared memory (rank inside the
+ *           warp row from match.any, per-warp counters, scan over warps and bins), then the sorted tile is written out
+ *           run by run: entries of one byte value are contiguous both in shared memory and in dbuf, so the stores of
+ *           a warp cover whole sectors; running[b] advances by the tile's count.
  * Algorithmic HBM traffic per block: N bytes read twice (second pass hits L2) + 4N bytes written.
  */
 #include "common.cuh"
@@ -20,18 +23,50 @@ namespace ibz2
 {
 namespace
 {
-constexpr int PREP_THREADS = 256;
-constexpr int GROUP_THREADS = 16;
-constexpr int GROUPS = PREP_THREADS / GROUP_THREADS;
+constexpr int PREP_THREADS = 1024;
+constexpr int PREP_WARPS = PREP_THREADS / 32;
+constexpr uint32_t ROWS = 8;                            /* rows of 32 symbols per warp and tile */
+constexpr uint32_t TILE = PREP_THREADS * ROWS;          /* 8192 symbols */
+constexpr uint32_t FULL = 0xFFFFFFFFU;
+constexpr uint32_t INVALID_KEY = 256;
 
 struct PrepShared
 {
-    uint16_t hist[PREP_THREADS][256]; /* [thread][bin] */
-    uint32_t groupBase[GROUPS][256];  /* [group][bin] */
-    uint32_t warpSums[PREP_THREADS / 32];
+    uint32_t sorted[TILE];                /* the tile in (byte, position) order */
+    uint16_t warpCount[PREP_WARPS][256];  /* per tile: symbols of byte b seen by warp w, then exclusive over the warps */
+    uint32_t running[256];                /* next dbuf index of byte b */
+    uint32_t localOff[256];               /* first index of byte b inside sorted[] */
+    uint32_t blockHist[256];
+    uint32_t warpSums[8];
 };
 
-__global__ void __launch_bounds__( PREP_THREADS )
+/* exclusive scan over 256 values held by threads 0..255 (one per thread); needs two __syncthreads by all threads */
+__device__ __forceinline__ uint32_t
+scan256( uint32_t value, uint32_t tid, uint32_t* warpSums )
+{
+    uint32_t incl = value;
+#pragma unroll
+    for ( int d = 1; d < 32; d <<= 1 ) {
+        const uint32_t up = __shfl_up_sync( FULL, incl, d );
+        if ( ( tid & 31U ) >= static_cast<uint32_t>( d ) ) {
+            incl += up;
+        }
+    }
+    if ( ( tid < 256U ) && ( ( tid & 31U ) == 31U ) ) {
+        warpSums[tid >> 5] = incl;
+    }
+    __syncthreads();
+    uint32_t base = incl - value;
+    if ( tid < 256U ) {
+        for ( uint32_t w = 0; w < ( tid >> 5 ); ++w ) {
+            base += warpSums[w];
+        }
+    }
+    __syncthreads();
+    return base;
+}
+
+__global__ void __launch_bounds__( PREP_THREADS, 2 )
 bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ dbufAll,
                   const BlockMeta* __restrict__ meta )
 {
@@ -46,85 +81,111 @@ bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ 
     const uint8_t* __restrict__ lbytes = lbytesAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
     uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( blockIdx.x ) * DBUF_STRIDE;
     const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31U;
+    const uint32_t warp = tid >> 5;
+    const uint32_t ltMask = ( 1U << lane ) - 1U;
 
-    /* slice of this thread: [begin, end), begin a multiple of 16 */
-    const uint32_t chunk = ( ( ( n + PREP_THREADS - 1 ) / PREP_THREADS ) + 15U ) & ~15U;
-    const uint32_t begin = min( n, tid * chunk );
-    const uint32_t end = min( n, begin + chunk );
+    if ( tid < 256U ) {
+        sh.blockHist[tid] = 0;
+    }
+    __syncthreads();
 
+    /* ---- pass 1: byte histogram of the block (bzip2.hpp:759,788) ---- */
+    for ( uint32_t base = 0; base < n; base += PREP_THREADS * 4U ) {
+        const uint32_t i = base + tid * 4U;
+        /* LBYTES_STRIDE pads the last word of a block */
+        const uint32_t word = i < n ? *reinterpret_cast<const uint32_t*>( lbytes + i ) : 0U;
+#pragma unroll
+        for ( uint32_t k = 0; k < 4U; ++k ) {
+            const uint32_t key = ( i + k < n ) ? ( ( word >> ( 8U * k ) ) & 0xFFU ) : INVALID_KEY;
+            const uint32_t same = __match_any_sync( FULL, key );
+            if ( ( key != INVALID_KEY ) && ( ( same & ltMask ) == 0 ) ) {
+                atomicAdd( &sh.blockHist[key], static_cast<uint32_t>( __popc( same ) ) );
+            }
+        }
+    }
+    __syncthreads();
     {
-        uint32_t* words = reinterpret_cast<uint32_t*>( &sh.hist[0][0] );
-        for ( uint32_t i = tid; i < PREP_THREADS * 256U / 2U; i += PREP_THREADS ) {
-            words[i] = 0;
+        /* cumulative byte counts (bzip2.hpp:814-823) */
+        const uint32_t mine = tid < 256U ? sh.blockHist[tid] : 0U;
+        const uint32_t base = scan256( mine, tid, sh.warpSums );
+        if ( tid < 256U ) {
+            sh.running[tid] = base;
         }
     }
     __syncthreads();
 
-    /* phase 1: private histogram */
-    uint16_t* const myHist = sh.hist[tid];
-    for ( uint32_t i = begin; i < end; i += 16U ) {
-        const uint4 v = *reinterpret_cast<const uint4*>( lbytes + i );
-        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
-#pragma unroll
-        for ( uint32_t k = 0; k < 16U; ++k ) {
-            if ( i + k < end ) {
-                const uint32_t b = ( w[k >> 2] >> ( 8U * ( k & 3U ) ) ) & 0xFFU;
-                myHist[b] = static_cast<uint16_t>( myHist[b] + 1U );
+    /* ---- pass 2: tile-wise stable scatter ---- */
+    for ( uint32_t tileBase = 0; tileBase < n; tileBase += TILE ) {
+        {
+            uint32_t* words = reinterpret_cast<uint32_t*>( &sh.warpCount[0][0] );
+            for ( uint32_t i = tid; i < PREP_WARPS * 256U / 2U; i += PREP_THREADS ) {
+                words[i] = 0;
             }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    /* phase 2: column tid -> exclusive prefixes over the threads */
-    uint32_t total = 0;
-    for ( int g = 0; g < GROUPS; ++g ) {
-        uint32_t inGroup = 0;
+        /* a) warp w owns symbols tileBase + 256 w .. + 255 as ROWS rows of 32; rank of each symbol among the equal
+         *    bytes its warp has seen so far */
+        const uint32_t first = tileBase + warp * ( 32U * ROWS ) + lane;
+        uint32_t keyRank[ROWS];   /* key | rank << 16 */
+        uint16_t* const myCount = sh.warpCount[warp];
 #pragma unroll
-        for ( int r = 0; r < GROUP_THREADS; ++r ) {
-            const int t = g * GROUP_THREADS + r;
-            const uint32_t c = sh.hist[t][tid];
-            sh.hist[t][tid] = static_cast<uint16_t>( inGroup );
-            inGroup += c;
+        for ( uint32_t r = 0; r < ROWS; ++r ) {
+            const uint32_t i = first + 32U * r;
+            const uint32_t key = i < n ? lbytes[i] : INVALID_KEY;
+            const uint32_t same = __match_any_sync( FULL, key );
+            const uint32_t leader = static_cast<uint32_t>( __ffs( static_cast<int>( same ) ) ) - 1U;
+            uint32_t before = 0;
+            if ( ( lane == leader ) && ( key != INVALID_KEY ) ) {
+                before = myCount[key];
+                myCount[key] = static_cast<uint16_t>( before + static_cast<uint32_t>( __popc( same ) ) );
+            }
+            before = __shfl_sync( FULL, before, leader );
+            keyRank[r] = key | ( ( before + static_cast<uint32_t>( __popc( same & ltMask ) ) ) << 16 );
+            __syncwarp();
         }
-        sh.groupBase[g][tid] = total;
-        total += inGroup;
-    }
-    /* exclusive scan of the bin totals over the 256 bins (cumulative byte counts, bzip2.hpp:814-823) */
-    uint32_t incl = total;
-#pragma unroll
-    for ( int d = 1; d < 32; d <<= 1 ) {
-        const uint32_t up = __shfl_up_sync( 0xFFFFFFFFU, incl, d );
-        if ( ( tid & 31U ) >= static_cast<uint32_t>( d ) ) {
-            incl += up;
-        }
-    }
-    if ( ( tid & 31U ) == 31U ) {
-        sh.warpSums[tid >> 5] = incl;
-    }
-    __syncthreads();
-    uint32_t binBase = incl - total;
-    for ( uint32_t w = 0; w < ( tid >> 5 ); ++w ) {
-        binBase += sh.warpSums[w];
-    }
-    for ( int g = 0; g < GROUPS; ++g ) {
-        sh.groupBase[g][tid] += binBase;
-    }
-    __syncthreads();
+        __syncthreads();
 
-    /* phase 3: replay the slice and scatter */
-    const uint32_t* const myBase = &sh.groupBase[tid / GROUP_THREADS][0];
-    for ( uint32_t i = begin; i < end; i += 16U ) {
-        const uint4 v = *reinterpret_cast<const uint4*>( lbytes + i );
-        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
-#pragma unroll
-        for ( uint32_t k = 0; k < 16U; ++k ) {
-            if ( i + k < end ) {
-                const uint32_t b = ( w[k >> 2] >> ( 8U * ( k & 3U ) ) ) & 0xFFU;
-                const uint32_t r = myHist[b];
-                myHist[b] = static_cast<uint16_t>( r + 1U );
-                dbuf[myBase[b] + r] = ( ( i + k ) << 8 ) | b;
+        /* b) per byte value: exclusive scan over the warps, tile count, exclusive scan over the byte values */
+        uint32_t tileCount = 0;
+        if ( tid < 256U ) {
+#pragma unroll 8
+            for ( uint32_t w = 0; w < static_cast<uint32_t>( PREP_WARPS ); ++w ) {
+                const uint32_t c = sh.warpCount[w][tid];
+                sh.warpCount[w][tid] = static_cast<uint16_t>( tileCount );
+                tileCount += c;
             }
         }
+        const uint32_t off = scan256( tileCount, tid, sh.warpSums );
+        if ( tid < 256U ) {
+            sh.localOff[tid] = off;
+        }
+        __syncthreads();
+
+        /* c) stable placement inside the tile */
+#pragma unroll
+        for ( uint32_t r = 0; r < ROWS; ++r ) {
+            const uint32_t key = keyRank[r] & 0xFFFFU;
+            if ( key != INVALID_KEY ) {
+                const uint32_t pos = sh.localOff[key] + sh.warpCount[warp][key] + ( keyRank[r] >> 16 );
+                sh.sorted[pos] = ( ( first + 32U * r ) << 8 ) | key;
+            }
+        }
+        __syncthreads();
+
+        /* d) write the runs out: neighbouring threads write neighbouring entries of one byte value */
+        const uint32_t tileN = min( TILE, n - tileBase );
+        for ( uint32_t pos = tid; pos < tileN; pos += PREP_THREADS ) {
+            const uint32_t e = sh.sorted[pos];
+            const uint32_t key = e & 0xFFU;
+            dbuf[sh.running[key] + ( pos - sh.localOff[key] )] = e;
+        }
+        __syncthreads();
+        if ( tid < 256U ) {
+            sh.running[tid] += tileCount;
+        }
+        /* the next iteration's first __syncthreads orders this update before any use */
     }
 }
 }  // namespace

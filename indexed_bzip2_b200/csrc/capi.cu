@@ -283,7 +283,7 @@ ibz2_create( int device, ibz2_ctx** out )
     }
     ctx->sms = prop.multiProcessorCount;
     g_smCount = ctx->sms;
-    ctx->batchBlocks = static_cast<uint32_t>( ctx->sms ) * 12U;
+    ctx->batchBlocks = static_cast<uint32_t>( ctx->sms ) * 64U;   /* two rounds of K2b's 32 decoders per SM */
     ibz2::initCrcConstants();
     if ( ( err = cudaGetLastError() ) != cudaSuccess ) {
         g_createError = std::string( "constant upload failed: " ) + cudaGetErrorString( err );
@@ -498,7 +498,19 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
                 uint8_t* dOut, uint64_t outCapacity, ibz2_block_result* results, uint64_t* totalOut )
 {
     const bool haveOutput = dOut != nullptr;
-    const uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
+    uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
+    if ( wave > ctx->scratchBlocks ) {
+        /* scratch is about 4.6 MB per block in flight: stay inside what the device has left */
+        size_t freeBytes = 0;
+        size_t totalBytes = 0;
+        if ( cudaMemGetInfo( &freeBytes, &totalBytes ) == cudaSuccess ) {
+            const uint64_t perBlock = ibz2::LBYTES_STRIDE + ibz2::DBUF_STRIDE * sizeof( uint32_t ) + ibz2::SEL_STRIDE
+                                      + sizeof( ibz2::BlockTables ) + 4096U;
+            const uint64_t reusable = static_cast<uint64_t>( ctx->scratchBlocks ) * perBlock;
+            const uint64_t fit = ( static_cast<uint64_t>( freeBytes ) + reusable ) / 10U * 9U / perBlock;
+            wave = static_cast<uint32_t>( std::max<uint64_t>( 1, std::min<uint64_t>( wave, fit ) ) );
+        }
+    }
     {
         const int rc = ensureScratch( ctx, wave );
         if ( rc != IBZ2_OK ) {
