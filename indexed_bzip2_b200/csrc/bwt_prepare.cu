@@ -9,10 +9,10 @@
  * A direct scatter writes 4 bytes at a time into 256 slowly advancing streams per block; with hundreds of blocks in
  * flight the half-written 32-byte sectors fall out of L2 and every store turns into a DRAM read-modify-write (measured:
  * 64 B of DRAM traffic per 4-byte entry).  So the scatter is staged through shared memory, tile by tile:
- *   pass 1  histogram of the whole block (warp-aggregated with match.any, so runs of equal bytes cost one add per row)
+ *   pass 1  histogram of the whole block (warp-aggregated per row, so runs of equal bytes cost one add per row)
  *           -> exclusive scan -> running[b] = where the next entry of byte b goes;
  *   pass 2  for every tile of TILE symbols, in order: stable local counting sort into shared memory (rank inside the
- *           warp row from match.any, per-warp counters, scan over warps and bins), then the sorted tile is written out
+ *           warp row from ballots, per-warp counters, scan over warps and bins), then the sorted tile is written out
  *           run by run: entries of one byte value are contiguous both in shared memory and in dbuf, so the stores of
  *           a warp cover whole sectors; running[b] advances by the tile's count.
  * Algorithmic HBM traffic per block: N bytes read twice (second pass hits L2) + 4N bytes written.
@@ -39,6 +39,21 @@ struct PrepShared
     uint32_t blockHist[256];
     uint32_t warpSums[8];
 };
+
+/* Lanes holding the same 9-bit key (what match.any returns), from one ballot per key bit: match.any itself costs a trip
+ * per DISTINCT value in the warp, which is 32 trips per row on high-entropy data. */
+__device__ __forceinline__ uint32_t
+matchKey( uint32_t key )
+{
+    uint32_t same = FULL;
+#pragma unroll
+    for ( uint32_t bit = 0; bit < 9U; ++bit ) {
+        const bool set = ( ( key >> bit ) & 1U ) != 0;
+        const uint32_t votes = __ballot_sync( FULL, set );
+        same &= set ? votes : ~votes;
+    }
+    return same;
+}
 
 /* exclusive scan over 256 values held by threads 0..255 (one per thread); needs two __syncthreads by all threads */
 __device__ __forceinline__ uint32_t
@@ -98,7 +113,7 @@ bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ 
 #pragma unroll
         for ( uint32_t k = 0; k < 4U; ++k ) {
             const uint32_t key = ( i + k < n ) ? ( ( word >> ( 8U * k ) ) & 0xFFU ) : INVALID_KEY;
-            const uint32_t same = __match_any_sync( FULL, key );
+            const uint32_t same = matchKey( key );
             if ( ( key != INVALID_KEY ) && ( ( same & ltMask ) == 0 ) ) {
                 atomicAdd( &sh.blockHist[key], static_cast<uint32_t>( __popc( same ) ) );
             }
@@ -134,7 +149,7 @@ bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ 
         for ( uint32_t r = 0; r < ROWS; ++r ) {
             const uint32_t i = first + 32U * r;
             const uint32_t key = i < n ? lbytes[i] : INVALID_KEY;
-            const uint32_t same = __match_any_sync( FULL, key );
+            const uint32_t same = matchKey( key );
             const uint32_t leader = static_cast<uint32_t>( __ffs( static_cast<int>( same ) ) ) - 1U;
             uint32_t before = 0;
             if ( ( lane == leader ) && ( key != INVALID_KEY ) ) {
