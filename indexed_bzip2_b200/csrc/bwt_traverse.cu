@@ -10,13 +10,19 @@
  *           through the start position p0 is remembered (sstar, kstar).
  *   rank    the successor list of the <= 14063 segments is ranked in shared memory by pointer jumping (Wyllie), with the
  *           list cut at sstar; that gives every segment on p0's cycle its output offset.
- *   pass B  every ranked segment is walked again and its bytes are written to their final positions.
+ *   copy    the bytes a thread met in pass A sit, in walking order, in the thread's own staging stream (STAGE_CAP bytes
+ *           per thread in HBM, written four at a time); once the ranking has given every segment its output offset the
+ *           warps copy the segments from the streams to their final positions, 32 consecutive bytes per step.  This
+ *           replaces a second walk: a walk costs one 32-byte HBM sector per step (T vectors of the blocks in flight are
+ *           far larger than L2), the copy moves each byte once, coalesced.
+ *   pass B  only for what did not fit a staging stream (sums of ~14 geometric segment lengths rarely exceed it; runs of
+ *           pathological T vectors can): those segments are walked again and written directly.
  *   fill    if p0's cycle is shorter than N (periodic data such as b"A" * n, where T splits into many short cycles) the
  *           walk laps its cycle; the remaining output is the periodic continuation of the first lap.
  * A block whose start cycle contains no splitter at all (only tiny cycles can) is walked serially by one thread.
  *
  * The output is the block's byte string BEFORE RLE1 undo ("prerle"), N bytes, written over the block's L buffer.
- * Algorithmic HBM traffic per block: 2 x 4N bytes of random 32-bit reads (two passes) + N bytes written.
+ * Algorithmic HBM traffic per block: 4N bytes of random 32-bit reads + N bytes staged, read back and written.
  */
 #include "common.cuh"
 
@@ -30,6 +36,8 @@ constexpr uint32_t SPACING_SHIFT = 6;
 constexpr uint32_t MAX_SEGMENTS = ( DBUF_SIZE + SPACING - 1 ) / SPACING; /* 14063 */
 constexpr uint32_t PER_THREAD = ( MAX_SEGMENTS + TRAV_THREADS - 1 ) / TRAV_THREADS;
 constexpr uint32_t NIL = 0xFFFFU;
+constexpr uint32_t FULL = 0xFFFFFFFFU;
+constexpr uint32_t STAGE_CAP = TRAV_STAGE_CAP;   /* bytes of staging stream per thread */
 
 struct TraverseShared
 {
@@ -41,7 +49,7 @@ struct TraverseShared
 
 __global__ void __launch_bounds__( TRAV_THREADS, 2 )
 bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll,
-                   BlockMeta* __restrict__ meta )
+                   BlockMeta* __restrict__ meta, uint8_t* __restrict__ stageAll )
 {
     extern __shared__ __align__( 16 ) uint8_t sharedRaw[];
     TraverseShared& sh = *reinterpret_cast<TraverseShared*>( sharedRaw );
@@ -55,6 +63,9 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
     uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
     const uint32_t tid = threadIdx.x;
     const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
+    uint8_t* const stageBlock = stageAll + static_cast<uint64_t>( blockIdx.x ) * TRAV_STAGE_STRIDE;
+    uint32_t* const myStage = reinterpret_cast<uint32_t*>( stageBlock + static_cast<uint64_t>( tid ) * STAGE_CAP );
+    uint16_t* const segLen = reinterpret_cast<uint16_t*>( stageBlock + static_cast<uint64_t>( TRAV_THREADS ) * STAGE_CAP );
     /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's ( T[k] << 8 ) | L[k],
      * so the walk starts at origPtr itself and every load yields the output byte and the next position at once
      * (the reference first hops to T[origPtr], bzip2.hpp:835-838, and reads L at the position it arrives at). */
@@ -66,25 +77,40 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
     }
     __syncthreads();
 
-    /* ---- pass A: segment lengths and successors ---- */
+    /* ---- pass A: segment lengths and successors; the bytes go to the thread's staging stream ---- */
     {
         uint32_t s = tid;
         uint32_t pos = s << SPACING_SHIFT;
         uint32_t steps = 0;
+        uint32_t cursor = 0;   /* bytes this thread has met so far */
+        uint32_t acc = 0;
         while ( s < segments ) {
             if ( pos == p0 ) {
                 sh.sstar = static_cast<int>( s );
                 sh.kstar = steps;
             }
-            pos = __ldg( dbuf + pos ) >> 8;
+            const uint32_t e = __ldg( dbuf + pos );
+            acc |= ( e & 0xFFU ) << ( 8U * ( cursor & 3U ) );
+            ++cursor;
+            if ( ( cursor & 3U ) == 0 ) {
+                if ( cursor <= STAGE_CAP ) {
+                    myStage[( cursor >> 2 ) - 1U] = acc;
+                }
+                acc = 0;
+            }
+            pos = e >> 8;
             ++steps;
             if ( ( pos & ( SPACING - 1 ) ) == 0 ) {
                 sh.jump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
                 sh.dist[s] = steps;
+                segLen[s] = static_cast<uint16_t>( min( steps, 0xFFFFU ) );
                 s += TRAV_THREADS;
                 pos = s << SPACING_SHIFT;
                 steps = 0;
             }
+        }
+        if ( ( ( cursor & 3U ) != 0 ) && ( cursor < STAGE_CAP ) ) {
+            myStage[cursor >> 2] = acc;
         }
     }
     __syncthreads();
@@ -152,12 +178,42 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
         const uint32_t ranked = sh.dist[first];            /* 0 when first == sstar */
         cycleLen = ranked + lenStar;
 
-        /* ---- pass B: write every ranked segment at its output offset ---- */
+        /* ---- copy: warp w moves the segments of its 32 threads from their staging streams to the output ---- */
         {
-            uint32_t s = tid;
-            while ( s < segments ) {
-                if ( sh.jump[s] == NIL ) {
-                    const uint32_t base = tailLen + ranked - sh.dist[s];
+            const uint32_t lane = tid & 31U;
+            const uint32_t warpFirst = tid & ~31U;
+            uint32_t done = 0;   /* bytes of MY stream that belong to the segments handled so far */
+            for ( uint32_t sBase = warpFirst; sBase < segments; sBase += TRAV_THREADS ) {
+                /* the segments sBase .. sBase + 31 belong to lanes 0 .. 31 */
+                const uint32_t s = sBase + lane;
+                uint32_t len = 0;
+                uint32_t base = 0;
+                bool onCycle = false;   /* a segment that reaches sstar lies on p0's cycle */
+                if ( s < segments ) {
+                    len = segLen[s];
+                    onCycle = sh.jump[s] == NIL;
+                    base = tailLen + ranked - sh.dist[s];
+                }
+                const bool fits = ( len < 0xFFFFU ) && ( done + len <= STAGE_CAP );
+                const uint32_t srcOffset = ( tid << TRAV_STAGE_CAP_SHIFT ) + done;
+                done += len;
+                uint32_t todo = __ballot_sync( FULL, onCycle && fits && ( len > 0 ) );
+                while ( todo != 0 ) {
+                    const uint32_t src = static_cast<uint32_t>( __ffs( static_cast<int>( todo ) ) ) - 1U;
+                    todo &= todo - 1U;
+                    const uint32_t l = __shfl_sync( FULL, len, src );
+                    const uint32_t b = __shfl_sync( FULL, base, src );
+                    const uint32_t o = __shfl_sync( FULL, srcOffset, src );
+                    const bool star = static_cast<int>( sBase + src ) == sstar;
+                    for ( uint32_t k = lane; k < l; k += 32U ) {
+                        const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( b + k );
+                        if ( idx < n ) {
+                            prerle[idx] = stageBlock[o + k];
+                        }
+                    }
+                }
+                /* ---- pass B for the segments whose bytes did not fit the staging stream ---- */
+                if ( onCycle && !fits ) {
                     const bool star = static_cast<int>( s ) == sstar;
                     uint32_t pos = s << SPACING_SHIFT;
                     uint32_t k = 0;
@@ -171,7 +227,6 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
                         ++k;
                     } while ( ( pos & ( SPACING - 1 ) ) != 0 );
                 }
-                s += TRAV_THREADS;
             }
         }
         __syncthreads();
@@ -190,10 +245,11 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
 }  // namespace
 
 void
-launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, cudaStream_t stream )
+launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, uint8_t* stage,
+                   cudaStream_t stream )
 {
     cudaFuncSetAttribute( bwtTraverseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                           static_cast<int>( sizeof( TraverseShared ) ) );
-    bwtTraverseKernel<<<nblocks, TRAV_THREADS, sizeof( TraverseShared ), stream>>>( dbuf, prerle, meta );
+    bwtTraverseKernel<<<nblocks, TRAV_THREADS, sizeof( TraverseShared ), stream>>>( dbuf, prerle, meta, stage );
 }
 }  // namespace ibz2

@@ -32,6 +32,7 @@ struct ibz2_ctx
     uint32_t* dDbuf = nullptr;
     uint8_t* dSelectors = nullptr;
     ibz2::BlockTables* dTables = nullptr;
+    uint8_t* dStage = nullptr;
     uint32_t* dCounter = nullptr;
     uint32_t* dWarpBase = nullptr;
     uint32_t* dPieceStart = nullptr;
@@ -98,6 +99,7 @@ freeScratch( ibz2_ctx* ctx )
     cudaFree( ctx->dDbuf );
     cudaFree( ctx->dSelectors );
     cudaFree( ctx->dTables );
+    cudaFree( ctx->dStage );
     cudaFree( ctx->dCounter );
     cudaFree( ctx->dWarpBase );
     cudaFree( ctx->dPieceStart );
@@ -107,6 +109,7 @@ freeScratch( ibz2_ctx* ctx )
     ctx->dDbuf = nullptr;
     ctx->dSelectors = nullptr;
     ctx->dTables = nullptr;
+    ctx->dStage = nullptr;
     ctx->dCounter = nullptr;
     ctx->dWarpBase = nullptr;
     ctx->dPieceStart = nullptr;
@@ -127,6 +130,7 @@ ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dDbuf, b * ibz2::DBUF_STRIDE * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dSelectors, b * ibz2::SEL_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dTables, b * sizeof( ibz2::BlockTables ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dStage, b * ibz2::TRAV_STAGE_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dCounter, ( b + 16 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dWarpBase, b * ibz2::RLE_RANGES * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dPieceStart, ( b + 1 ) * sizeof( uint32_t ) ) );
@@ -500,12 +504,12 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
     const bool haveOutput = dOut != nullptr;
     uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
     if ( wave > ctx->scratchBlocks ) {
-        /* scratch is about 4.6 MB per block in flight: stay inside what the device has left */
+        /* scratch is about 6.7 MB per block in flight: stay inside what the device has left */
         size_t freeBytes = 0;
         size_t totalBytes = 0;
         if ( cudaMemGetInfo( &freeBytes, &totalBytes ) == cudaSuccess ) {
             const uint64_t perBlock = ibz2::LBYTES_STRIDE + ibz2::DBUF_STRIDE * sizeof( uint32_t ) + ibz2::SEL_STRIDE
-                                      + sizeof( ibz2::BlockTables ) + 4096U;
+                                      + sizeof( ibz2::BlockTables ) + ibz2::TRAV_STAGE_STRIDE + 4096U;
             const uint64_t reusable = static_cast<uint64_t>( ctx->scratchBlocks ) * perBlock;
             const uint64_t fit = ( static_cast<uint64_t>( freeBytes ) + reusable ) / 10U * 9U / perBlock;
             wave = static_cast<uint32_t>( std::max<uint64_t>( 1, std::min<uint64_t>( wave, fit ) ) );
@@ -545,7 +549,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         we.e[1] = nextEvent( ctx );
         ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, count, s );
         we.e[2] = nextEvent( ctx );
-        ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, s );
+        ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, ctx->dStage, s );
         we.e[3] = nextEvent( ctx );
         ibz2::launchRleScan( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, s );
         ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
@@ -866,7 +870,7 @@ ibz2_debug_decode_block( ibz2_ctx* ctx, const void* data, uint64_t nbytes, uint6
         IBZ2_CUDA_CHECK( ctx, cudaMemcpy( tvec, ctx->dDbuf, static_cast<uint64_t>( n ) * sizeof( uint32_t ),
                                           cudaMemcpyDeviceToHost ) );
     }
-    ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, 1, s );
+    ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, 1, ctx->dStage, s );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
     IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
     if ( ( prerle != nullptr ) && ( n > 0 ) ) {

@@ -164,7 +164,12 @@ void launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, ui
 void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, uint32_t nblocks,
                        cudaStream_t stream );
 
-void launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks,
+/* K4b staging: one stream of TRAV_STAGE_CAP bytes per thread of the block's CTA, then u16 segment lengths */
+constexpr uint32_t TRAV_STAGE_CAP_SHIFT = 11;
+constexpr uint32_t TRAV_STAGE_CAP = 1U << TRAV_STAGE_CAP_SHIFT;
+constexpr uint64_t TRAV_STAGE_STRIDE = 1024ULL * TRAV_STAGE_CAP + 32768ULL;
+/* stage: device u8[nblocks][TRAV_STAGE_STRIDE] */
+void launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, uint8_t* stage,
                         cudaStream_t stream );
 
 void launchRleScan( const uint8_t* prerle, uint32_t* offsets, uint32_t* warpBase, BlockMeta* meta,
