@@ -18,6 +18,9 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 BUILD = PKG / "build"
 LIB = PKG / "libibz2_cuda.so"
+HOST_LIB = PKG / "libibz2_host.so"     # C++ readers + flat C entry points for the Python module
+CLI = PKG / "bin" / "ibzip2"           # command-line tool
+HOST_FLAGS = ["-std=c++17", "-O2", "-g", "-fPIC", "-Wall", "-Wextra", "-pthread", "-rdynamic"]
 
 CUDA_SOURCES = ["blockfinder.cu", "huffman_header.cu", "huffman_bits.cu", "huffman_careful.cu", "mtf.cu", "bwt_prepare.cu", "bwt_traverse.cu", "rle.cu", "crc.cu", "capi.cu"]
 NVCC_FLAGS = [
@@ -74,7 +77,33 @@ def build_native(force: bool = False, verbose: bool = False) -> Path:
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
+    build_host(force=force or bool(jobs))
     return LIB
+
+
+def build_host(force: bool = False) -> None:
+    """The host side above the C ABI: readers (header-only C++), their C wrapper and the CLI, compiled with g++."""
+    # the system g++ (dynamic libstdc++); $CXX in this image points at a toolchain that links libstdc++ statically, which
+    # gives the .so a second, uninitialised copy of the iostream locale machinery inside a Python process
+    cxx = os.environ.get("IBZ2_CXX") or ("/usr/bin/g++" if Path("/usr/bin/g++").exists() else shutil.which("g++") or "g++")
+    host = PKG / "host"
+    tools = PKG / "tools"
+    deps = list(host.glob("*.hpp")) + list(host.glob("*.cpp")) + list(tools.glob("*.cpp")) + [
+        PKG.parent / "include" / "ibz2_cuda.h", LIB, Path(__file__)]
+    link = ["-L" + str(PKG), "-libz2_cuda", "-Wl,-rpath,$ORIGIN"]
+    if force or _stale(HOST_LIB, deps):
+        cmd = [cxx, *HOST_FLAGS, "-shared", "-DIBZ2_NO_MAIN", str(host / "reader_capi.cpp"), str(tools / "ibzip2.cpp"),
+               "-o", str(HOST_LIB), *link]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"host library build failed:\n{res.stdout}\n{res.stderr}")
+    if force or _stale(CLI, deps):
+        CLI.parent.mkdir(exist_ok=True)
+        cmd = [cxx, *HOST_FLAGS, str(tools / "ibzip2.cpp"), "-o", str(CLI), "-L" + str(PKG), "-libz2_cuda",
+               "-Wl,-rpath,$ORIGIN/.."]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"ibzip2 CLI build failed:\n{res.stdout}\n{res.stderr}")
 
 
 if __name__ == "__main__":

@@ -1,0 +1,227 @@
+/*
+ * GpuDecoder -- C++ face of the C ABI in include/ibz2_cuda.h for ONE compressed file held in HBM.
+ * It stands where the reference has its BlockFinder thread and BlockFetcher thread pool
+ * (core/BlockFinder.hpp:36-219, core/BlockFetcher.hpp:244-317, indexed_bzip2/BZ2BlockFetcher.hpp:64-138):
+ *   blockOffsets()   <- BlockFinder::get( i ) for all i          (K1 over the whole file, once)
+ *   decode( ... )    <- BlockFetcher::get( offset ) for a batch  (K2..K6)
+ *   probeHeader()    <- BZ2BlockFetcher::readBlockHeader          (host, a few dozen bits)
+ * and turns per-block status codes back into the exceptions the reference throws at the same places.
+ * There is no CPU decode path: without a usable B200 the constructor throws.
+ */
+#pragma once
+
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <optional>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/ibz2_cuda.h"
+
+namespace ibz2host
+{
+/** Mirrors rapidgzip::BitReader::EndOfFileReached (core/BitReader.hpp:82): the CLI prints a dedicated message for it. */
+class EndOfFileReached : public std::exception
+{
+public:
+    [[nodiscard]] const char*
+    what() const noexcept override
+    {
+        return "End of file reached";
+    }
+};
+
+/** Rethrows what bzip2::Block would have thrown for this status (bzip2.hpp:479-907). */
+[[noreturn]] inline void
+throwForStatus( const ibz2_block_result& r )
+{
+    std::stringstream msg;
+    switch ( r.status ) {
+    case IBZ2_ST_BAD_MAGIC:
+        msg << "[BZip2 block header] invalid compressed magic at offset " << r.enc_offset_bits << " b";
+        throw std::domain_error( msg.str() );
+    case IBZ2_ST_RANDOMISED:
+        throw std::domain_error( "[BZip2 block header] deprecated isRandomized bit is not supported" );
+    case IBZ2_ST_ORIGPTR_RANGE:
+        msg << "[BZip2 block header] origPtr " << r.orig_ptr << " is larger than buffer size";
+        throw std::logic_error( msg.str() );
+    case IBZ2_ST_GROUP_COUNT:
+        throw std::logic_error( "[BZip2 block header] invalid number of Huffman trees" );
+    case IBZ2_ST_SELECTOR_COUNT:
+        throw std::logic_error( "[BZip2 block header] the number of selectors is invalid" );
+    case IBZ2_ST_SELECTOR_UNARY:
+        throw std::domain_error( "[BZip2 block header] could not find zero termination after group count bits" );
+    case IBZ2_ST_CODE_LENGTH:
+        throw std::logic_error( "[BZip2 block header] start_huffman_length is larger than the maximum code length" );
+    case IBZ2_ST_CODE_LENGTHS:
+        throw std::domain_error( "Constructing a Huffman coding from the given code length sequence failed!" );
+    case IBZ2_ST_SELECTOR_OVERRUN:
+        throw std::domain_error( "[BZip2 block data] selector out of maximum range" );
+    case IBZ2_ST_DBUF_OVERFLOW:
+        throw std::domain_error( "[BZip2 block data] dbufCount exceeds dbufSize" );
+    case IBZ2_ST_INVALID_CODE:
+        throw std::bad_optional_access();
+    case IBZ2_ST_ORIGPTR:
+        msg << "[BZip2 block data] origPtr error " << r.orig_ptr;
+        throw std::domain_error( msg.str() );
+    case IBZ2_ST_CRC:
+        msg << "Calculated CRC " << std::hex << r.calculated_crc << " for block mismatches " << r.expected_crc;
+        throw std::runtime_error( msg.str() );
+    case IBZ2_ST_EOF:
+        throw EndOfFileReached();
+    default:
+        msg << "Block decode failed with status " << r.status;
+        throw std::runtime_error( msg.str() );
+    }
+}
+
+class GpuDecoder
+{
+public:
+    explicit
+    GpuDecoder( int device = 0 )
+    {
+        const int rc = ibz2_create( device, &m_ctx );
+        if ( rc != IBZ2_OK ) {
+            throw std::runtime_error( std::string( "Cannot open the CUDA bzip2 decoder (there is no CPU fallback): " )
+                                      + ibz2_last_error( nullptr ) );
+        }
+    }
+
+    ~GpuDecoder()
+    {
+        if ( m_ctx != nullptr ) {
+            if ( m_deviceData != nullptr ) {
+                ibz2_device_free( m_ctx, m_deviceData );
+            }
+            if ( m_pinned != nullptr ) {
+                ibz2_host_free_pinned( m_ctx, m_pinned );
+            }
+            ibz2_destroy( m_ctx );
+        }
+    }
+
+    GpuDecoder( const GpuDecoder& ) = delete;
+    GpuDecoder& operator=( const GpuDecoder& ) = delete;
+
+    /** Copies the compressed file to the device; @p data may be released afterwards. */
+    void
+    upload( const uint8_t* data, size_t size )
+    {
+        m_size = size;
+        check( ibz2_device_alloc( m_ctx, size + 16, &m_deviceData ), "ibz2_device_alloc" );
+        if ( size > 0 ) {
+            check( ibz2_memcpy_h2d( m_ctx, m_deviceData, data, size ), "ibz2_memcpy_h2d" );
+        }
+    }
+
+    [[nodiscard]] size_t
+    size() const
+    {
+        return m_size;
+    }
+
+    /** All data-block magics, ascending (what rapidgzip::BlockFinder collects: block magic only). */
+    [[nodiscard]] std::vector<uint64_t>
+    findBlocks() const
+    {
+        std::vector<uint64_t> offsets( 1024 );
+        while ( true ) {
+            uint64_t count = 0;
+            const int rc = ibz2_find_magics( m_ctx, m_deviceData, m_size, IBZ2_MEM_DEVICE, 0, IBZ2_FIND_BLOCK,
+                                             offsets.data(), offsets.size(), &count );
+            if ( rc == IBZ2_E_CAPACITY ) {
+                offsets.resize( count );
+                continue;
+            }
+            check( rc, "ibz2_find_magics" );
+            offsets.resize( count );
+            return offsets;
+        }
+    }
+
+    /**
+     * Decodes the blocks at @p offsets (bit offsets of their magics) into @p out, back to back.
+     * @p results gets one entry per block; failing blocks keep their status and do not fail the call.
+     */
+    void
+    decode( const uint64_t* offsets, size_t count, std::vector<ibz2_block_result>& results, uint8_t*& out,
+            size_t& outSize )
+    {
+        results.assign( count, ibz2_block_result{} );
+        outSize = 0;
+        out = nullptr;
+        if ( count == 0 ) {
+            return;
+        }
+        size_t capacity = count * 1000000ULL + 65536ULL;
+        for ( int attempt = 0; attempt < 2; ++attempt ) {
+            ensurePinned( capacity );
+            uint64_t total = 0;
+            check( ibz2_decode_blocks( m_ctx, m_deviceData, m_size, IBZ2_MEM_DEVICE, offsets, count, m_pinned,
+                                       m_pinnedCapacity, IBZ2_MEM_HOST, results.data(), &total ),
+                   "ibz2_decode_blocks" );
+            const bool overflow = std::any_of( results.begin(), results.end(), [] ( const ibz2_block_result& r ) {
+                return r.status == IBZ2_ST_OUTPUT_CAPACITY;
+            } );
+            if ( !overflow ) {
+                outSize = total;
+                out = static_cast<uint8_t*>( m_pinned );
+                return;
+            }
+            capacity = total + 65536ULL;   /* RLE1 can expand a block 51-fold: now the sizes are known */
+        }
+        throw std::runtime_error( "Decoded block sizes changed between two decodes of the same blocks" );
+    }
+
+    /** BZ2BlockFetcher::readBlockHeader (BZ2BlockFetcher.hpp:64-82) on the host copy of the file. */
+    [[nodiscard]] static ibz2_block_result
+    probeHeader( const uint8_t* data, size_t size, uint64_t bitOffset )
+    {
+        ibz2_block_result result{};
+        ibz2_read_block_header( data, size, bitOffset, &result );
+        return result;
+    }
+
+    [[nodiscard]] ibz2_timings
+    timings() const
+    {
+        ibz2_timings t{};
+        ibz2_get_timings( m_ctx, &t );
+        return t;
+    }
+
+private:
+    void
+    check( int rc, const char* what ) const
+    {
+        if ( rc != IBZ2_OK ) {
+            throw std::runtime_error( std::string( what ) + " failed: " + ibz2_last_error( m_ctx ) );
+        }
+    }
+
+    void
+    ensurePinned( size_t capacity )
+    {
+        if ( capacity <= m_pinnedCapacity ) {
+            return;
+        }
+        if ( m_pinned != nullptr ) {
+            ibz2_host_free_pinned( m_ctx, m_pinned );
+            m_pinned = nullptr;
+            m_pinnedCapacity = 0;
+        }
+        check( ibz2_host_alloc_pinned( m_ctx, capacity, &m_pinned ), "ibz2_host_alloc_pinned" );
+        m_pinnedCapacity = capacity;
+    }
+
+    ibz2_ctx* m_ctx{ nullptr };
+    void* m_deviceData{ nullptr };
+    size_t m_size{ 0 };
+    void* m_pinned{ nullptr };
+    size_t m_pinnedCapacity{ 0 };
+};
+}  // namespace ibz2host

@@ -1,0 +1,349 @@
+/*
+ * ParallelBZ2Reader -- seekable reader over a bzip2 file whose blocks are decoded on a B200 (include/ibz2_cuda.h).
+ * Drop-in for indexed_bzip2::ParallelBZ2Reader (indexed_bzip2/ParallelBZ2Reader.hpp:39-498): same constructors,
+ * methods, positions, end-of-file behaviour, exceptions and -- bit for bit -- the same block map.
+ *
+ * Where the reference has a block-finder thread and a pool of decode threads with prefetching, this reader has
+ *   - the whole compressed file in HBM (uploaded on first use),
+ *   - ONE finder pass over it (K1) that yields every data-block offset,
+ *   - batches: when a read needs a block that is not decoded yet, that block and the following ones are decoded in
+ *     one ibz2_decode_blocks call.  Sequential reading doubles the batch up to MAX_BATCH_BLOCKS (the GPU wants
+ *     thousands of blocks in flight); a seek resets it to a few blocks so that random access stays cheap.
+ * The block map is filled in file order exactly as ParallelBZ2Reader.hpp:191-238 does it, including the probing for
+ * end-of-stream blocks and the "trailing garbage" cut-off; it may only run AHEAD of the reference's (a decoded batch is
+ * entered at once), never differ from it.
+ * Like the reference, an object must not be used from several threads at once.
+ */
+#pragma once
+
+#include <algorithm>
+#include <iostream>
+#include <memory>
+
+#include "BlockIndex.hpp"
+#include "BZ2ReaderInterface.hpp"
+#include "BlockSource.hpp"
+
+namespace ibz2host
+{
+class ParallelBZ2Reader final : public BZ2ReaderInterface
+{
+public:
+    explicit
+    ParallelBZ2Reader( UniqueFileReader fileReader, size_t parallelization = 0, int device = 0 ) :
+        m_source( requireSeekable( std::move( fileReader ) ), parallelization, device )
+    {}
+
+    explicit
+    ParallelBZ2Reader( int fileDescriptor, size_t parallelization = 0 ) :
+        ParallelBZ2Reader( std::make_unique<StandardFileReader>( fileDescriptor ), parallelization )
+    {}
+
+    explicit
+    ParallelBZ2Reader( const std::string& filePath, size_t parallelization = 0 ) :
+        ParallelBZ2Reader( std::make_unique<StandardFileReader>( filePath ), parallelization )
+    {}
+
+    /* FileReader overrides */
+
+    [[nodiscard]] int
+    fileno() const
+    {
+        throw std::logic_error( "This is a virtual file object, which has no corresponding file descriptor!" );
+    }
+
+    [[nodiscard]] bool seekable() const override { return true; }
+
+    void
+    close() override
+    {
+        m_source.close();
+        m_closed = true;
+    }
+
+    [[nodiscard]] bool closed() const override { return m_closed; }
+    [[nodiscard]] bool eof() const override { return m_atEndOfFile; }
+
+    [[nodiscard]] bool
+    fail() const
+    {
+        throw std::logic_error( "Not implemented!" );
+    }
+
+    [[nodiscard]] size_t
+    tell() const override
+    {
+        if ( m_atEndOfFile ) {
+            const auto fileSize = size();
+            if ( !fileSize ) {
+                throw std::logic_error( "When the file end has been reached, the block map should have been finalized "
+                                        "and the file size should be available!" );
+            }
+            return *fileSize;
+        }
+        return m_currentPosition;
+    }
+
+    [[nodiscard]] std::optional<size_t>
+    size() const override
+    {
+        if ( !m_index.finished() ) {
+            return std::nullopt;
+        }
+        return m_index.back().second;
+    }
+
+    void
+    clearerr()
+    {
+        m_atEndOfFile = false;
+        throw std::invalid_argument( "Not fully tested!" );
+    }
+
+    /* BZ2ReaderInterface overrides */
+
+    using BZ2ReaderInterface::read;
+
+    size_t
+    read( const WriteFunctor& writeFunctor,
+          const size_t        nBytesToRead = std::numeric_limits<size_t>::max() ) override
+    {
+        if ( closed() ) {
+            throw std::invalid_argument( "You may not call read on closed ParallelBZ2Reader!" );
+        }
+        if ( eof() || ( nBytesToRead == 0 ) ) {
+            return 0;
+        }
+
+        size_t nBytesDecoded = 0;
+        while ( ( nBytesDecoded < nBytesToRead ) && !eof() ) {
+            BlockSource::Block block;
+
+            auto span = m_index.locate( m_currentPosition );
+            if ( !span.contains( m_currentPosition ) ) {
+                /* a block that has not been entered into the block map yet (ParallelBZ2Reader.hpp:191-244) */
+                const auto dataBlockIndex = m_index.dataBlockCount();
+                if ( dataBlockIndex >= m_source.finderCount() ) {
+                    m_index.finish();
+                    m_atEndOfFile = true;
+                    break;
+                }
+                const auto encodedOffsetInBits = m_source.finderOffsets()[dataBlockIndex];
+                block = m_source.fetch( encodedOffsetInBits, dataBlockIndex );
+                m_index.append( block.result->enc_offset_bits, block.result->enc_size_bits, block.result->out_size );
+                probeAfter( *block.result );
+
+                span = m_index.locate( m_currentPosition );
+                if ( !span.contains( m_currentPosition ) ) {
+                    continue;
+                }
+            } else {
+                block = m_source.fetch( span.encodedOffsetInBits );
+            }
+            const uint8_t* const blockBytes = block.data;
+            const size_t blockSize = block.result->out_size;
+
+            const auto offsetInBlock = m_currentPosition - span.decodedOffsetInBytes;
+            if ( offsetInBlock >= blockSize ) {
+                throw std::logic_error( "Block does not contain the requested offset even though it "
+                                        "shouldn't be according to block map!" );
+            }
+            const auto nBytesToDecode = std::min( blockSize - offsetInBlock, nBytesToRead - nBytesDecoded );
+            if ( writeFunctor ) {
+                writeFunctor( blockBytes + offsetInBlock, nBytesToDecode );
+            }
+            nBytesDecoded += nBytesToDecode;
+            m_currentPosition += nBytesToDecode;
+        }
+        return nBytesDecoded;
+    }
+
+    size_t
+    seek( long long int offset, int origin = SEEK_SET ) override
+    {
+        if ( closed() ) {
+            throw std::invalid_argument( "You may not call seek on closed ParallelBZ2Reader!" );
+        }
+        if ( ( origin == SEEK_END ) && !m_index.finished() ) {
+            read();   /* size() needs the complete block map */
+        }
+        long long int target = offset;
+        if ( origin == SEEK_CUR ) {
+            target += static_cast<long long int>( tell() );
+        } else if ( origin == SEEK_END ) {
+            target += static_cast<long long int>( size().value_or( 0 ) );
+        }
+        const auto positiveOffset = static_cast<size_t>( std::max( 0LL, target ) );
+
+        if ( positiveOffset == tell() ) {
+            return positiveOffset;
+        }
+        m_source.noteSeek();   /* random access: start again with small batches */
+
+        if ( positiveOffset < tell() ) {
+            m_atEndOfFile = false;
+            m_currentPosition = positiveOffset;
+            return positiveOffset;
+        }
+
+        const auto span = m_index.locate( positiveOffset );
+        if ( span.valid && ( positiveOffset < span.decodedOffsetInBytes ) ) {
+            throw std::logic_error( "Block map returned unwanted block!" );
+        }
+        if ( span.contains( positiveOffset ) ) {
+            m_atEndOfFile = false;
+            m_currentPosition = positiveOffset;
+            return tell();
+        }
+        if ( m_index.finished() ) {
+            m_atEndOfFile = true;
+            m_currentPosition = m_index.back().second;
+            return tell();
+        }
+
+        /* beyond what is known: decode forward without a sink (ParallelBZ2Reader.hpp:318-324) */
+        m_atEndOfFile = false;
+        m_currentPosition = span.decodedOffsetInBytes + span.decodedSizeInBytes;
+        read( -1, nullptr, positiveOffset - tell() );
+        return tell();
+    }
+
+    /* BZip2 specific methods */
+
+    [[nodiscard]] bool blockOffsetsComplete() const override { return m_index.finished(); }
+
+    [[nodiscard]] std::map<size_t, size_t>
+    blockOffsets() override
+    {
+        if ( !m_index.finished() ) {
+            read();
+            if ( !m_index.finished() ) {
+                throw std::logic_error( "Reading everything should have finalized the block map!" );
+            }
+        }
+        return m_index.offsets();
+    }
+
+    [[nodiscard]] std::map<size_t, size_t>
+    availableBlockOffsets() const override
+    {
+        return m_index.offsets();
+    }
+
+    void
+    setBlockOffsets( std::map<size_t, size_t> offsets ) override
+    {
+        if ( offsets.empty() ) {
+            throw std::invalid_argument( "May not clear offsets. Construct a new ParallelBZ2Reader instead!" );
+        }
+        /* entries without data are end-of-stream blocks, the last one always is (ParallelBZ2Reader.hpp:463-472) */
+        std::vector<uint64_t> dataBlocks;
+        for ( auto it = offsets.begin(), nit = std::next( offsets.begin() ); nit != offsets.end(); ++it, ++nit ) {
+            if ( it->second != nit->second ) {
+                dataBlocks.push_back( it->first );
+            }
+        }
+        m_source.setFinderOffsets( std::move( dataBlocks ) );
+        if ( offsets.size() < 2 ) {
+            throw std::invalid_argument( "Block offset map must contain at least one valid block and one EOS block!" );
+        }
+        m_index.assign( offsets );
+    }
+
+    [[nodiscard]] size_t
+    tellCompressed() const override
+    {
+        const auto span = m_index.locate( m_currentPosition );
+        if ( span.contains( m_currentPosition ) ) {
+            return span.encodedOffsetInBits;
+        }
+        return m_index.back().first;
+    }
+
+    /** The reference stops its thread pools here; this reader has none, so only the decoded batch is dropped. */
+    void
+    joinThreads()
+    {
+        m_source.dropBatch();
+    }
+
+    /** New next to the reference: the index as the text the CLI's -L writes, one "bits,bytes" pair per line. */
+    void
+    exportIndex( std::ostream& out )
+    {
+        for ( const auto& [bits, bytes] : blockOffsets() ) {
+            out << bits << "," << bytes << "\n";
+        }
+    }
+
+    void
+    importIndex( std::istream& in )
+    {
+        std::map<size_t, size_t> offsets;
+        std::string line;
+        while ( std::getline( in, line ) ) {
+            if ( line.empty() ) {
+                continue;
+            }
+            const auto comma = line.find( ',' );
+            if ( comma == std::string::npos ) {
+                throw std::invalid_argument( "Index lines must look like <bits>,<bytes>" );
+            }
+            offsets.emplace( std::stoull( line.substr( 0, comma ) ), std::stoull( line.substr( comma + 1 ) ) );
+        }
+        setBlockOffsets( std::move( offsets ) );
+    }
+
+    [[nodiscard]] ibz2_timings
+    lastTimings()
+    {
+        return m_source.gpu().timings();
+    }
+
+private:
+    static UniqueFileReader
+    requireSeekable( UniqueFileReader fileReader )
+    {
+        if ( !fileReader || !fileReader->seekable() ) {
+            throw std::invalid_argument( "Parallel BZ2 Reader will not work on non-seekable input like stdin (yet)!" );
+        }
+        return fileReader;
+    }
+
+    /** ParallelBZ2Reader.hpp:203-238: an end-of-stream block after a data block gets its own entry. */
+    void
+    probeAfter( const ibz2_block_result& block )
+    {
+        if ( block.is_eof != 0 ) {
+            return;
+        }
+        const auto next = m_source.probeHeader( block.enc_offset_bits + block.enc_size_bits );
+        if ( next.status == IBZ2_ST_EOF ) {
+            throw EndOfFileReached();
+        }
+        if ( next.status != IBZ2_ST_OK ) {
+            throwForStatus( next );
+        }
+        if ( next.is_eos == 0 ) {
+            return;
+        }
+        m_index.append( next.enc_offset_bits, next.enc_size_bits, 0 );
+        const auto nextStreamOffsetInBits = next.enc_offset_bits + next.enc_size_bits;
+        if ( nextStreamOffsetInBits < m_source.fileSizeInBits() ) {
+            uint64_t position = nextStreamOffsetInBits;
+            if ( ibz2_read_stream_header( m_source.fileData(), m_source.fileSize(), &position ) <= 0 ) {
+                std::cerr << "[Warning] Trailing garbage after EOF ignored!\n";
+                /* valid blocks behind a gap are not read any more: truncate the finder's list */
+                m_source.truncateFinder( m_index.dataBlockCount() );
+            }
+        }
+    }
+
+    BlockSource m_source;
+    BlockIndex m_index;
+
+    size_t m_currentPosition{ 0 };
+    bool m_atEndOfFile{ false };
+    bool m_closed{ false };
+};
+}  // namespace ibz2host

@@ -1,0 +1,345 @@
+/*
+ * reader_capi.cpp -- flat C entry points over ParallelBZ2Reader / BZ2Reader for FFI callers (the Python module
+ * indexed_bzip2_b200/__init__.py binds them with ctypes, the way the reference's Cython wrapper binds the C++ classes,
+ * python/indexed_bzip2/indexed_bzip2.pyx:26-67).  Exceptions are caught at this boundary; the kind of the last one
+ * is kept so that the caller can raise the exception type Cython's "except +" would have produced.
+ */
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <new>
+#include <optional>
+#include <string>
+
+#include "BZ2Reader.hpp"
+#include "ParallelBZ2Reader.hpp"
+
+using namespace ibz2host;
+
+int ibzip2CLI( int argc, char** argv );   /* tools/ibzip2.cpp */
+
+#include <csignal>
+#include <execinfo.h>
+namespace
+{
+/* IBZ2_DEBUG_SEGV=1: print a native backtrace when the process dies inside this library */
+void
+segvHandler( int sig )
+{
+    void* frames[64];
+    const int n = backtrace( frames, 64 );
+    backtrace_symbols_fd( frames, n, 2 );
+    signal( sig, SIG_DFL );
+    raise( sig );
+}
+
+struct SegvInstaller
+{
+    SegvInstaller()
+    {
+        if ( getenv( "IBZ2_DEBUG_SEGV" ) != nullptr ) {
+            signal( SIGSEGV, segvHandler );
+        }
+    }
+} g_segvInstaller;
+}  // namespace
+
+extern "C" {
+enum ibz2r_error_kind {
+    IBZ2R_NONE = 0,
+    IBZ2R_INVALID_ARGUMENT = 1,   /* ValueError */
+    IBZ2R_DOMAIN_ERROR = 2,       /* ValueError */
+    IBZ2R_OUT_OF_RANGE = 3,       /* IndexError */
+    IBZ2R_RUNTIME_ERROR = 4,      /* RuntimeError */
+    IBZ2R_LOGIC_ERROR = 5,        /* RuntimeError */
+    IBZ2R_END_OF_FILE = 6,        /* RuntimeError (EndOfFileReached derives from std::exception) */
+    IBZ2R_BAD_ALLOC = 7,          /* MemoryError */
+    IBZ2R_OTHER = 8               /* RuntimeError */
+};
+}
+
+struct ibz2_reader
+{
+    std::unique_ptr<BZ2ReaderInterface> reader;
+    ParallelBZ2Reader* parallel{ nullptr };
+    std::string lastError;
+    int lastKind{ IBZ2R_NONE };
+};
+
+namespace
+{
+thread_local std::string g_openError;
+thread_local int g_openKind = IBZ2R_NONE;
+
+template<typename Function>
+long long
+guarded( std::string& message, int& kind, Function&& function )
+{
+    kind = IBZ2R_NONE;
+    message.clear();
+    try {
+        return function();
+    } catch ( const EndOfFileReached& e ) {
+        kind = IBZ2R_END_OF_FILE;
+        message = "Unexpected end of file. Truncated or invalid bzip2?";
+    } catch ( const std::invalid_argument& e ) {
+        kind = IBZ2R_INVALID_ARGUMENT;
+        message = e.what();
+    } catch ( const std::domain_error& e ) {
+        kind = IBZ2R_DOMAIN_ERROR;
+        message = e.what();
+    } catch ( const std::out_of_range& e ) {
+        kind = IBZ2R_OUT_OF_RANGE;
+        message = e.what();
+    } catch ( const std::logic_error& e ) {
+        kind = IBZ2R_LOGIC_ERROR;
+        message = e.what();
+    } catch ( const std::bad_alloc& e ) {
+        kind = IBZ2R_BAD_ALLOC;
+        message = e.what();
+    } catch ( const std::runtime_error& e ) {
+        kind = IBZ2R_RUNTIME_ERROR;
+        message = e.what();
+    } catch ( const std::exception& e ) {
+        kind = IBZ2R_OTHER;
+        message = e.what();
+    } catch ( ... ) {
+        kind = IBZ2R_OTHER;
+        message = "unknown exception";
+    }
+    return -1;
+}
+
+ibz2_reader*
+wrap( UniqueFileReader fileReader, size_t parallelization )
+{
+    auto handle = std::make_unique<ibz2_reader>();
+    /* parallelization == 1 selects the serial class, anything else the parallel one (indexed_bzip2.pyx:295-296) */
+    if ( parallelization == 1 ) {
+        handle->reader = std::make_unique<BZ2Reader>( std::move( fileReader ) );
+    } else {
+        auto parallel = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), parallelization );
+        handle->parallel = parallel.get();
+        handle->reader = std::move( parallel );
+    }
+    return handle.release();
+}
+
+template<typename Function>
+ibz2_reader*
+openWith( Function&& function )
+{
+    ibz2_reader* result = nullptr;
+    guarded( g_openError, g_openKind, [&] () { result = function(); return 0LL; } );
+    return result;
+}
+}  // namespace
+
+extern "C" {
+ibz2_reader*
+ibz2r_open_path( const char* path, size_t parallelization )
+{
+    return openWith( [&] () { return wrap( std::make_unique<StandardFileReader>( std::string( path ) ), parallelization ); } );
+}
+
+ibz2_reader*
+ibz2r_open_fd( int fd, size_t parallelization )
+{
+    return openWith( [&] () { return wrap( std::make_unique<StandardFileReader>( fd ), parallelization ); } );
+}
+
+ibz2_reader*
+ibz2r_open_memory( const void* data, size_t size, size_t parallelization )
+{
+    return openWith( [&] () { return wrap( std::make_unique<MemoryFileReader>( data, size ), parallelization ); } );
+}
+
+void
+ibz2r_destroy( ibz2_reader* r )
+{
+    delete r;
+}
+
+const char*
+ibz2r_last_error( const ibz2_reader* r )
+{
+    return r != nullptr ? r->lastError.c_str() : g_openError.c_str();
+}
+
+int
+ibz2r_last_error_kind( const ibz2_reader* r )
+{
+    return r != nullptr ? r->lastKind : g_openKind;
+}
+
+long long
+ibz2r_read( ibz2_reader* r, void* buffer, size_t size )
+{
+    return guarded( r->lastError, r->lastKind, [&] () {
+        return static_cast<long long>( r->reader->read( -1, static_cast<char*>( buffer ), size ) );
+    } );
+}
+
+long long
+ibz2r_read_to_fd( ibz2_reader* r, int fd, size_t size )
+{
+    return guarded( r->lastError, r->lastKind, [&] () {
+        return static_cast<long long>( r->reader->read( fd, nullptr, size ) );
+    } );
+}
+
+long long
+ibz2r_seek( ibz2_reader* r, long long offset, int whence )
+{
+    return guarded( r->lastError, r->lastKind, [&] () { return static_cast<long long>( r->reader->seek( offset, whence ) ); } );
+}
+
+long long
+ibz2r_tell( ibz2_reader* r )
+{
+    return guarded( r->lastError, r->lastKind, [&] () { return static_cast<long long>( r->reader->tell() ); } );
+}
+
+/* the decoded size; -1 while the block map is incomplete unless `force` asks to decode to the end first */
+long long
+ibz2r_size( ibz2_reader* r, int force )
+{
+    return guarded( r->lastError, r->lastKind, [&] () {
+        if ( !r->reader->size() ) {
+            if ( force == 0 ) {
+                return -1LL;
+            }
+            const auto here = r->reader->tell();
+            r->reader->seek( 0, SEEK_END );
+            r->reader->seek( static_cast<long long>( here ), SEEK_SET );
+        }
+        return static_cast<long long>( r->reader->size().value_or( 0 ) );
+    } );
+}
+
+long long
+ibz2r_tell_compressed( ibz2_reader* r )
+{
+    return guarded( r->lastError, r->lastKind, [&] () { return static_cast<long long>( r->reader->tellCompressed() ); } );
+}
+
+int
+ibz2r_eof( ibz2_reader* r )
+{
+    return r->reader->eof() ? 1 : 0;
+}
+
+int
+ibz2r_closed( ibz2_reader* r )
+{
+    return r->reader->closed() ? 1 : 0;
+}
+
+int
+ibz2r_close( ibz2_reader* r )
+{
+    return static_cast<int>( guarded( r->lastError, r->lastKind, [&] () { r->reader->close(); return 0LL; } ) );
+}
+
+int
+ibz2r_block_offsets_complete( ibz2_reader* r )
+{
+    return r->reader->blockOffsetsComplete() ? 1 : 0;
+}
+
+/* pairs: ( encoded bits, decoded bytes ); returns the number of entries (which may exceed capacity), -1 on error */
+long long
+ibz2r_block_offsets( ibz2_reader* r, uint64_t* pairs, size_t capacity, int availableOnly )
+{
+    return guarded( r->lastError, r->lastKind, [&] () {
+        const auto offsets = availableOnly != 0 ? r->reader->availableBlockOffsets() : r->reader->blockOffsets();
+        size_t i = 0;
+        for ( const auto& [bits, bytes] : offsets ) {
+            if ( i < capacity ) {
+                pairs[2 * i] = bits;
+                pairs[2 * i + 1] = bytes;
+            }
+            ++i;
+        }
+        return static_cast<long long>( offsets.size() );
+    } );
+}
+
+int
+ibz2r_set_block_offsets( ibz2_reader* r, const uint64_t* pairs, size_t count )
+{
+    return static_cast<int>( guarded( r->lastError, r->lastKind, [&] () {
+        std::map<size_t, size_t> offsets;
+        for ( size_t i = 0; i < count; ++i ) {
+            offsets.emplace( pairs[2 * i], pairs[2 * i + 1] );
+        }
+        r->reader->setBlockOffsets( std::move( offsets ) );
+        return 0LL;
+    } ) );
+}
+
+int
+ibz2r_join_threads( ibz2_reader* r )
+{
+    if ( r->parallel != nullptr ) {
+        r->parallel->joinThreads();
+    }
+    return 0;
+}
+
+/* ---- test hook (no GPU): drives a BlockIndex the way the readers do, so that the block-map rules can be checked
+ * against the reference's golden maps on a machine without a GPU.
+ * triples: ( encoded offset, encoded size, decoded size ) per append; returns the number of map entries, -1 on error. */
+long long
+ibz2r_index_simulate( const uint64_t* triples, size_t count, int finish, uint64_t* pairs, size_t capacity,
+                      uint64_t probe, uint64_t* located )
+{
+    std::string message;
+    int kind = IBZ2R_NONE;
+    return guarded( message, kind, [&] () {
+        BlockIndex index;
+        for ( size_t i = 0; i < count; ++i ) {
+            index.append( triples[3 * i], triples[3 * i + 1], triples[3 * i + 2] );
+        }
+        if ( finish != 0 ) {
+            index.finish();
+        }
+        const auto offsets = index.offsets();
+        size_t i = 0;
+        for ( const auto& [bits, bytes] : offsets ) {
+            if ( i < capacity ) {
+                pairs[2 * i] = bits;
+                pairs[2 * i + 1] = bytes;
+            }
+            ++i;
+        }
+        if ( located != nullptr ) {
+            const auto span = index.locate( probe );
+            located[0] = span.valid ? 1 : 0;
+            located[1] = span.encodedOffsetInBits;
+            located[2] = span.decodedOffsetInBytes;
+            located[3] = span.decodedSizeInBytes;
+            located[4] = index.dataBlockCount();
+        }
+        return static_cast<long long>( offsets.size() );
+    } );
+}
+
+/* the reference's Python cli() calls ibzip2CLI with sys.argv (indexed_bzip2.pyx:343-363) */
+int
+ibz2r_cli( int argc, char** argv )
+{
+    std::string message;
+    int kind = IBZ2R_NONE;
+    const auto rc = guarded( message, kind, [&] () { return static_cast<long long>( ibzip2CLI( argc, argv ) ); } );
+    if ( kind == IBZ2R_END_OF_FILE ) {
+        std::cerr << "Unexpected end of file. Truncated or invalid bzip2?\n";
+        return 1;
+    }
+    if ( kind != IBZ2R_NONE ) {
+        std::cerr << "Caught exception: " << message << "\n";
+        return 1;
+    }
+    return static_cast<int>( rc );
+}
+}  // extern "C"

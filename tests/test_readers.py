@@ -1,0 +1,257 @@
+"""Drop-in surface tests: the C++ readers (indexed_bzip2_b200/host), the Python module and the ibzip2 CLI against the
+golden outputs of the compiled, unmodified reference (tests/golden/golden.json: decoded bytes, blockOffsets() of
+ParallelBZ2Reader and BZ2Reader, `ibzip2 -l`, CLI exit status / stderr) and against the CPU oracle.
+
+The GPU tests read like the reference's own testParallelBZ2Reader.cpp / testBZ2Reader.cpp / testPythonWrappers.py:
+decode, compare bytes; seek around, compare slices; export the index, import it into a fresh reader, read again.
+"""
+import ctypes as C
+import hashlib
+import io
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import _oracle as orc
+import indexed_bzip2_b200 as ibz2
+
+ROOT = orc.ROOT
+GOLDEN = json.loads((ROOT / "tests" / "golden" / "golden.json").read_text())
+ALL = sorted(GOLDEN)
+VALID = sorted(k for k, v in GOLDEN.items() if v["parallel"]["rc"] == 0)
+CLI = ROOT / "indexed_bzip2_b200" / "bin" / "ibzip2"
+
+
+def path(name):
+    return str(ROOT / "tests" / "golden" / "cases" / f"{name}.bz2")
+
+
+def sha(data):
+    return hashlib.sha256(data).hexdigest()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# host logic without a GPU
+# ---------------------------------------------------------------------------------------------------------------
+
+def simulate_index(triples, finish=True, probe=0):
+    lib = ibz2._load()
+    lib.ibz2r_index_simulate.restype = C.c_longlong
+    lib.ibz2r_index_simulate.argtypes = [C.POINTER(C.c_uint64), C.c_size_t, C.c_int, C.POINTER(C.c_uint64), C.c_size_t,
+                                         C.c_uint64, C.POINTER(C.c_uint64)]
+    flat = (C.c_uint64 * max(1, 3 * len(triples)))(*[x for t in triples for x in t])
+    pairs = (C.c_uint64 * 4096)()
+    located = (C.c_uint64 * 5)()
+    count = lib.ibz2r_index_simulate(flat, len(triples), 1 if finish else 0, pairs, 2048, probe, located)
+    assert count >= 0
+    return [[pairs[2 * i], pairs[2 * i + 1]] for i in range(count)], list(located)
+
+
+@pytest.mark.parametrize("name", VALID)
+def test_block_index_reproduces_reference_maps(name):
+    """Feeding the blocks of the reference's own ParallelBZ2Reader map back through BlockIndex (append per block and
+    EOS, then finish) must give that map again, sentinel included (core/BlockMap.hpp:69-93,174-198)."""
+    want = GOLDEN[name]["parallel"]["offsets"]
+    entries = want[:-1] if len(want) > 1 else []
+    triples = [(bits, want[i + 1][0] - bits, want[i + 1][1] - nbytes) for i, (bits, nbytes) in enumerate(entries)]
+    got, _ = simulate_index(triples)
+    assert got == want
+    unfinished, located = simulate_index(triples, finish=False)
+    assert unfinished == entries
+    assert located[4] == sum(1 for t in triples if t[2] > 0)   # dataBlockCount() while the map is still growing
+
+
+def test_block_index_locate_prefers_the_block_after_an_eos():
+    # base64-32KiB | 1B | empty | base64-32KiB (Appendix B of SURVEY.md)
+    triples = [(32, 199677, 32768), (199709, 115, 0), (199824, 179, 1), (200003, 117, 0), (200232, 199677, 32768),
+               (399909, 83, 0)]
+    offsets, located = simulate_index(triples, probe=32768)
+    assert offsets == [[32, 0], [199709, 32768], [199824, 32768], [200003, 32769], [200232, 32769], [399909, 65537],
+                       [399992, 65537]]
+    assert located[:4] == [1, 199824, 32768, 1]   # the 1-byte block, not the EOS entry that starts at the same byte
+    _, located = simulate_index(triples, probe=65537)
+    assert located[3] == 0                        # nothing holds the byte one past the end
+    assert simulate_index([], finish=True)[0] == [[0, 0]]   # empty file (BlockMap.hpp:184-187)
+
+
+def test_host_library_exports_the_reader_entry_points():
+    lib = ibz2._load()
+    for name in ("ibz2r_open_path", "ibz2r_open_fd", "ibz2r_open_memory", "ibz2r_destroy", "ibz2r_read", "ibz2r_read_to_fd",
+                 "ibz2r_seek", "ibz2r_tell", "ibz2r_size", "ibz2r_tell_compressed", "ibz2r_eof", "ibz2r_closed",
+                 "ibz2r_close", "ibz2r_block_offsets_complete", "ibz2r_block_offsets", "ibz2r_set_block_offsets",
+                 "ibz2r_join_threads", "ibz2r_cli", "ibz2r_last_error", "ibz2r_last_error_kind"):
+        assert hasattr(lib, name), name
+    assert ibz2.__version__ == "1.7.0"
+    with pytest.raises(TypeError):
+        ibz2.open(path("ref-1B"), parallelization="4")
+
+
+def test_cli_version_and_help_need_no_gpu():
+    out = subprocess.run([str(CLI), "--version"], capture_output=True, text=True)
+    assert out.returncode == 0
+    assert out.stdout == "ibzip2, CLI to the indexed and seekable bzip2 decoding library indexed-bzip2 version 1.7.0.\n"
+    assert subprocess.run([str(CLI), "-h"], capture_output=True).returncode == 0
+    out = subprocess.run([str(CLI)], capture_output=True, text=True, stdin=subprocess.DEVNULL)
+    assert out.returncode == 1
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# on the B200
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ALL)
+def test_parallel_reader_matches_reference(name):
+    want = GOLDEN[name]["parallel"]
+    f = ibz2.open(path(name), parallelization=4)
+    if want["rc"] != 0:
+        with pytest.raises(Exception) as info:
+            f.read()
+        if want["error"] != "std::exception":
+            assert want["error"] in str(info.value)
+        else:
+            assert "end of file" in str(info.value).lower()
+        return
+    data = f.read()
+    assert len(data) == want["size"] and sha(data) == want["sha256"]
+    assert f.block_offsets_complete()
+    assert [list(kv) for kv in sorted(f.block_offsets().items())] == want["offsets"]
+    assert f.size() == want["size"] and f.tell() == want["size"]
+    oracle = orc.parallel_reader(open(path(name), "rb").read())
+    assert data == oracle.data
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ALL)
+def test_serial_reader_matches_reference(name):
+    want = GOLDEN[name]["serial"]
+    f = ibz2.open(path(name), parallelization=1)
+    if want["rc"] != 0:
+        with pytest.raises(Exception) as info:
+            f.read()
+        if want["error"] != "std::exception":
+            assert want["error"] in str(info.value)
+        return
+    data = f.read()
+    assert len(data) == want["size"] and sha(data) == want["sha256"]
+    assert [list(kv) for kv in sorted(f.block_offsets().items())] == want["offsets"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["text-450k-l1", "multistream-b64-1B-empty-b64", "pbzip2-style-5-streams", "longruns-3M-l1"])
+@pytest.mark.parametrize("parallelization", [1, 4])
+def test_seek_and_partial_reads(name, parallelization):
+    raw = orc.parallel_reader(open(path(name), "rb").read()).data
+    rng = np.random.default_rng(5)
+    f = ibz2.open(path(name), parallelization=parallelization)
+    assert f.seekable() and f.readable() and f.tell() == 0
+    assert f.read(10) == raw[:10] and f.tell() == 10
+    for _ in range(25):
+        offset = int(rng.integers(0, len(raw)))
+        size = int(rng.integers(1, 70000))
+        assert f.seek(offset) == offset
+        assert f.read(size) == raw[offset:offset + size]
+    assert f.seek(0, io.SEEK_END) == len(raw) and f.read(1) == b""
+    assert f.seek(-5, io.SEEK_END) == len(raw) - 5 and f.read() == raw[-5:]
+    assert f.seek(3) == 3 and f.seek(4, io.SEEK_CUR) == 7 and f.read(3) == raw[7:10]
+    assert f.seek(len(raw) + 1000) == len(raw)
+    f.close()
+    assert f.closed
+
+
+@pytest.mark.gpu
+def test_index_export_import_roundtrip(tmp_path):
+    name = "pbzip2-style-5-streams"
+    raw = orc.parallel_reader(open(path(name), "rb").read()).data
+    first = ibz2.open(path(name), parallelization=4)
+    offsets = first.block_offsets()
+    index_file = tmp_path / "index.csv"
+    first.export_index(index_file)
+    assert index_file.read_text() == "".join(f"{b},{n}\n" for b, n in GOLDEN[name]["parallel"]["offsets"])
+
+    for flavour in (GOLDEN[name]["parallel"]["offsets"], GOLDEN[name]["serial"]["offsets"]):
+        second = ibz2.open(path(name), parallelization=4)
+        second.set_block_offsets({b: n for b, n in flavour})   # either map flavour is accepted (ParallelBZ2Reader.hpp:463-472)
+        assert second.block_offsets_complete()
+        assert second.size() == len(raw)
+        rng = np.random.default_rng(7)
+        for _ in range(20):
+            offset = int(rng.integers(0, len(raw)))
+            second.seek(offset)
+            assert second.read(4096) == raw[offset:offset + 4096]
+    third = ibz2.open(path(name), parallelization=4)
+    third.import_index(index_file)
+    assert third.block_offsets() == offsets
+    third.seek(len(raw) // 2)
+    assert third.read() == raw[len(raw) // 2:]
+    with pytest.raises(ValueError):
+        ibz2.open(path(name), parallelization=4).set_block_offsets({})
+    with pytest.raises(ValueError):
+        ibz2.open(path(name), parallelization=4).set_block_offsets({32: 0})
+
+
+@pytest.mark.gpu
+def test_python_sources_fd_fileobject_bytesio():
+    name = "text-450k-l1"
+    raw = orc.parallel_reader(open(path(name), "rb").read()).data
+    with open(path(name), "rb") as fobj:
+        assert ibz2.open(fobj, parallelization=2).read() == raw                 # object with fileno()
+        assert ibz2.open(fobj.fileno(), parallelization=2).read() == raw        # plain descriptor
+    memory = io.BytesIO(open(path(name), "rb").read())
+    memory.seek(17)
+    f = ibz2.open(memory, parallelization=3)                                    # read/seek/tell/seekable object
+    assert memory.tell() == 17
+    assert f.read(100) == raw[:100] and f.readline() == raw[100:raw.index(b"\n", 100) + 1]
+    raw_file = ibz2.IndexedBzip2FileRaw(path(name), 4)
+    buffer = bytearray(1000)
+    assert raw_file.readinto(buffer) == 1000 and bytes(buffer) == raw[:1000]
+    assert raw_file.bz2reader.tell_compressed() == 32
+    raw_file.join_threads()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ALL)
+@pytest.mark.parametrize("flavour,parallelism", [("cli_parallel", "4"), ("cli_serial", "1")])
+def test_cli_decompress_matches_reference(name, flavour, parallelism):
+    want = GOLDEN[name][flavour]
+    out = subprocess.run([str(CLI), "-d", "-c", "-P", parallelism, path(name)], capture_output=True)
+    assert out.returncode == want["rc"]
+    assert out.stderr.decode().strip() == want["stderr"]
+    if want["rc"] == 0 or flavour == "cli_parallel":
+        assert len(out.stdout) == want["stdout_size"] and sha(out.stdout) == want["stdout_sha256"]
+    else:
+        # the serial reference writes the bytes of a block before it finds the CRC wrong; this reader does not
+        assert len(out.stdout) <= want["stdout_size"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["multistream-b64-1B-empty-b64", "err-gap-then-valid", "text-450k-l1", "ref-empty"])
+def test_cli_offset_lists(name, tmp_path):
+    out = subprocess.run([str(CLI), "-l", "-", path(name)], capture_output=True, text=True)
+    assert out.returncode == 0
+    assert [int(x) for x in out.stdout.split()] == GOLDEN[name]["finder"]
+    listing = tmp_path / "offsets.txt"
+    out = subprocess.run([str(CLI), "-L", str(listing), "-P", "4", path(name)], capture_output=True, text=True)
+    assert out.returncode == 0
+    assert listing.read_text() == "".join(f"{b},{n}\n" for b, n in GOLDEN[name]["parallel"]["offsets"])
+    out = subprocess.run([str(CLI), "-L", str(listing), path(name)], capture_output=True, text=True)
+    assert out.returncode == 1 and "already exists" in out.stderr
+
+
+@pytest.mark.gpu
+def test_cli_output_file_rules(tmp_path):
+    source = tmp_path / "sample.BZ2"
+    source.write_bytes(open(path("text-450k-l1"), "rb").read())
+    raw = orc.parallel_reader(source.read_bytes()).data
+    out = subprocess.run([str(CLI), "-d", "-t", "-v", str(source)], capture_output=True, text=True)
+    entries = len(GOLDEN["text-450k-l1"]["parallel"]["offsets"])   # data blocks + EOS + end sentinel
+    assert out.returncode == 0 and f"Found {entries} blocks" in out.stdout
+    assert (tmp_path / "sample").read_bytes() == raw                   # '.bz2' stripped, case-insensitively
+    out = subprocess.run([str(CLI), "-d", str(source)], capture_output=True, text=True)
+    assert out.returncode == 1 and "already exists" in out.stderr
+    assert subprocess.run([str(CLI), "-d", "-f", str(source)], capture_output=True).returncode == 0
+    piped = subprocess.run([str(CLI), "-d", "-c"], input=source.read_bytes(), capture_output=True)
+    assert piped.returncode == 0 and piped.stdout == raw               # standard input -> standard output
