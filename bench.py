@@ -252,13 +252,11 @@ def run_ours(args):
 
     # this rank's share: blocks whose magic starts in [first_byte, last_byte); the window runs past last_byte so that
     # the last owned block is complete (a block never exceeds ~1.1 MB compressed)
-    first_byte = C * rank // world
-    last_byte = C * (rank + 1) // world
-    slack = 4 << 20
-    win_end = min(C, last_byte + slack)
-    window = comp[first_byte:win_end]
-    first_bit = 0
-    last_bit = (last_byte - first_byte) * 8 if rank + 1 < world else (1 << 64) - 1
+    from indexed_bzip2_b200.partition import rank_share
+
+    share = rank_share(C, rank, world)
+    window = comp[share.first_byte:share.end_byte]
+    first_bit, last_bit = share.first_bit, share.last_bit
     out_cap = int(w.raw_size / world * 1.1) + (64 << 20)
 
     ctx = _capi.Context(local_rank)
@@ -363,7 +361,7 @@ def run_ours(args):
             peak, peak_src = 6650.0, "fallback of B200_PROFILING.md"
         per_step = {s: stage_ms[s] / args.steps for s in STAGES}
         dominant = max(per_step, key=per_step.get)
-        waves = max(1, -(-len(results) // (args.batch_blocks or 148 * 12)))
+        waves = max(1, -(-len(results) // (args.batch_blocks or 148 * 64)))
         alg = algorithmic_bytes(dominant, my_c, n_symbols, int(total))
         achieved = alg / (per_step[dominant] * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": dominant.replace("_ms", ""), "achieved": round(achieved, 2), "peak": peak,
