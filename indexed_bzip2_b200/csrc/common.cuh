@@ -77,6 +77,7 @@ struct alignas( 16 ) BlockTables
     uint32_t selectorsCount;
     uint32_t groupCount;
     uint32_t pad;
+    uint16_t eobPerm[MAX_GROUPS + 2];           /* perm index of the end-of-block symbol (the last one of its length) */
 };
 
 /* The symbol stream of a block is cut into chunks of MTF_CHUNK coded symbols; K2b leaves one checkpoint per chunk. */
@@ -149,7 +150,7 @@ void launchFindMagics( const uint8_t* data, uint64_t nbytes, uint32_t which, uin
 void launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* lbytes, uint8_t* selectors, BlockTables* tables, uint32_t* scratch,
                           uint32_t* counter, cudaStream_t stream );
-constexpr uint32_t HUFFMAN_LAUNCHES = 6;
+constexpr uint32_t HUFFMAN_LAUNCHES = 7;
 
 void launchHuffmanHeader( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* selectors, BlockTables* tables, cudaStream_t stream );

@@ -6,8 +6,8 @@
  * shorten it, so the chip is filled with as many independent chains as shared memory allows:
  *   - every SM runs one persistent CTA of BITS_WARPS warps with BITS_LANES active lanes each = 32 decoders per SM;
  *   - the six 9-bit LUTs of a decoder's block (K2a's BlockTables::lut, 6 KB) sit in shared memory as
- *     u16 lut[table * 512 + index][slot]: the decoders of one warp are neighbouring slots, i.e. they read different
- *     banks whatever they look up;
+ *     u16 lut[index][table][slot]: the decoders of one warp are neighbouring slots, i.e. they read different
+ *     banks whatever they look up, and an entry's address is one shift and one multiply-add away from the window;
  *   - decoders pull block indices from a global counter; the unit of lockstep inside a warp is one GROUP of 50 symbols
  *     (the table switch of bzip2.hpp:710-721), so a decoder that finishes its block waits at most 49 symbols for its
  *     warp before it fetches the next block;
@@ -34,6 +34,7 @@ constexpr int BITS_LANES = 8;
 constexpr int BITS_SLOTS = BITS_WARPS * BITS_LANES;
 static_assert( BITS_SLOTS == 32, "the LUT rows are 32 decoders wide" );
 constexpr uint32_t LUT_ROW_BYTES = BITS_SLOTS * 2U;               /* one u16 per decoder */
+constexpr uint32_t LUT_IDX_STRIDE = MAX_GROUPS * LUT_ROW_BYTES;   /* u16 lut[index][table][decoder] */
 constexpr uint32_t LUT_ENTRIES = MAX_GROUPS * HUFF_LUT_SIZE;      /* 3072 rows */
 constexpr uint32_t SYM_LIMIT = DBUF_SIZE;                         /* a clean block has at most this many symbols */
 constexpr uint32_t GROUP_MAX_WORDS = ( GROUP_SIZE * MAX_CODE_LEN + 31U ) / 32U + 4U + 96U;   /* + prefetch distance */
@@ -94,18 +95,88 @@ decodeLong( const BlockTables* __restrict__ bt, uint32_t table, uint32_t hi )
     return ( static_cast<uint32_t>( bt->perm[table][idx] ) << 5 ) | len;
 }
 
+/* ---- shared memory of one CTA: everything a decoder looks at per symbol, one bank column per decoder ---- */
+constexpr uint32_t LONG_FIRST_LEN = HUFF_LUT_BITS;                          /* limits are kept for lengths 9..20 */
+constexpr uint32_t LONG_LIMITS = MAX_CODE_LEN - LONG_FIRST_LEN + 1U;        /* 12 */
+constexpr uint32_t LONG_OFFSETS = MAX_CODE_LEN - LONG_FIRST_LEN;            /* lengths 10..20: 11 */
+constexpr uint32_t SH_LUT_BYTES = LUT_ENTRIES * LUT_ROW_BYTES;              /* u16 [6 * 512][32] */
+constexpr uint32_t SH_LIM_OFFSET = SH_LUT_BYTES;                            /* u32 [6][12][32], 20-bit left-aligned code limits */
+constexpr uint32_t SH_LIM_BYTES = MAX_GROUPS * LONG_LIMITS * BITS_SLOTS * 4U;
+constexpr uint32_t SH_OFF_OFFSET = SH_LIM_OFFSET + SH_LIM_BYTES;            /* u16 [6][11][32], perm offset of each length */
+constexpr uint32_t SH_OFF_BYTES = MAX_GROUPS * LONG_OFFSETS * BITS_SLOTS * 2U;
+constexpr uint32_t SH_EOB_OFFSET = SH_OFF_OFFSET + SH_OFF_BYTES;            /* u16 [8][32], perm index of the end-of-block symbol */
+constexpr uint32_t SH_TOTAL_BYTES = SH_EOB_OFFSET + 8U * BITS_SLOTS * 2U;
+static_assert( SH_TOTAL_BYTES <= 227U * 1024U, "one CTA per SM" );
+
+__device__ __forceinline__ uint32_t
+ldsU16( uint32_t addr )
+{
+    uint32_t v;   /* a wider destination is zero-extended: no separate mask on the dependent chain */
+    asm volatile( "ld.volatile.shared.u16 %0, [%1];" : "=r"( v ) : "r"( addr ) );
+    return v;
+}
+
+__device__ __forceinline__ uint32_t
+ldsU32( uint32_t addr )
+{
+    uint32_t v;
+    asm volatile( "ld.shared.u32 %0, [%1];" : "=r"( v ) : "r"( addr ) );
+    return v;
+}
+
+/* LUT entry for the 9 bits on top of the window; tableAddr = shared address of lut[0][table][slot] */
+__device__ __forceinline__ uint32_t
+lookup( uint32_t tableAddr, uint32_t hi )
+{
+    return ldsU16( ( hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_IDX_STRIDE + tableAddr );   /* shift + multiply-add */
+}
+
+/* A code of more than 9 bits (HuffmanCodingShortBitsCached.hpp:117-150), entirely from shared memory and without the
+ * symbol itself: canonical codes grow with their length when left-aligned, so the length is 10 + the number of per-length
+ * limits the window has reached, and the code's rank among all codes (its index into perm) follows from the limit below
+ * it.  Needs 20 valid bits in hi.  Returns ( permIndex << 5 ) | length, 0 when no code matches. */
+__device__ __noinline__ uint32_t
+decodeLongShared( uint32_t limAddr, uint32_t offAddr, uint32_t hi )
+{
+    const uint32_t h20 = hi >> 12;
+    uint32_t lim[LONG_LIMITS];
+#pragma unroll
+    for ( uint32_t i = 0; i < LONG_LIMITS; ++i ) {
+        lim[i] = ldsU32( limAddr + i * ( BITS_SLOTS * 4U ) );
+    }
+    uint32_t len = LONG_FIRST_LEN + 1U;
+    uint32_t lower = lim[0];
+#pragma unroll
+    for ( uint32_t i = 1; i + 1U < LONG_LIMITS; ++i ) {
+        const bool ge = h20 >= lim[i];
+        len += ge ? 1U : 0U;
+        lower = ge ? lim[i] : lower;
+    }
+    if ( h20 >= lim[LONG_LIMITS - 1U] ) {
+        return 0;
+    }
+    const uint32_t rel = ( h20 - lower ) >> ( MAX_CODE_LEN - len );
+    const uint32_t idx = ldsU16( offAddr + ( len - LONG_FIRST_LEN - 1U ) * ( BITS_SLOTS * 2U ) ) + rel;
+    return ( idx << 5 ) | len;
+}
+
 __global__ void __launch_bounds__( BITS_WARPS * 32, 1 )
 huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks,
                    const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
                    uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter )
 {
-    extern __shared__ __align__( 16 ) uint8_t lutShared[];   /* u16 [LUT_ENTRIES][BITS_SLOTS] */
+    extern __shared__ __align__( 16 ) uint8_t lutShared[];
     const uint32_t lane = threadIdx.x & 31U;
     if ( lane >= static_cast<uint32_t>( BITS_LANES ) ) {
         return;
     }
     const uint32_t slot = ( threadIdx.x >> 5 ) * BITS_LANES + lane;
     uint8_t* const myLut = lutShared + slot * 2U;
+    const uint32_t sharedBase = static_cast<uint32_t>( __cvta_generic_to_shared( lutShared ) );
+    const uint32_t myLutAddr = sharedBase + slot * 2U;
+    const uint32_t myLimAddr = sharedBase + SH_LIM_OFFSET + slot * 4U;
+    const uint32_t myOffAddr = sharedBase + SH_OFF_OFFSET + slot * 2U;
+    const uint32_t myEobAddr = sharedBase + SH_EOB_OFFSET + slot * 2U;
     const uint64_t nbits = nbytes * 8U;
     const uint64_t fullWords = nbytes >> 2;   /* words that can be loaded without looking at the file end */
     const uint32_t* const dataWords = reinterpret_cast<const uint32_t*>( data );
@@ -141,18 +212,34 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             {
                 /* LUTs -> this decoder's column */
                 const uint4* src = reinterpret_cast<const uint4*>( &bt->lut[0][0] );
-                const uint32_t quads = bt->groupCount * ( HUFF_LUT_SIZE / 8U );
-                uint8_t* dst = myLut;
+                const uint32_t groupCount = bt->groupCount;
+                const uint32_t quads = groupCount * ( HUFF_LUT_SIZE / 8U );
                 for ( uint32_t q = 0; q < quads; ++q ) {
                     const uint4 v = __ldg( src + q );
                     const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+                    /* quad q holds entries 8 * ( q % 64 ) .. + 7 of table q / 64 */
+                    uint8_t* dst = myLut + ( q >> 6 ) * LUT_ROW_BYTES + ( ( q & 63U ) * 8U ) * LUT_IDX_STRIDE;
 #pragma unroll
                     for ( uint32_t i = 0; i < 4U; ++i ) {
                         *reinterpret_cast<uint16_t*>( dst ) = static_cast<uint16_t>( w[i] );
-                        *reinterpret_cast<uint16_t*>( dst + LUT_ROW_BYTES ) = static_cast<uint16_t>( w[i] >> 16 );
-                        dst += 2U * LUT_ROW_BYTES;
+                        *reinterpret_cast<uint16_t*>( dst + LUT_IDX_STRIDE ) = static_cast<uint16_t>( w[i] >> 16 );
+                        dst += 2U * LUT_IDX_STRIDE;
                     }
                 }
+                /* what the codes of more than 9 bits need: limits as 20-bit left-aligned values, perm offsets, EOB index */
+                for ( uint32_t g = 0; g < groupCount; ++g ) {
+                    for ( uint32_t i = 0; i < LONG_LIMITS; ++i ) {
+                        const uint64_t limit = bt->limit[g][LONG_FIRST_LEN + i];   /* <= 2^32, a multiple of 2^12 */
+                        *reinterpret_cast<uint32_t*>( lutShared + SH_LIM_OFFSET + ( ( g * LONG_LIMITS + i ) * BITS_SLOTS + slot ) * 4U )
+                            = static_cast<uint32_t>( limit >> 12 );
+                    }
+                    for ( uint32_t i = 0; i < LONG_OFFSETS; ++i ) {
+                        *reinterpret_cast<uint16_t*>( lutShared + SH_OFF_OFFSET + ( ( g * LONG_OFFSETS + i ) * BITS_SLOTS + slot ) * 2U )
+                            = bt->offset[g][LONG_FIRST_LEN + 1U + i];
+                    }
+                    *reinterpret_cast<uint16_t*>( lutShared + SH_EOB_OFFSET + ( g * BITS_SLOTS + slot ) * 2U ) = bt->eobPerm[g];
+                }
+                asm volatile( "" ::: "memory" );   /* the asm loads below read what was just stored */
             }
             const uint64_t startBit = bt->dataStartBit;
             d.wordIdx = startBit >> 5;
@@ -181,33 +268,43 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 selWord = *reinterpret_cast<const uint32_t*>( selectors + selIdx );
             }
             const uint32_t table = ( selWord >> ( 8U * ( selIdx & 3U ) ) ) & 0xFFU;
-            const uint8_t* const tableLut = myLut + table * ( HUFF_LUT_SIZE * LUT_ROW_BYTES );
+            const uint8_t* const tableLut = myLut + table * LUT_ROW_BYTES;
             ++selIdx;
             uint32_t* const pairOut = reinterpret_cast<uint32_t*>( symOut + nsym );   /* nsym is a multiple of 50 */
 
             if ( d.wordIdx + GROUP_MAX_WORDS < fullWords ) {
                 /* ---- hot loop: two symbols per iteration, no file-end checks ----
+                 * The chain that bounds a block is  window -> LUT -> length -> shifted window -> LUT ...  Everything
+                 * else is kept off it: the window is shifted by the LUT's length and the NEXT lookup is issued before
+                 * anything is decided about the current entry (a miss has length 0, so nothing was consumed and the
+                 * long-code path starts from an intact window and repeats the lookup); the refill, the end-of-block
+                 * test, the stores and all branches run in the shadow of that lookup.
                  * Two raw words are kept in flight behind the window so that a load has two refills to land. */
+                const uint32_t tableAddr = myLutAddr + table * LUT_ROW_BYTES;
+                const uint32_t limAddr = myLimAddr + table * ( LONG_LIMITS * BITS_SLOTS * 4U );
+                const uint32_t offAddr = myOffAddr + table * ( LONG_OFFSETS * BITS_SLOTS * 2U );
+                const uint32_t eobIdx = ldsU16( myEobAddr + table * ( BITS_SLOTS * 2U ) );
+                const uint32_t longTag = 0x8000U | ( table << 9 );
                 const uint32_t* wp = dataWords + d.wordIdx;
                 uint32_t raw0 = __byte_perm( d.nextW, 0, 0x0123 );   /* back to memory order: swapped when used */
                 uint32_t raw1 = __ldg( wp + 1 );
+                uint32_t hi = d.hi;
+                uint32_t lo = d.lo;
+                int nb = d.nb;
                 uint32_t g = 0;
-                uint32_t eobTail = 0;   /* bits consumed after the end-of-block symbol */
+                uint32_t e = lookup( tableAddr, hi );   /* at least 15 valid bits here */
 #pragma unroll 5
                 for ( ; g < GROUP_SIZE / 2U; ++g ) {
-                    /* The first lookup only needs the top 9 bits, which are valid before the refill (at least 15 bits
-                     * are left after a pair), so it is issued first and the refill fills its latency. */
-                    uint32_t e0 = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_ROW_BYTES );
                     {
                         /* refill, written as selects so that it is predicated, not branched around: the load then
                          * lands in raw1's own register and nothing waits for it before the next refill */
-                        const bool rf = d.nb <= 32;
+                        const bool rf = nb <= 32;
                         const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                        const uint32_t addHi = __funnelshift_rc( x, 0U, static_cast<uint32_t>( d.nb ) );
-                        const uint32_t newLo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - d.nb ) );
-                        d.hi |= rf ? addHi : 0U;
-                        d.lo = rf ? newLo : d.lo;
-                        d.nb += rf ? 32 : 0;
+                        const uint32_t addHi = __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
+                        const uint32_t newLo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
+                        hi |= rf ? addHi : 0U;
+                        lo = rf ? newLo : lo;
+                        nb += rf ? 32 : 0;
                         raw0 = rf ? raw1 : raw0;
                         wp += rf ? 1 : 0;
                         if ( rf ) {
@@ -217,79 +314,108 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                             }
                         }
                     }
+                    /* ---- first symbol of the pair: at least 33 valid bits ---- */
+                    const uint32_t e0 = e;
+                    {
+                        const uint32_t hiNext = __funnelshift_l( lo, hi, e0 );   /* shifts by e0 & 31 = the length */
+                        e = lookup( tableAddr, hiNext );
+                        if ( e0 != 0 ) {
+                            hi = hiNext;
+                        }
+                    }
+                    uint32_t out0 = e0 >> 5;
+                    bool end0 = out0 > symbolCount;
                     if ( e0 == 0 ) {
-                        e0 = decodeLong( bt, table, d.hi );
-                        if ( e0 == 0 ) {
+                        const uint32_t r = decodeLongShared( limAddr, offAddr, hi );
+                        if ( r == 0 ) {
                             outcome = 2;
                             break;
                         }
-                        consume( d, e0 & 31U );
-                        if ( d.nb <= 32 ) {
+                        const uint32_t len = r & 31U;
+                        hi = __funnelshift_l( lo, hi, len );
+                        lo <<= len;
+                        nb -= static_cast<int>( len );
+                        if ( nb <= 32 ) {
                             const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                            d.hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( d.nb ) );
-                            d.lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - d.nb ) );
-                            d.nb += 32;
+                            hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
+                            lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
+                            nb += 32;
                             raw0 = raw1;
                             raw1 = __ldg( wp + 2 );
                             ++wp;
                         }
+                        e = lookup( tableAddr, hi );
+                        out0 = longTag | ( r >> 5 );
+                        end0 = ( r >> 5 ) == eobIdx;
                     } else {
-                        consume( d, e0 & 31U );
+                        lo <<= ( e0 & 31U );
+                        nb -= static_cast<int>( e0 & 31U );
                     }
-                    const uint32_t sym0 = e0 >> 5;
-                    uint32_t e1 = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_ROW_BYTES );
-                    if ( e1 == 0 ) {
-                        if ( sym0 > symbolCount ) {
-                            e1 = ( symbolCount + 2U ) << 5;   /* whatever follows the end-of-block symbol is not ours */
-                        } else {
-                            e1 = decodeLong( bt, table, d.hi );
-                            if ( e1 == 0 ) {
-                                outcome = 2;
-                                break;
-                            }
-                        }
-                        consume( d, e1 & 31U );
-                        if ( d.nb <= 32 ) {
-                            /* a long code can leave fewer than the 9 bits the next pair looks up before refilling */
-                            const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                            d.hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( d.nb ) );
-                            d.lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - d.nb ) );
-                            d.nb += 32;
-                            raw0 = raw1;
-                            raw1 = __ldg( wp + 2 );
-                            ++wp;
-                        }
-                    } else {
-                        consume( d, e1 & 31U );
-                    }
-                    const uint32_t sym1 = e1 >> 5;
-                    pairOut[g] = sym0 | ( sym1 << 16 );
-                    if ( max( sym0, sym1 ) > symbolCount ) {
+                    if ( end0 ) {
                         /* end of block (bzip2.hpp:766-768) */
                         outcome = 1;
-                        if ( sym0 > symbolCount ) {
-                            nsym += 2U * g;
-                            eobTail = e1 & 31U;
-                        } else {
-                            nsym += 2U * g + 1U;
+                        nsym += 2U * g;
+                        break;
+                    }
+                    /* ---- second symbol: at least 24 valid bits ---- */
+                    const uint32_t e1 = e;
+                    {
+                        const uint32_t hiNext = __funnelshift_l( lo, hi, e1 );
+                        e = lookup( tableAddr, hiNext );   /* first symbol of the next pair: at least 15 valid bits */
+                        if ( e1 != 0 ) {
+                            hi = hiNext;
                         }
+                    }
+                    uint32_t out1 = e1 >> 5;
+                    bool end1 = out1 > symbolCount;
+                    if ( e1 == 0 ) {
+                        const uint32_t r = decodeLongShared( limAddr, offAddr, hi );
+                        if ( r == 0 ) {
+                            outcome = 2;
+                            break;
+                        }
+                        const uint32_t len = r & 31U;
+                        hi = __funnelshift_l( lo, hi, len );
+                        lo <<= len;
+                        nb -= static_cast<int>( len );
+                        if ( nb <= 32 ) {
+                            const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
+                            hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
+                            lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
+                            nb += 32;
+                            raw0 = raw1;
+                            raw1 = __ldg( wp + 2 );
+                            ++wp;
+                        }
+                        e = lookup( tableAddr, hi );
+                        out1 = longTag | ( r >> 5 );
+                        end1 = ( r >> 5 ) == eobIdx;
+                    } else {
+                        lo <<= ( e1 & 31U );
+                        nb -= static_cast<int>( e1 & 31U );
+                    }
+                    pairOut[g] = out0 | ( out1 << 16 );
+                    if ( end1 ) {
+                        outcome = 1;
+                        nsym += 2U * g + 1U;
                         break;
                     }
                 }
                 /* the window holds wp[-2], wp[-1]; raw0 = wp[0]: hand the position back in file terms */
+                d.hi = hi;
+                d.lo = lo;
+                d.nb = nb;
                 d.wordIdx = static_cast<uint64_t>( wp - dataWords );
                 d.nextW = __byte_perm( raw0, 0, 0x0123 );
                 if ( outcome == 0 ) {
                     nsym += GROUP_SIZE;
-                } else if ( eobTail != 0 ) {
-                    d.nb += static_cast<int>( eobTail );   /* only the bit position is used from here on */
                 }
             } else {
                 /* ---- the last groups before the end of the file: same loop with checked loads ---- */
                 uint32_t g = 0;
                 for ( ; g < GROUP_SIZE; ++g ) {
                     refillChecked( d, data, nbytes );
-                    uint32_t e = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_ROW_BYTES );
+                    uint32_t e = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_IDX_STRIDE );
                     if ( e == 0 ) {
                         e = decodeLong( bt, table, d.hi );
                         if ( e == 0 ) {
@@ -322,18 +448,70 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
         }
     }
 }
+
+/* Symbols that K2b left as ( 0x8000 | table << 9 | permIndex ) -> the symbol itself (HuffmanCodingSymbolsPerLength.hpp:
+ * 105-124).  One pass over the symbol arrays with 16-byte accesses; about one symbol in a hundred is rewritten. */
+constexpr int RESOLVE_THREADS = 256;
+constexpr uint32_t RESOLVE_PER_CTA = RESOLVE_THREADS * 8U * 8U;   /* symbols per CTA */
+
+__global__ void __launch_bounds__( RESOLVE_THREADS )
+resolveLongSymbolsKernel( const BlockMeta* __restrict__ meta, const BlockTables* __restrict__ tablesAll,
+                          uint32_t* __restrict__ scratchAll )
+{
+    const uint32_t block = blockIdx.y;
+    const BlockMeta& bm = meta[block];
+    if ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) {
+        return;
+    }
+    const uint32_t nCoded = bm.nCoded;
+    const uint32_t ctaFirst = blockIdx.x * RESOLVE_PER_CTA;
+    if ( ctaFirst >= nCoded ) {
+        return;
+    }
+    const BlockTables& bt = tablesAll[block];
+    uint4* const sym = reinterpret_cast<uint4*>( reinterpret_cast<uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE )
+                                                 + K2_SYM16_OFFSET );
+    const uint32_t quads = ( nCoded + 7U ) / 8U;   /* the slot is larger than any clean block: whole quads are ours */
+#pragma unroll
+    for ( uint32_t i = 0; i < 8U; ++i ) {
+        const uint32_t q = ctaFirst / 8U + i * RESOLVE_THREADS + threadIdx.x;
+        if ( q >= quads ) {
+            break;
+        }
+        uint4 v = sym[q];
+        if ( ( ( v.x | v.y | v.z | v.w ) & 0x80008000U ) == 0 ) {
+            continue;
+        }
+        uint32_t w[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+        for ( uint32_t k = 0; k < 4U; ++k ) {
+            uint32_t a = w[k] & 0xFFFFU;
+            uint32_t b = w[k] >> 16;
+            if ( ( a & 0x8000U ) != 0 ) {
+                a = bt.perm[( a >> 9 ) & 7U][a & 0x1FFU];
+            }
+            if ( ( b & 0x8000U ) != 0 ) {
+                b = bt.perm[( b >> 9 ) & 7U][b & 0x1FFU];
+            }
+            w[k] = a | ( b << 16 );
+        }
+        sym[q] = make_uint4( w[0], w[1], w[2], w[3] );
+    }
+}
 }  // namespace
 
 void
 launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, const uint8_t* selectors,
                    const BlockTables* tables, uint32_t* scratch, uint32_t* counter, cudaStream_t stream )
 {
-    const size_t shared = static_cast<size_t>( LUT_ENTRIES ) * LUT_ROW_BYTES;
+    const size_t shared = SH_TOTAL_BYTES;
     cudaFuncSetAttribute( huffmanBitsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>( shared ) );
     cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
     const uint32_t ctas = static_cast<uint32_t>( std::min<uint64_t>( static_cast<uint64_t>( smCount() ),
                                                                    ( nblocks + BITS_SLOTS - 1U ) / BITS_SLOTS ) );
     huffmanBitsKernel<<<ctas, BITS_WARPS * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables,
                                                                  scratch, counter );
+    const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
+    resolveLongSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
 }
 }  // namespace ibz2

@@ -31,6 +31,7 @@ struct WarpShared
     uint32_t maxLen[MAX_GROUPS + 2];
     uint8_t lens[264];
     uint8_t s2b[256];
+    uint8_t eobLen[MAX_GROUPS + 2];   /* code length of the end-of-block symbol per table */
 };
 
 /* MSB-first bit cursor shared by the warp (semantics of BitReader<true, uint64_t>, core/BitReader.hpp:190-290). */
@@ -169,6 +170,7 @@ buildTable( WarpShared& ws, uint32_t g, uint32_t nsym, uint32_t lane )
     }
     if ( lane == 0 ) {
         ws.maxLen[g] = maxLen;
+        ws.eobLen[g] = ws.lens[nsym - 1U];
     }
     /* symbols sorted by (length, symbol): lane l places the symbols of length l */
     if ( ( lane >= 1U ) && ( lane <= MAX_CODE_LEN ) && ( c > 0 ) ) {
@@ -419,6 +421,8 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
             }
             if ( lane < groupCount ) {
                 bt.maxLen[lane] = ws.maxLen[lane];
+                /* perm is sorted by (length, symbol) and the end-of-block symbol is the largest one */
+                bt.eobPerm[lane] = static_cast<uint16_t>( ws.offset[lane][ws.eobLen[lane]] + ws.count[lane][ws.eobLen[lane]] - 1U );
             }
             for ( uint32_t i = lane; i < 256U; i += 32U ) {
                 bt.s2b[i] = i < symbolCount ? ws.s2b[i] : static_cast<uint8_t>( i );

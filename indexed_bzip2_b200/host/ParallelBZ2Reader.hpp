@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <iostream>
 #include <memory>
+#include <vector>
 
 #include "BlockIndex.hpp"
 #include "BZ2ReaderInterface.hpp"
@@ -304,7 +305,24 @@ private:
     static UniqueFileReader
     requireSeekable( UniqueFileReader fileReader )
     {
-        if ( !fileReader || !fileReader->seekable() ) {
+        if ( !fileReader ) {
+            throw std::invalid_argument( "File reader must not be null!" );
+        }
+        if ( !fileReader->seekable() ) {
+            /* ensureSharedFileReader (core/filereader/Shared.hpp:471-473) puts a SinglePassFileReader, which keeps
+             * everything it has read, in front of a pipe; the GPU path wants the whole file anyway, so read it now. */
+            std::vector<uint8_t> bytes;
+            std::vector<char> chunk( 4U << 20 );
+            while ( true ) {
+                const size_t n = fileReader->read( chunk.data(), chunk.size() );
+                if ( n == 0 ) {
+                    break;
+                }
+                bytes.insert( bytes.end(), chunk.begin(), chunk.begin() + static_cast<std::ptrdiff_t>( n ) );
+            }
+            fileReader = std::make_unique<MemoryFileReader>( std::move( bytes ) );
+        }
+        if ( !fileReader->seekable() ) {
             throw std::invalid_argument( "Parallel BZ2 Reader will not work on non-seekable input like stdin (yet)!" );
         }
         return fileReader;
