@@ -89,7 +89,7 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
                 sh.sstar = static_cast<int>( s );
                 sh.kstar = steps;
             }
-            const uint32_t e = __ldg( dbuf + pos );
+            const uint32_t e = __ldcg( dbuf + pos );
             acc |= ( e & 0xFFU ) << ( 8U * ( cursor & 3U ) );
             ++cursor;
             if ( ( cursor & 3U ) == 0 ) {
@@ -124,7 +124,7 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
             uint32_t pos = p0;
             uint32_t k = 0;
             do {
-                const uint32_t e = __ldg( dbuf + pos );
+                const uint32_t e = __ldcg( dbuf + pos );
                 prerle[k++] = static_cast<uint8_t>( e );
                 pos = e >> 8;
             } while ( ( pos != p0 ) && ( k < n ) );
@@ -218,7 +218,7 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
                     uint32_t pos = s << SPACING_SHIFT;
                     uint32_t k = 0;
                     do {
-                        const uint32_t e = __ldg( dbuf + pos );
+                        const uint32_t e = __ldcg( dbuf + pos );
                         const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( base + k );
                         if ( idx < n ) {
                             prerle[idx] = static_cast<uint8_t>( e );

@@ -29,8 +29,8 @@ namespace ibz2
 {
 namespace
 {
-constexpr int BITS_WARPS = 4;
-constexpr int BITS_LANES = 8;
+constexpr int BITS_WARPS = 16;
+constexpr int BITS_LANES = 2;
 constexpr int BITS_SLOTS = BITS_WARPS * BITS_LANES;
 static_assert( BITS_SLOTS == 32, "the LUT rows are 32 decoders wide" );
 constexpr uint32_t LUT_ROW_BYTES = BITS_SLOTS * 2U;               /* one u16 per decoder */
@@ -163,14 +163,19 @@ decodeLongShared( uint32_t limAddr, uint32_t offAddr, uint32_t hi )
 __global__ void __launch_bounds__( BITS_WARPS * 32, 1 )
 huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks,
                    const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
-                   uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter )
+                   uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, uint32_t slotsPerCta )
 {
     extern __shared__ __align__( 16 ) uint8_t lutShared[];
     const uint32_t lane = threadIdx.x & 31U;
     if ( lane >= static_cast<uint32_t>( BITS_LANES ) ) {
         return;
     }
-    const uint32_t slot = ( threadIdx.x >> 5 ) * BITS_LANES + lane;
+    /* the lanes of one warp are BITS_WARPS slots apart: different banks whatever they look up; a launch with few blocks
+     * (slotsPerCta < 32) leaves the second lane of every warp idle rather than whole SMs */
+    const uint32_t slot = lane * BITS_WARPS + ( threadIdx.x >> 5 );
+    if ( slot >= slotsPerCta ) {
+        return;
+    }
     uint8_t* const myLut = lutShared + slot * 2U;
     const uint32_t sharedBase = static_cast<uint32_t>( __cvta_generic_to_shared( lutShared ) );
     const uint32_t myLutAddr = sharedBase + slot * 2U;
@@ -216,7 +221,15 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 const uint32_t quads = groupCount * ( HUFF_LUT_SIZE / 8U );
                 for ( uint32_t q = 0; q < quads; ++q ) {
                     const uint4 v = __ldg( src + q );
-                    const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+                    uint32_t w[4] = { v.x, v.y, v.z, v.w };
+                    /* The end-of-block symbol is taken out of the shared-memory copy: the hot loop then has ONE
+                     * exceptional entry value (0 = "not a plain symbol of at most 9 bits") to test for. */
+#pragma unroll
+                    for ( uint32_t i = 0; i < 4U; ++i ) {
+                        const uint32_t a = ( ( w[i] & 0xFFFFU ) >> 5 ) > symbolCount ? 0U : ( w[i] & 0xFFFFU );
+                        const uint32_t b = ( w[i] >> 21 ) > symbolCount ? 0U : ( w[i] >> 16 );
+                        w[i] = a | ( b << 16 );
+                    }
                     /* quad q holds entries 8 * ( q % 64 ) .. + 7 of table q / 64 */
                     uint8_t* dst = myLut + ( q >> 6 ) * LUT_ROW_BYTES + ( ( q & 63U ) * 8U ) * LUT_IDX_STRIDE;
 #pragma unroll
@@ -274,16 +287,16 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
 
             if ( d.wordIdx + GROUP_MAX_WORDS < fullWords ) {
                 /* ---- hot loop: two symbols per iteration, no file-end checks ----
-                 * The chain that bounds a block is  window -> LUT -> length -> shifted window -> LUT ...  Everything
-                 * else is kept off it: the window is shifted by the LUT's length and the NEXT lookup is issued before
-                 * anything is decided about the current entry (a miss has length 0, so nothing was consumed and the
-                 * long-code path starts from an intact window and repeats the lookup); the refill, the end-of-block
-                 * test, the stores and all branches run in the shadow of that lookup.
-                 * Two raw words are kept in flight behind the window so that a load has two refills to land. */
+                 * A lane's instruction stream is what bounds a block (one warp instruction every ~5 cycles, nothing to
+                 * overlap it with inside the block), so the pair is ONE basic block with as few instructions as the
+                 * format allows: look up, shift the window by the entry's length, look up again.  An entry of 0 (code
+                 * longer than 9 bits, the end-of-block symbol, or no code) has length 0: the window stays where it
+                 * is and every later lookup misses too, so one test at the end of the pair finds it, with the window
+                 * still in front of the first symbol that needs the slow path.
+                 * Two raw words are kept in flight behind the window so that a load has a whole pair to land. */
                 const uint32_t tableAddr = myLutAddr + table * LUT_ROW_BYTES;
                 const uint32_t limAddr = myLimAddr + table * ( LONG_LIMITS * BITS_SLOTS * 4U );
                 const uint32_t offAddr = myOffAddr + table * ( LONG_OFFSETS * BITS_SLOTS * 2U );
-                const uint32_t eobIdx = ldsU16( myEobAddr + table * ( BITS_SLOTS * 2U ) );
                 const uint32_t longTag = 0x8000U | ( table << 9 );
                 const uint32_t* wp = dataWords + d.wordIdx;
                 uint32_t raw0 = __byte_perm( d.nextW, 0, 0x0123 );   /* back to memory order: swapped when used */
@@ -296,109 +309,93 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
 #pragma unroll 5
                 for ( ; g < GROUP_SIZE / 2U; ++g ) {
                     {
-                        /* refill, written as selects so that it is predicated, not branched around: the load then
-                         * lands in raw1's own register and nothing waits for it before the next refill */
+                        /* refill as selects (no branch); lo is empty whenever rf holds */
                         const bool rf = nb <= 32;
-                        const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                        const uint32_t addHi = __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
-                        const uint32_t newLo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
-                        hi |= rf ? addHi : 0U;
-                        lo = rf ? newLo : lo;
+                        const uint32_t x = rf ? __byte_perm( raw0, 0, 0x0123 ) : 0U;
+                        hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
+                        lo |= __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                         nb += rf ? 32 : 0;
                         raw0 = rf ? raw1 : raw0;
                         wp += rf ? 1 : 0;
-                        if ( rf ) {
-                            raw1 = __ldg( wp + 1 );
-                            if ( ( reinterpret_cast<uintptr_t>( wp ) & 127U ) == 0 ) {
-                                prefetchL1( wp + 64 );   /* stays inside the file: see GROUP_MAX_WORDS */
+                        raw1 = __ldg( wp + 1 );
+                        if ( rf && ( ( reinterpret_cast<uintptr_t>( wp ) & 127U ) == 0 ) ) {
+                            prefetchL1( wp + 64 );   /* stays inside the file: see GROUP_MAX_WORDS */
+                        }
+                    }
+                    /* at least 33 valid bits; a plain symbol takes at most 9 */
+                    const uint32_t e0 = e;
+                    hi = __funnelshift_l( lo, hi, e0 );   /* shifts by e0 & 31 = the length */
+                    lo <<= ( e0 & 31U );
+                    nb -= static_cast<int>( e0 & 31U );
+                    const uint32_t e1 = lookup( tableAddr, hi );
+                    hi = __funnelshift_l( lo, hi, e1 );
+                    lo <<= ( e1 & 31U );
+                    nb -= static_cast<int>( e1 & 31U );
+                    e = lookup( tableAddr, hi );          /* first symbol of the next pair: at least 15 valid bits */
+                    pairOut[g] = ( e0 >> 5 ) | ( ( e1 >> 5 ) << 16 );
+                    if ( e1 == 0 ) {
+                        /* ---- slow path: the window stands in front of symbol `k` of the pair ---- */
+                        uint32_t outFirst = e0 >> 5;
+                        uint32_t outSecond = 0;
+                        const uint32_t lim0 = ldsU32( limAddr );   /* codes of at most 9 bits are below it */
+                        for ( uint32_t k = ( e0 == 0 ) ? 0U : 1U; k < 2U; ++k ) {
+                            if ( nb <= 32 ) {
+                                const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
+                                hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
+                                lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
+                                nb += 32;
+                                raw0 = raw1;
+                                ++wp;
+                                raw1 = __ldg( wp + 1 );
+                            }
+                            uint32_t ee = lookup( tableAddr, hi );
+                            uint32_t out = ee >> 5;
+                            bool isEob = false;
+                            if ( ee == 0 ) {
+                                if ( ( hi >> 12 ) < lim0 ) {
+                                    /* a code of at most 9 bits that is not in the shared-memory LUT: end of block */
+                                    ee = bt->lut[table][hi >> ( 32 - HUFF_LUT_BITS )];
+                                    isEob = true;
+                                } else {
+                                    const uint32_t r = decodeLongShared( limAddr, offAddr, hi );
+                                    if ( r == 0 ) {
+                                        outcome = 2;
+                                        break;
+                                    }
+                                    ee = r;
+                                    out = longTag | ( r >> 5 );
+                                    isEob = ( r >> 5 ) == ldsU16( myEobAddr + table * ( BITS_SLOTS * 2U ) );
+                                }
+                            }
+                            hi = __funnelshift_l( lo, hi, ee );
+                            lo <<= ( ee & 31U );
+                            nb -= static_cast<int>( ee & 31U );
+                            if ( isEob ) {
+                                /* end of block (bzip2.hpp:766-768) */
+                                outcome = 1;
+                                nsym += 2U * g + k;
+                                break;
+                            }
+                            if ( k == 0 ) {
+                                outFirst = out;
+                            } else {
+                                outSecond = out;
                             }
                         }
-                    }
-                    /* ---- first symbol of the pair: at least 33 valid bits ---- */
-                    const uint32_t e0 = e;
-                    {
-                        const uint32_t hiNext = __funnelshift_l( lo, hi, e0 );   /* shifts by e0 & 31 = the length */
-                        e = lookup( tableAddr, hiNext );
-                        if ( e0 != 0 ) {
-                            hi = hiNext;
-                        }
-                    }
-                    uint32_t out0 = e0 >> 5;
-                    bool end0 = out0 > symbolCount;
-                    if ( e0 == 0 ) {
-                        const uint32_t r = decodeLongShared( limAddr, offAddr, hi );
-                        if ( r == 0 ) {
-                            outcome = 2;
+                        pairOut[g] = outFirst | ( outSecond << 16 );
+                        if ( outcome != 0 ) {
                             break;
                         }
-                        const uint32_t len = r & 31U;
-                        hi = __funnelshift_l( lo, hi, len );
-                        lo <<= len;
-                        nb -= static_cast<int>( len );
                         if ( nb <= 32 ) {
                             const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
                             hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
                             lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                             nb += 32;
                             raw0 = raw1;
-                            raw1 = __ldg( wp + 2 );
                             ++wp;
+                            raw1 = __ldg( wp + 1 );
                         }
                         e = lookup( tableAddr, hi );
-                        out0 = longTag | ( r >> 5 );
-                        end0 = ( r >> 5 ) == eobIdx;
-                    } else {
-                        lo <<= ( e0 & 31U );
-                        nb -= static_cast<int>( e0 & 31U );
-                    }
-                    if ( end0 ) {
-                        /* end of block (bzip2.hpp:766-768) */
-                        outcome = 1;
-                        nsym += 2U * g;
-                        break;
-                    }
-                    /* ---- second symbol: at least 24 valid bits ---- */
-                    const uint32_t e1 = e;
-                    {
-                        const uint32_t hiNext = __funnelshift_l( lo, hi, e1 );
-                        e = lookup( tableAddr, hiNext );   /* first symbol of the next pair: at least 15 valid bits */
-                        if ( e1 != 0 ) {
-                            hi = hiNext;
-                        }
-                    }
-                    uint32_t out1 = e1 >> 5;
-                    bool end1 = out1 > symbolCount;
-                    if ( e1 == 0 ) {
-                        const uint32_t r = decodeLongShared( limAddr, offAddr, hi );
-                        if ( r == 0 ) {
-                            outcome = 2;
-                            break;
-                        }
-                        const uint32_t len = r & 31U;
-                        hi = __funnelshift_l( lo, hi, len );
-                        lo <<= len;
-                        nb -= static_cast<int>( len );
-                        if ( nb <= 32 ) {
-                            const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                            hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
-                            lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
-                            nb += 32;
-                            raw0 = raw1;
-                            raw1 = __ldg( wp + 2 );
-                            ++wp;
-                        }
-                        e = lookup( tableAddr, hi );
-                        out1 = longTag | ( r >> 5 );
-                        end1 = ( r >> 5 ) == eobIdx;
-                    } else {
-                        lo <<= ( e1 & 31U );
-                        nb -= static_cast<int>( e1 & 31U );
-                    }
-                    pairOut[g] = out0 | ( out1 << 16 );
-                    if ( end1 ) {
-                        outcome = 1;
-                        nsym += 2U * g + 1U;
-                        break;
                     }
                 }
                 /* the window holds wp[-2], wp[-1]; raw0 = wp[0]: hand the position back in file terms */
@@ -416,6 +413,9 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 for ( ; g < GROUP_SIZE; ++g ) {
                     refillChecked( d, data, nbytes );
                     uint32_t e = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_IDX_STRIDE );
+                    if ( e == 0 ) {
+                        e = bt->lut[table][d.hi >> ( 32 - HUFF_LUT_BITS )];   /* the end-of-block symbol, if short */
+                    }
                     if ( e == 0 ) {
                         e = decodeLong( bt, table, d.hi );
                         if ( e == 0 ) {
@@ -507,10 +507,10 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
     const size_t shared = SH_TOTAL_BYTES;
     cudaFuncSetAttribute( huffmanBitsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>( shared ) );
     cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
-    const uint32_t ctas = static_cast<uint32_t>( std::min<uint64_t>( static_cast<uint64_t>( smCount() ),
-                                                                   ( nblocks + BITS_SLOTS - 1U ) / BITS_SLOTS ) );
+    const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() ), nblocks ) );
+    const uint32_t slotsPerCta = std::min<uint32_t>( BITS_SLOTS, ( nblocks + ctas - 1U ) / ctas );
     huffmanBitsKernel<<<ctas, BITS_WARPS * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables,
-                                                                 scratch, counter );
+                                                                 scratch, counter, slotsPerCta );
     const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
     resolveLongSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
 }
