@@ -3,56 +3,227 @@
  * (with K4a's packing, entry k carries L[T[k]], so the walk reads entry origPtr first: p0 = origPtr)
  * (BurrowsWheelerTransformData::decodeBlock, indexed_bzip2/bzip2.hpp:863-879, without its RLE1 / CRC half).
  *
- * The walk is a dependent-load chain, so it is broken up by list ranking.  One CTA per block:
- *   pass A  every position that is a multiple of SPACING is a "splitter".  Each thread walks from its splitters until
- *           the next splitter, recording the segment's length and successor.  Segment lengths are geometric, so each
- *           lane keeps walking its own list of splitters (no waiting for the slowest lane).  The segment that passes
- *           through the start position p0 is remembered (sstar, kstar).
- *   rank    the successor list of the <= 14063 segments is ranked in shared memory by pointer jumping (Wyllie), with the
- *           list cut at sstar; that gives every segment on p0's cycle its output offset.
- *   copy    the bytes a thread met in pass A sit, in walking order, in the thread's own staging stream (STAGE_CAP bytes
- *           per thread in HBM, written four at a time); once the ranking has given every segment its output offset the
- *           warps copy the segments from the streams to their final positions, 32 consecutive bytes per step.  This
- *           replaces a second walk: a walk costs one 32-byte HBM sector per step (T vectors of the blocks in flight are
- *           far larger than L2), the copy moves each byte once, coalesced.
- *   pass B  only for what did not fit a staging stream (sums of ~14 geometric segment lengths rarely exceed it; runs of
- *           pathological T vectors can): those segments are walked again and written directly.
- *   fill    if p0's cycle is shorter than N (periodic data such as b"A" * n, where T splits into many short cycles) the
- *           walk laps its cycle; the remaining output is the periodic continuation of the first lap.
+ * The walk is a dependent-load chain, so it is broken up by list ranking: every position that is a multiple of
+ * TRAV_SPACING is a "splitter", the stretch from one splitter to the next one met is a segment (geometric lengths, mean
+ * TRAV_SPACING), segments are walked independently and put in order afterwards.
+ *
+ *   bwtWalkKernel   ONE persistent grid for all blocks of the wave.  A random 4-byte read costs HBM a whole 128-byte
+ *                   line (measured: 114 B of DRAM traffic per entry when the T vectors of ~300 blocks are walked at
+ *                   once), but all 32 entries of a line are wanted eventually -- so the walk keeps the T vectors it
+ *                   is working on INSIDE L2: segments are handed out in block order from one global counter (a warp
+ *                   takes TRAV_CHUNK at a time, its lanes take the next one whenever they finish, nobody waits for a
+ *                   slow lane), and the number of threads in flight is chosen so that the blocks being walked --
+ *                   exponentially distributed behind the head of the queue with a mean of threads / segments per
+ *                   block = 5.4 blocks = 19 MB -- fit L2 several times over.  Every line is then fetched from HBM
+ *                   about once and hit 31 more times.
+ *                   The bytes a segment meets go to the segment's own slot (TRAV_SLOT_BYTES, four at a time);
+ *                   of a longer segment (1.8 %) only the position after TRAV_SLOT_BYTES steps is kept.
+ *   bwtOrderKernel  one CTA per block: the successor list of the <= 14063 segments is ranked in shared memory by
+ *                   pointer jumping (Wyllie), cut at the segment that passes through p0; that gives every segment on
+ *                   p0's cycle its output offset; each thread then copies its segments' slots to their places
+ *                   (aligned 4-byte stores) and re-walks what did not fit a slot.
+ *           fill    if p0's cycle is shorter than N (periodic data such as b"A" * n, where T splits into many short
+ *                   cycles) the walk laps its cycle; the remaining output is the periodic continuation of the first lap.
  * A block whose start cycle contains no splitter at all (only tiny cycles can) is walked serially by one thread.
  *
  * The output is the block's byte string BEFORE RLE1 undo ("prerle"), N bytes, written over the block's L buffer.
- * Algorithmic HBM traffic per block: 4N bytes of random 32-bit reads + N bytes staged, read back and written.
+ * Algorithmic HBM traffic per block: 4N bytes of T read once + N bytes staged, read back and written.
  */
 #include "common.cuh"
+
+#include <algorithm>
+#include <cstdlib>
 
 namespace ibz2
 {
 namespace
 {
-constexpr int TRAV_THREADS = 1024;
-constexpr uint32_t SPACING = 64;
-constexpr uint32_t SPACING_SHIFT = 6;
-constexpr uint32_t MAX_SEGMENTS = ( DBUF_SIZE + SPACING - 1 ) / SPACING; /* 14063 */
-constexpr uint32_t PER_THREAD = ( MAX_SEGMENTS + TRAV_THREADS - 1 ) / TRAV_THREADS;
+constexpr uint32_t SPACING = TRAV_SPACING;
+constexpr uint32_t SPACING_SHIFT = TRAV_SPACING_SHIFT;
+constexpr uint32_t MAX_SEGMENTS = TRAV_MAX_SEGMENTS;
+constexpr uint32_t SLOT = TRAV_SLOT_BYTES;
 constexpr uint32_t NIL = 0xFFFFU;
 constexpr uint32_t FULL = 0xFFFFFFFFU;
-constexpr uint32_t STAGE_CAP = TRAV_STAGE_CAP;   /* bytes of staging stream per thread */
 
-struct TraverseShared
+constexpr uint32_t TRAV_CHUNK = 64;                                              /* segments a warp takes at a time */
+constexpr uint32_t CHUNKS_PER_BLOCK = ( MAX_SEGMENTS + TRAV_CHUNK - 1U ) / TRAV_CHUNK;   /* 220 */
+constexpr int WALK_THREADS_DEFAULT = 512;                                        /* per SM */
+
+struct BlockStage
+{
+    uint8_t* slots;      /* [segment][SLOT] */
+    uint32_t* segLen;    /* steps from the segment's splitter to the next splitter */
+    uint32_t* ovfPos;    /* position reached after SLOT steps (only meaningful when segLen > SLOT) */
+    uint16_t* segJump;   /* the splitter (segment index) the segment ends at */
+};
+
+__device__ __forceinline__ BlockStage
+blockStage( uint8_t* stageAll, uint32_t block )
+{
+    uint8_t* const base = stageAll + TRAV_STAGE_HEADER + static_cast<uint64_t>( block ) * TRAV_STAGE_STRIDE;
+    BlockStage st;
+    st.slots = base;
+    st.segLen = reinterpret_cast<uint32_t*>( base + TRAV_LEN_OFFSET );
+    st.ovfPos = reinterpret_cast<uint32_t*>( base + TRAV_OVF_OFFSET );
+    st.segJump = reinterpret_cast<uint16_t*>( base + TRAV_JUMP_OFFSET );
+    return st;
+}
+
+/* ------------------------------------------------------------------ walk ------------------------------------ */
+__global__ void __launch_bounds__( 1024, 1 )
+bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ meta, uint8_t* __restrict__ stageAll,
+               uint32_t nblocks )
+{
+    uint32_t* const chunkCounter = reinterpret_cast<uint32_t*>( stageAll );
+    const uint32_t lane = threadIdx.x & 31U;
+    const uint32_t lowerLanes = ( 1U << lane ) - 1U;
+    const uint32_t totalChunks = nblocks * CHUNKS_PER_BLOCK;
+
+    /* the warp's pool (warp-uniform): segments poolNext .. poolEnd - 1 of block poolBlock */
+    uint32_t poolBlock = 0;
+    uint32_t poolNext = 0;
+    uint32_t poolEnd = 0;
+    uint32_t poolP0 = 0;
+    bool exhausted = false;
+
+    /* the lane's segment */
+    bool active = false;
+    const uint32_t* dbuf = nullptr;
+    uint32_t* slotWords = nullptr;
+    uint32_t myBlock = 0;
+    uint32_t s = 0;
+    uint32_t p0 = 0;
+    uint32_t pos = 0;
+    uint32_t steps = 0;
+    uint32_t acc = 0;
+
+    while ( true ) {
+        uint32_t need = __ballot_sync( FULL, !active );
+        while ( ( need != 0 ) && !exhausted ) {
+            if ( poolNext == poolEnd ) {
+                uint32_t c = 0;
+                if ( lane == 0 ) {
+                    c = atomicAdd( chunkCounter, 1U );
+                }
+                c = __shfl_sync( FULL, c, 0 );
+                if ( c >= totalChunks ) {
+                    exhausted = true;
+                    break;
+                }
+                const uint32_t b = c / CHUNKS_PER_BLOCK;
+                const uint32_t first = ( c - b * CHUNKS_PER_BLOCK ) * TRAV_CHUNK;
+                const BlockMeta& bm = meta[b];
+                if ( ( bm.status != IBZ2_ST_OK ) || ( bm.n == 0 ) ) {
+                    continue;
+                }
+                const uint32_t segments = ( bm.n + SPACING - 1U ) >> SPACING_SHIFT;
+                if ( first >= segments ) {
+                    continue;
+                }
+                poolBlock = b;
+                poolNext = first;
+                poolEnd = min( first + TRAV_CHUNK, segments );
+                poolP0 = bm.origPtr;
+            }
+            const uint32_t avail = poolEnd - poolNext;
+            const uint32_t rank = __popc( need & lowerLanes );
+            if ( ( ( ( need >> lane ) & 1U ) != 0 ) && ( rank < avail ) ) {
+                s = poolNext + rank;
+                myBlock = poolBlock;
+                p0 = poolP0;
+                dbuf = dbufAll + static_cast<uint64_t>( poolBlock ) * DBUF_STRIDE;
+                slotWords = reinterpret_cast<uint32_t*>( stageAll + TRAV_STAGE_HEADER
+                                                         + static_cast<uint64_t>( poolBlock ) * TRAV_STAGE_STRIDE
+                                                         + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT ) );
+                pos = s << SPACING_SHIFT;
+                steps = 0;
+                acc = 0;
+                active = true;
+            }
+            poolNext += min( avail, static_cast<uint32_t>( __popc( need ) ) );
+            need = __ballot_sync( FULL, !active );
+        }
+        if ( need == FULL ) {
+            break;   /* nothing left to hand out and nobody walking */
+        }
+        if ( active ) {
+            /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's
+             * ( T[k] << 8 ) | L[k], so the walk starts at origPtr itself and every load yields the output byte and the
+             * next position at once (the reference first hops to T[origPtr], bzip2.hpp:835-838). */
+            if ( pos == p0 ) {
+                meta[myBlock].travStar = static_cast<int32_t>( s );
+                meta[myBlock].travK = steps;
+            }
+            const uint32_t e = __ldcg( dbuf + pos );
+            acc |= ( e & 0xFFU ) << ( 8U * ( steps & 3U ) );
+            ++steps;
+            if ( ( steps & 3U ) == 0 ) {
+                if ( steps <= SLOT ) {
+                    slotWords[( steps >> 2 ) - 1U] = acc;
+                }
+                acc = 0;
+            }
+            pos = e >> 8;
+            if ( steps == SLOT ) {
+                blockStage( stageAll, myBlock ).ovfPos[s] = pos;
+            }
+            if ( ( pos & ( SPACING - 1U ) ) == 0 ) {
+                const BlockStage st = blockStage( stageAll, myBlock );
+                st.segJump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
+                st.segLen[s] = steps;
+                if ( ( ( steps & 3U ) != 0 ) && ( steps < SLOT ) ) {
+                    slotWords[steps >> 2] = acc;
+                }
+                active = false;
+            }
+        }
+    }
+}
+
+/* ------------------------------------------------------------------ order ----------------------------------- */
+constexpr int ORDER_THREADS = 1024;
+constexpr uint32_t PER_THREAD = ( MAX_SEGMENTS + ORDER_THREADS - 1 ) / ORDER_THREADS;
+
+struct OrderShared
 {
     uint32_t dist[MAX_SEGMENTS + 1];
     uint16_t jump[MAX_SEGMENTS + 1];
-    int sstar;
-    uint32_t kstar;
+    uint32_t cycleLen;
 };
 
-__global__ void __launch_bounds__( TRAV_THREADS, 2 )
-bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll,
-                   BlockMeta* __restrict__ meta, uint8_t* __restrict__ stageAll )
+/* len bytes of a segment: slot bytes srcFirst .. srcFirst + len - 1 -> prerle[dst ..], 4 bytes per store where aligned */
+__device__ __forceinline__ void
+copySlotBytes( const uint8_t* __restrict__ slot, uint32_t srcFirst, uint8_t* __restrict__ prerle, uint32_t dst,
+               uint32_t len )
+{
+    uint32_t k = 0;
+    while ( ( k < len ) && ( ( ( dst + k ) & 3U ) != 0 ) ) {
+        prerle[dst + k] = slot[srcFirst + k];
+        ++k;
+    }
+    if ( k + 4U <= len ) {
+        const uint32_t src = srcFirst + k;
+        const uint32_t* words = reinterpret_cast<const uint32_t*>( slot ) + ( src >> 2 );
+        const uint32_t shift = ( src & 3U ) * 8U;
+        uint32_t w0 = __ldcs( words );
+        for ( ; k + 4U <= len; k += 4U ) {
+            /* one word past the last byte wanted may be read: still inside the block's staging area */
+            const uint32_t w1 = __ldcs( ++words );
+            *reinterpret_cast<uint32_t*>( prerle + dst + k ) = __funnelshift_r( w0, w1, shift );
+            w0 = w1;
+        }
+    }
+    for ( ; k < len; ++k ) {
+        prerle[dst + k] = slot[srcFirst + k];
+    }
+}
+
+__global__ void __launch_bounds__( ORDER_THREADS, 2 )
+bwtOrderKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll, BlockMeta* __restrict__ meta,
+                uint8_t* __restrict__ stageAll )
 {
     extern __shared__ __align__( 16 ) uint8_t sharedRaw[];
-    TraverseShared& sh = *reinterpret_cast<TraverseShared*>( sharedRaw );
+    OrderShared& sh = *reinterpret_cast<OrderShared*>( sharedRaw );
 
     BlockMeta& bm = meta[blockIdx.x];
     if ( ( bm.status != IBZ2_ST_OK ) || ( bm.n == 0 ) ) {
@@ -61,61 +232,11 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
     const uint32_t n = bm.n;
     const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( blockIdx.x ) * DBUF_STRIDE;
     uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
+    const BlockStage st = blockStage( stageAll, blockIdx.x );
     const uint32_t tid = threadIdx.x;
     const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
-    uint8_t* const stageBlock = stageAll + static_cast<uint64_t>( blockIdx.x ) * TRAV_STAGE_STRIDE;
-    uint32_t* const myStage = reinterpret_cast<uint32_t*>( stageBlock + static_cast<uint64_t>( tid ) * STAGE_CAP );
-    uint16_t* const segLen = reinterpret_cast<uint16_t*>( stageBlock + static_cast<uint64_t>( TRAV_THREADS ) * STAGE_CAP );
-    /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's ( T[k] << 8 ) | L[k],
-     * so the walk starts at origPtr itself and every load yields the output byte and the next position at once
-     * (the reference first hops to T[origPtr], bzip2.hpp:835-838, and reads L at the position it arrives at). */
     const uint32_t p0 = bm.origPtr;
-
-    if ( tid == 0 ) {
-        sh.sstar = -1;
-        sh.kstar = 0;
-    }
-    __syncthreads();
-
-    /* ---- pass A: segment lengths and successors; the bytes go to the thread's staging stream ---- */
-    {
-        uint32_t s = tid;
-        uint32_t pos = s << SPACING_SHIFT;
-        uint32_t steps = 0;
-        uint32_t cursor = 0;   /* bytes this thread has met so far */
-        uint32_t acc = 0;
-        while ( s < segments ) {
-            if ( pos == p0 ) {
-                sh.sstar = static_cast<int>( s );
-                sh.kstar = steps;
-            }
-            const uint32_t e = __ldcg( dbuf + pos );
-            acc |= ( e & 0xFFU ) << ( 8U * ( cursor & 3U ) );
-            ++cursor;
-            if ( ( cursor & 3U ) == 0 ) {
-                if ( cursor <= STAGE_CAP ) {
-                    myStage[( cursor >> 2 ) - 1U] = acc;
-                }
-                acc = 0;
-            }
-            pos = e >> 8;
-            ++steps;
-            if ( ( pos & ( SPACING - 1 ) ) == 0 ) {
-                sh.jump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
-                sh.dist[s] = steps;
-                segLen[s] = static_cast<uint16_t>( min( steps, 0xFFFFU ) );
-                s += TRAV_THREADS;
-                pos = s << SPACING_SHIFT;
-                steps = 0;
-            }
-        }
-        if ( ( ( cursor & 3U ) != 0 ) && ( cursor < STAGE_CAP ) ) {
-            myStage[cursor >> 2] = acc;
-        }
-    }
-    __syncthreads();
-
-    const int sstar = sh.sstar;
+    const int sstar = bm.travStar;
     uint32_t cycleLen = 0;
 
     if ( sstar < 0 ) {
@@ -128,12 +249,17 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
                 prerle[k++] = static_cast<uint8_t>( e );
                 pos = e >> 8;
             } while ( ( pos != p0 ) && ( k < n ) );
-            sh.kstar = k;
+            sh.cycleLen = k;
         }
         __syncthreads();
-        cycleLen = sh.kstar;
+        cycleLen = sh.cycleLen;
     } else {
-        const uint32_t kstar = sh.kstar;
+        for ( uint32_t s = tid; s < segments; s += ORDER_THREADS ) {
+            sh.dist[s] = st.segLen[s];
+            sh.jump[s] = st.segJump[s];
+        }
+        __syncthreads();
+        const uint32_t kstar = bm.travK;
         const uint32_t lenStar = sh.dist[sstar];
         const uint32_t first = sh.jump[sstar];  /* the splitter reached from p0 */
         __syncthreads();
@@ -149,7 +275,7 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
             uint16_t newJump[PER_THREAD];
 #pragma unroll
             for ( uint32_t i = 0; i < PER_THREAD; ++i ) {
-                const uint32_t s = tid + i * TRAV_THREADS;
+                const uint32_t s = tid + i * ORDER_THREADS;
                 if ( s < segments ) {
                     const uint32_t j = sh.jump[s];
                     uint32_t d = sh.dist[s];
@@ -165,7 +291,7 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
             __syncthreads();
 #pragma unroll
             for ( uint32_t i = 0; i < PER_THREAD; ++i ) {
-                const uint32_t s = tid + i * TRAV_THREADS;
+                const uint32_t s = tid + i * ORDER_THREADS;
                 if ( s < segments ) {
                     sh.dist[s] = newDist[i];
                     sh.jump[s] = newJump[i];
@@ -178,54 +304,37 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
         const uint32_t ranked = sh.dist[first];            /* 0 when first == sstar */
         cycleLen = ranked + lenStar;
 
-        /* ---- copy: warp w moves the segments of its 32 threads from their staging streams to the output ---- */
-        {
-            const uint32_t lane = tid & 31U;
-            const uint32_t warpFirst = tid & ~31U;
-            uint32_t done = 0;   /* bytes of MY stream that belong to the segments handled so far */
-            for ( uint32_t sBase = warpFirst; sBase < segments; sBase += TRAV_THREADS ) {
-                /* the segments sBase .. sBase + 31 belong to lanes 0 .. 31 */
-                const uint32_t s = sBase + lane;
-                uint32_t len = 0;
-                uint32_t base = 0;
-                bool onCycle = false;   /* a segment that reaches sstar lies on p0's cycle */
-                if ( s < segments ) {
-                    len = segLen[s];
-                    onCycle = sh.jump[s] == NIL;
-                    base = tailLen + ranked - sh.dist[s];
-                }
-                const bool fits = ( len < 0xFFFFU ) && ( done + len <= STAGE_CAP );
-                const uint32_t srcOffset = ( tid << TRAV_STAGE_CAP_SHIFT ) + done;
-                done += len;
-                uint32_t todo = __ballot_sync( FULL, onCycle && fits && ( len > 0 ) );
-                while ( todo != 0 ) {
-                    const uint32_t src = static_cast<uint32_t>( __ffs( static_cast<int>( todo ) ) ) - 1U;
-                    todo &= todo - 1U;
-                    const uint32_t l = __shfl_sync( FULL, len, src );
-                    const uint32_t b = __shfl_sync( FULL, base, src );
-                    const uint32_t o = __shfl_sync( FULL, srcOffset, src );
-                    const bool star = static_cast<int>( sBase + src ) == sstar;
-                    for ( uint32_t k = lane; k < l; k += 32U ) {
-                        const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( b + k );
-                        if ( idx < n ) {
-                            prerle[idx] = stageBlock[o + k];
-                        }
+        /* ---- copy: every thread places its own segments ---- */
+        for ( uint32_t s = tid; s < segments; s += ORDER_THREADS ) {
+            if ( sh.jump[s] != NIL ) {
+                continue;   /* does not reach sstar: not on p0's cycle */
+            }
+            const uint32_t len = static_cast<int>( s ) == sstar ? lenStar : st.segLen[s];
+            const uint32_t base = tailLen + ranked - sh.dist[s];   /* output offset of the segment's first byte */
+            const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );
+            const uint32_t staged = min( len, SLOT );
+            if ( static_cast<int>( s ) == sstar ) {
+                /* steps kstar .. len - 1 open the output, steps 0 .. kstar - 1 close the lap */
+                for ( uint32_t k = 0; k < staged; ++k ) {
+                    const uint32_t idx = k >= kstar ? k - kstar : base + k;
+                    if ( idx < n ) {
+                        prerle[idx] = slot[k];
                     }
                 }
-                /* ---- pass B for the segments whose bytes did not fit the staging stream ---- */
-                if ( onCycle && !fits ) {
-                    const bool star = static_cast<int>( s ) == sstar;
-                    uint32_t pos = s << SPACING_SHIFT;
-                    uint32_t k = 0;
-                    do {
-                        const uint32_t e = __ldcg( dbuf + pos );
-                        const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( base + k );
-                        if ( idx < n ) {
-                            prerle[idx] = static_cast<uint8_t>( e );
-                        }
-                        pos = e >> 8;
-                        ++k;
-                    } while ( ( pos & ( SPACING - 1 ) ) != 0 );
+            } else if ( base < n ) {
+                copySlotBytes( slot, 0, prerle, base, min( staged, n - base ) );
+            }
+            if ( len > SLOT ) {
+                /* the rest of a long segment: walked again from where the slot ended */
+                const bool star = static_cast<int>( s ) == sstar;
+                uint32_t pos = st.ovfPos[s];
+                for ( uint32_t k = SLOT; k < len; ++k ) {
+                    const uint32_t e = __ldcg( dbuf + pos );
+                    const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( base + k );
+                    if ( idx < n ) {
+                        prerle[idx] = static_cast<uint8_t>( e );
+                    }
+                    pos = e >> 8;
                 }
             }
         }
@@ -234,7 +343,7 @@ bwtTraverseKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ p
 
     /* ---- periodic continuation when the start cycle is shorter than the block ---- */
     if ( cycleLen < n ) {
-        for ( uint32_t j = cycleLen + tid; j < n; j += TRAV_THREADS ) {
+        for ( uint32_t j = cycleLen + tid; j < n; j += ORDER_THREADS ) {
             prerle[j] = prerle[j % cycleLen];
         }
     }
@@ -248,8 +357,19 @@ void
 launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, uint8_t* stage,
                    cudaStream_t stream )
 {
-    cudaFuncSetAttribute( bwtTraverseKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          static_cast<int>( sizeof( TraverseShared ) ) );
-    bwtTraverseKernel<<<nblocks, TRAV_THREADS, sizeof( TraverseShared ), stream>>>( dbuf, prerle, meta, stage );
+    static const int walkThreads = [] () {
+        const char* const env = std::getenv( "IBZ2_WALK_THREADS" );
+        const int v = env != nullptr ? std::atoi( env ) : WALK_THREADS_DEFAULT;
+        return ( ( v >= 32 ) && ( v <= 1024 ) ) ? ( v / 32 ) * 32 : WALK_THREADS_DEFAULT;
+    }();
+    cudaMemsetAsync( stage, 0, sizeof( uint32_t ), stream );
+    /* small waves: no more warps than there are chunks of work */
+    const uint64_t chunks = static_cast<uint64_t>( nblocks ) * CHUNKS_PER_BLOCK;
+    const uint32_t ctas = static_cast<uint32_t>( std::min<uint64_t>( static_cast<uint64_t>( smCount() ),
+                                                                   ( chunks * 32U + walkThreads - 1U ) / walkThreads ) );
+    bwtWalkKernel<<<std::max( 1U, ctas ), walkThreads, 0, stream>>>( dbuf, meta, stage, nblocks );
+    cudaFuncSetAttribute( bwtOrderKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          static_cast<int>( sizeof( OrderShared ) ) );
+    bwtOrderKernel<<<nblocks, ORDER_THREADS, sizeof( OrderShared ), stream>>>( dbuf, prerle, meta, stage );
 }
 }  // namespace ibz2

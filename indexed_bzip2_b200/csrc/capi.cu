@@ -130,7 +130,7 @@ ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dDbuf, b * ibz2::DBUF_STRIDE * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dSelectors, b * ibz2::SEL_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dTables, b * sizeof( ibz2::BlockTables ) ) );
-    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dStage, b * ibz2::TRAV_STAGE_STRIDE ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dStage, ibz2::TRAV_STAGE_HEADER + b * ibz2::TRAV_STAGE_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dCounter, ( b + 16 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dWarpBase, b * ibz2::RLE_RANGES * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dPieceStart, ( b + 1 ) * sizeof( uint32_t ) ) );
@@ -555,7 +555,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
                                   ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
         we.e[4] = nextEvent( ctx );
-        ctx->timings.launches += 4 + ibz2::HUFFMAN_LAUNCHES;
+        ctx->timings.launches += 5 + ibz2::HUFFMAN_LAUNCHES;
         if ( haveOutput ) {
             ibz2::launchRleWrite( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, dOut, s );
             we.e[5] = nextEvent( ctx );

@@ -53,6 +53,8 @@ struct BlockMeta
     uint32_t cycleLen;    /* K4b: length of the permutation cycle through origPtr (diagnostic) */
     uint32_t writeOutput; /* scan: 1 when the block's bytes fit the output buffer */
     uint32_t nCoded;      /* K2b: Huffman symbols stored for K2c..K2e (run symbols and MTF symbols, without EOB) */
+    int32_t travStar;     /* K4b walk: the segment that passes through origPtr (-1: none), set to -1 by K2a */
+    uint32_t travK;       /* K4b walk: number of steps from that segment's start to origPtr */
 };
 
 /* ---- K2 intermediates (see huffman_header.cu / huffman_bits.cu / mtf.cu) ----
@@ -165,11 +167,21 @@ void launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, ui
 void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, uint32_t nblocks,
                        cudaStream_t stream );
 
-/* K4b staging: one stream of TRAV_STAGE_CAP bytes per thread of the block's CTA, then u16 segment lengths */
-constexpr uint32_t TRAV_STAGE_CAP_SHIFT = 11;
-constexpr uint32_t TRAV_STAGE_CAP = 1U << TRAV_STAGE_CAP_SHIFT;
-constexpr uint64_t TRAV_STAGE_STRIDE = 1024ULL * TRAV_STAGE_CAP + 32768ULL;
-/* stage: device u8[nblocks][TRAV_STAGE_STRIDE] */
+/* K4b staging, per block: one slot of TRAV_SLOT_BYTES per segment (the first bytes the segment's walk met), then per
+ * segment its length (u32), its successor segment (u16) and the position at which a walk longer than the slot goes on
+ * (u32).  The buffer starts with a TRAV_STAGE_HEADER holding the walk kernel's work counter. */
+constexpr uint32_t TRAV_SPACING_SHIFT = 6;
+constexpr uint32_t TRAV_SPACING = 1U << TRAV_SPACING_SHIFT;                    /* a splitter every 64 positions */
+constexpr uint32_t TRAV_MAX_SEGMENTS = ( DBUF_SIZE + TRAV_SPACING - 1U ) / TRAV_SPACING;   /* 14063 */
+constexpr uint32_t TRAV_SEG_CAP = ( TRAV_MAX_SEGMENTS + 63U ) & ~63U;          /* 14080 */
+constexpr uint32_t TRAV_SLOT_SHIFT = 8;
+constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 4 x the mean segment length */
+constexpr uint64_t TRAV_LEN_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;
+constexpr uint64_t TRAV_OVF_OFFSET = TRAV_LEN_OFFSET + TRAV_SEG_CAP * 4ULL;
+constexpr uint64_t TRAV_JUMP_OFFSET = TRAV_OVF_OFFSET + TRAV_SEG_CAP * 4ULL;
+constexpr uint64_t TRAV_STAGE_STRIDE = ( TRAV_JUMP_OFFSET + TRAV_SEG_CAP * 2ULL + 255ULL ) & ~255ULL;
+constexpr uint64_t TRAV_STAGE_HEADER = 256;
+/* stage: device u8[TRAV_STAGE_HEADER + nblocks * TRAV_STAGE_STRIDE] */
 void launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, uint8_t* stage,
                         cudaStream_t stream );
 

@@ -4,7 +4,7 @@
  *
  * The bit stream of a block is a dependent chain (window -> LUT -> code length -> shift); nothing inside one block can
  * shorten it, so the chip is filled with as many independent chains as shared memory allows:
- *   - every SM runs one persistent CTA of BITS_WARPS warps with BITS_LANES active lanes each = 32 decoders per SM;
+ *   - every SM runs one persistent CTA of 32 / BITS_LANES warps with BITS_LANES active lanes each = 32 decoders per SM;
  *   - the six 9-bit LUTs of a decoder's block (K2a's BlockTables::lut, 6 KB) sit in shared memory as
  *     u16 lut[index][table][slot]: the decoders of one warp are neighbouring slots, i.e. they read different
  *     banks whatever they look up, and an entry's address is one shift and one multiply-add away from the window;
@@ -24,15 +24,14 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace ibz2
 {
 namespace
 {
-constexpr int BITS_WARPS = 16;
-constexpr int BITS_LANES = 2;
-constexpr int BITS_SLOTS = BITS_WARPS * BITS_LANES;
-static_assert( BITS_SLOTS == 32, "the LUT rows are 32 decoders wide" );
+constexpr int BITS_SLOTS = 32;   /* decoders per SM: the LUT rows are 32 decoders wide */
+constexpr int BITS_LANES_DEFAULT = 2;   /* active lanes per warp; BITS_SLOTS / lanes warps per CTA */
 constexpr uint32_t LUT_ROW_BYTES = BITS_SLOTS * 2U;               /* one u16 per decoder */
 constexpr uint32_t LUT_IDX_STRIDE = MAX_GROUPS * LUT_ROW_BYTES;   /* u16 lut[index][table][decoder] */
 constexpr uint32_t LUT_ENTRIES = MAX_GROUPS * HUFF_LUT_SIZE;      /* 3072 rows */
@@ -160,12 +159,14 @@ decodeLongShared( uint32_t limAddr, uint32_t offAddr, uint32_t hi )
     return ( idx << 5 ) | len;
 }
 
-__global__ void __launch_bounds__( BITS_WARPS * 32, 1 )
+template<int BITS_LANES>
+__global__ void __launch_bounds__( ( BITS_SLOTS / BITS_LANES ) * 32, 1 )
 huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks,
                    const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
                    uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, uint32_t slotsPerCta )
 {
     extern __shared__ __align__( 16 ) uint8_t lutShared[];
+    constexpr int BITS_WARPS = BITS_SLOTS / BITS_LANES;
     const uint32_t lane = threadIdx.x & 31U;
     if ( lane >= static_cast<uint32_t>( BITS_LANES ) ) {
         return;
@@ -505,11 +506,18 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
                    const BlockTables* tables, uint32_t* scratch, uint32_t* counter, cudaStream_t stream )
 {
     const size_t shared = SH_TOTAL_BYTES;
-    cudaFuncSetAttribute( huffmanBitsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>( shared ) );
+    static const int lanes = [] () {
+        const char* const env = std::getenv( "IBZ2_K2B_LANES" );
+        const int v = env != nullptr ? std::atoi( env ) : BITS_LANES_DEFAULT;
+        return ( ( v == 1 ) || ( v == 2 ) || ( v == 4 ) || ( v == 8 ) ) ? v : BITS_LANES_DEFAULT;
+    }();
+    auto* const kernel = lanes == 1 ? huffmanBitsKernel<1> : lanes == 2 ? huffmanBitsKernel<2>
+                         : lanes == 4 ? huffmanBitsKernel<4> : huffmanBitsKernel<8>;
+    cudaFuncSetAttribute( kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>( shared ) );
     cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
     const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() ), nblocks ) );
     const uint32_t slotsPerCta = std::min<uint32_t>( BITS_SLOTS, ( nblocks + ctas - 1U ) / ctas );
-    huffmanBitsKernel<<<ctas, BITS_WARPS * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables,
+    kernel<<<ctas, ( BITS_SLOTS / lanes ) * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables,
                                                                  scratch, counter, slotsPerCta );
     const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
     resolveLongSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );

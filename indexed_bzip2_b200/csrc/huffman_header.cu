@@ -452,6 +452,8 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         bm.crcAcc = 0;
         bm.calcCrc = 0;
         bm.cycleLen = 0;
+        bm.travStar = -1;
+        bm.travK = 0;
         bm.writeOutput = 0;
         bm.outOffset = 0;
     }
