@@ -47,7 +47,8 @@ constexpr uint32_t FULL = 0xFFFFFFFFU;
 
 constexpr uint32_t TRAV_CHUNK = 64;                                              /* segments a warp takes at a time */
 constexpr uint32_t CHUNKS_PER_BLOCK = ( MAX_SEGMENTS + TRAV_CHUNK - 1U ) / TRAV_CHUNK;   /* 220 */
-constexpr int WALK_THREADS_DEFAULT = 512;                                        /* per SM */
+constexpr int WALK_THREADS_DEFAULT = 384;                                        /* per SM */
+constexpr uint32_t WALK_STEPS = 4;                                               /* steps per look at the pool */
 
 struct BlockStage
 {
@@ -146,35 +147,39 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
         if ( need == FULL ) {
             break;   /* nothing left to hand out and nobody walking */
         }
-        if ( active ) {
-            /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's
-             * ( T[k] << 8 ) | L[k], so the walk starts at origPtr itself and every load yields the output byte and the
-             * next position at once (the reference first hops to T[origPtr], bzip2.hpp:835-838). */
-            if ( pos == p0 ) {
-                meta[myBlock].travStar = static_cast<int32_t>( s );
-                meta[myBlock].travK = steps;
-            }
-            const uint32_t e = __ldcg( dbuf + pos );
-            acc |= ( e & 0xFFU ) << ( 8U * ( steps & 3U ) );
-            ++steps;
-            if ( ( steps & 3U ) == 0 ) {
-                if ( steps <= SLOT ) {
-                    slotWords[( steps >> 2 ) - 1U] = acc;
+        /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's
+         * ( T[k] << 8 ) | L[k], so the walk starts at origPtr itself and every load yields the output byte and the
+         * next position at once (the reference first hops to T[origPtr], bzip2.hpp:835-838).
+         * WALK_STEPS steps between two looks at the pool: a lane that finishes early idles for at most three steps. */
+#pragma unroll
+        for ( uint32_t u = 0; u < WALK_STEPS; ++u ) {
+            if ( active ) {
+                if ( pos == p0 ) {
+                    meta[myBlock].travStar = static_cast<int32_t>( s );
+                    meta[myBlock].travK = steps;
                 }
-                acc = 0;
-            }
-            pos = e >> 8;
-            if ( steps == SLOT ) {
-                blockStage( stageAll, myBlock ).ovfPos[s] = pos;
-            }
-            if ( ( pos & ( SPACING - 1U ) ) == 0 ) {
-                const BlockStage st = blockStage( stageAll, myBlock );
-                st.segJump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
-                st.segLen[s] = steps;
-                if ( ( ( steps & 3U ) != 0 ) && ( steps < SLOT ) ) {
-                    slotWords[steps >> 2] = acc;
+                const uint32_t e = __ldcg( dbuf + pos );
+                acc |= ( e & 0xFFU ) << ( 8U * ( steps & 3U ) );
+                ++steps;
+                if ( ( steps & 3U ) == 0 ) {
+                    if ( steps <= SLOT ) {
+                        slotWords[( steps >> 2 ) - 1U] = acc;
+                    }
+                    acc = 0;
                 }
-                active = false;
+                pos = e >> 8;
+                if ( steps == SLOT ) {
+                    blockStage( stageAll, myBlock ).ovfPos[s] = pos;
+                }
+                if ( ( pos & ( SPACING - 1U ) ) == 0 ) {
+                    const BlockStage st = blockStage( stageAll, myBlock );
+                    st.segJump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
+                    st.segLen[s] = steps;
+                    if ( ( ( steps & 3U ) != 0 ) && ( steps < SLOT ) ) {
+                        slotWords[steps >> 2] = acc;
+                    }
+                    active = false;
+                }
             }
         }
     }
@@ -205,10 +210,10 @@ copySlotBytes( const uint8_t* __restrict__ slot, uint32_t srcFirst, uint8_t* __r
         const uint32_t src = srcFirst + k;
         const uint32_t* words = reinterpret_cast<const uint32_t*>( slot ) + ( src >> 2 );
         const uint32_t shift = ( src & 3U ) * 8U;
-        uint32_t w0 = __ldcs( words );
+        uint32_t w0 = __ldg( words );
         for ( ; k + 4U <= len; k += 4U ) {
             /* one word past the last byte wanted may be read: still inside the block's staging area */
-            const uint32_t w1 = __ldcs( ++words );
+            const uint32_t w1 = __ldg( ++words );
             *reinterpret_cast<uint32_t*>( prerle + dst + k ) = __funnelshift_r( w0, w1, shift );
             w0 = w1;
         }

@@ -299,9 +299,11 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 const uint32_t limAddr = myLimAddr + table * ( LONG_LIMITS * BITS_SLOTS * 4U );
                 const uint32_t offAddr = myOffAddr + table * ( LONG_OFFSETS * BITS_SLOTS * 2U );
                 const uint32_t longTag = 0x8000U | ( table << 9 );
-                const uint32_t* wp = dataWords + d.wordIdx;
+                const uint32_t* const wbase = dataWords + d.wordIdx;
+                uint32_t wofs = 0;                                   /* words consumed in this group */
+                prefetchL1( wbase + 64 );                            /* stays inside the file: see GROUP_MAX_WORDS */
                 uint32_t raw0 = __byte_perm( d.nextW, 0, 0x0123 );   /* back to memory order: swapped when used */
-                uint32_t raw1 = __ldg( wp + 1 );
+                uint32_t raw1 = __ldg( wbase + 1 );
                 uint32_t hi = d.hi;
                 uint32_t lo = d.lo;
                 int nb = d.nb;
@@ -317,11 +319,8 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                         lo |= __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                         nb += rf ? 32 : 0;
                         raw0 = rf ? raw1 : raw0;
-                        wp += rf ? 1 : 0;
-                        raw1 = __ldg( wp + 1 );
-                        if ( rf && ( ( reinterpret_cast<uintptr_t>( wp ) & 127U ) == 0 ) ) {
-                            prefetchL1( wp + 64 );   /* stays inside the file: see GROUP_MAX_WORDS */
-                        }
+                        wofs += rf ? 1U : 0U;
+                        raw1 = __ldg( wbase + wofs + 1U );
                     }
                     /* at least 33 valid bits; a plain symbol takes at most 9 */
                     const uint32_t e0 = e;
@@ -346,8 +345,8 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                                 lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                                 nb += 32;
                                 raw0 = raw1;
-                                ++wp;
-                                raw1 = __ldg( wp + 1 );
+                                ++wofs;
+                                raw1 = __ldg( wbase + wofs + 1U );
                             }
                             uint32_t ee = lookup( tableAddr, hi );
                             uint32_t out = ee >> 5;
@@ -393,17 +392,17 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                             lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                             nb += 32;
                             raw0 = raw1;
-                            ++wp;
-                            raw1 = __ldg( wp + 1 );
+                            ++wofs;
+                            raw1 = __ldg( wbase + wofs + 1U );
                         }
                         e = lookup( tableAddr, hi );
                     }
                 }
-                /* the window holds wp[-2], wp[-1]; raw0 = wp[0]: hand the position back in file terms */
+                /* the window holds words [-2] and [-1] of wbase + wofs, raw0 = word [0]: hand the position back in file terms */
                 d.hi = hi;
                 d.lo = lo;
                 d.nb = nb;
-                d.wordIdx = static_cast<uint64_t>( wp - dataWords );
+                d.wordIdx += wofs;
                 d.nextW = __byte_perm( raw0, 0, 0x0123 );
                 if ( outcome == 0 ) {
                     nsym += GROUP_SIZE;
