@@ -10,6 +10,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace
@@ -22,6 +23,8 @@ struct ibz2_ctx
     int device = 0;
     int sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copyStream = nullptr;   /* device -> host copies of finished waves, overlapped with the next wave */
+    uint64_t* hRunning = nullptr;        /* pinned: output bytes produced up to the end of the last finished wave */
     std::string lastError;
     uint32_t batchBlocks = 0;
 
@@ -38,6 +41,7 @@ struct ibz2_ctx
     uint32_t* dPieceStart = nullptr;
     uint64_t* dRunning = nullptr;
     ibz2::BlockMeta* hMeta = nullptr; /* pinned, scratchBlocks entries */
+    uint32_t* hOrder = nullptr;       /* pinned, scratchBlocks entries: K2b's block order of the wave */
 
     /* staging for host-side inputs / outputs */
     uint8_t* dIn = nullptr;
@@ -104,6 +108,7 @@ freeScratch( ibz2_ctx* ctx )
     cudaFree( ctx->dWarpBase );
     cudaFree( ctx->dPieceStart );
     cudaFreeHost( ctx->hMeta );
+    cudaFreeHost( ctx->hOrder );
     ctx->dMeta = nullptr;
     ctx->dLbytes = nullptr;
     ctx->dDbuf = nullptr;
@@ -114,6 +119,7 @@ freeScratch( ibz2_ctx* ctx )
     ctx->dWarpBase = nullptr;
     ctx->dPieceStart = nullptr;
     ctx->hMeta = nullptr;
+    ctx->hOrder = nullptr;
     ctx->scratchBlocks = 0;
 }
 
@@ -135,6 +141,7 @@ ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dWarpBase, b * ibz2::RLE_RANGES * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dPieceStart, ( b + 1 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMallocHost( &ctx->hMeta, b * sizeof( ibz2::BlockMeta ) ) );
+    IBZ2_CUDA_CHECK( ctx, cudaMallocHost( &ctx->hOrder, b * sizeof( uint32_t ) ) );
     ctx->scratchBlocks = blocks;
     return IBZ2_OK;
 }
@@ -272,6 +279,8 @@ ibz2_create( int device, ibz2_ctx** out )
     if ( ( ( err = cudaSetDevice( device ) ) != cudaSuccess )
          || ( ( err = cudaGetDeviceProperties( &prop, device ) ) != cudaSuccess )
          || ( ( err = cudaStreamCreateWithFlags( &ctx->stream, cudaStreamNonBlocking ) ) != cudaSuccess )
+         || ( ( err = cudaStreamCreateWithFlags( &ctx->copyStream, cudaStreamNonBlocking ) ) != cudaSuccess )
+         || ( ( err = cudaMallocHost( &ctx->hRunning, 2 * sizeof( uint64_t ) ) ) != cudaSuccess )
          || ( ( err = cudaMalloc( &ctx->dRunning, 2 * sizeof( uint64_t ) ) ) != cudaSuccess ) ) {
         g_createError = std::string( "CUDA initialisation failed: " ) + cudaGetErrorString( err );
         delete ctx;
@@ -314,6 +323,10 @@ ibz2_destroy( ibz2_ctx* ctx )
     cudaFree( ctx->dFound );
     cudaFree( ctx->dFoundCount );
     cudaFree( ctx->dRunning );
+    cudaFreeHost( ctx->hRunning );
+    if ( ctx->copyStream != nullptr ) {
+        cudaStreamDestroy( ctx->copyStream );
+    }
     for ( cudaEvent_t e : ctx->events ) {
         cudaEventDestroy( e );
     }
@@ -499,10 +512,17 @@ findOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, uint32_t whi
 /* K2..K6 over device-resident input, in waves of at most ctx->batchBlocks blocks; dOut may be null (sizes only). */
 static int
 decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint64_t* offsets, uint64_t nblocks,
-                uint8_t* dOut, uint64_t outCapacity, ibz2_block_result* results, uint64_t* totalOut )
+                uint8_t* dOut, uint64_t outCapacity, ibz2_block_result* results, uint64_t* totalOut,
+                void* hostOut = nullptr )
 {
     const bool haveOutput = dOut != nullptr;
     uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
+    const bool pipelined = haveOutput && ( hostOut != nullptr );
+    if ( pipelined ) {
+        /* host output: waves of one K2b round, so that a finished wave travels to the host while the next one decodes */
+        wave = std::min( wave, ctx->batchBlocks / 2U );
+    }
+    uint64_t copied = 0;   /* output bytes already on their way to the host */
     if ( wave > ctx->scratchBlocks ) {
         /* scratch is about 6.7 MB per block in flight: stay inside what the device has left */
         size_t freeBytes = 0;
@@ -531,6 +551,14 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         const uint32_t count = static_cast<uint32_t>( std::min<uint64_t>( wave, nblocks - first ) );
         /* the previous wave's results must have left the pinned mirror before it is refilled */
         IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+        if ( pipelined && ( first > 0 ) ) {
+            const uint64_t produced = std::min<uint64_t>( ctx->hRunning[0], outCapacity );
+            if ( produced > copied ) {
+                IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( static_cast<uint8_t*>( hostOut ) + copied, dOut + copied, produced - copied,
+                                                       cudaMemcpyDeviceToHost, ctx->copyStream ) );
+                copied = produced;
+            }
+        }
         if ( first > 0 ) {
             for ( uint32_t i = 0; i < wave; ++i ) {
                 fillResult( ctx->hMeta[i], &results[first - wave + i] );
@@ -542,10 +570,29 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         }
         IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dMeta, ctx->hMeta, sizeof( ibz2::BlockMeta ) * count,
                                                cudaMemcpyHostToDevice, s ) );
+        {
+            /* K2b hands its decoders the blocks of the wave longest first (compressed size stands in for the symbol
+             * count, which nobody knows yet): one block is one sequential chain, so the wave ends when the decoder
+             * with the most work ends */
+            std::vector<std::pair<uint64_t, uint32_t>> bySize( count );
+            for ( uint32_t i = 0; i < count; ++i ) {
+                const uint64_t begin = offsets[first + i] & ~IBZ2_OFFSET_EOS_FLAG;
+                const uint64_t end = ( first + i + 1 < nblocks ) ? ( offsets[first + i + 1] & ~IBZ2_OFFSET_EOS_FLAG ) : nbytes * 8U;
+                bySize[i] = { end > begin ? end - begin : 0U, i };
+            }
+            std::sort( bySize.begin(), bySize.end(), [] ( const auto& a, const auto& b ) {
+                return ( a.first != b.first ) ? ( a.first > b.first ) : ( a.second < b.second );
+            } );
+            for ( uint32_t i = 0; i < count; ++i ) {
+                ctx->hOrder[i] = bySize[i].second;
+            }
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dCounter + ibz2::K2B_ORDER_OFFSET, ctx->hOrder, sizeof( uint32_t ) * count,
+                                                   cudaMemcpyHostToDevice, s ) );
+        }
         WaveEvents we{};
         we.e[0] = nextEvent( ctx );
         ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, ctx->dTables,
-                                   ctx->dDbuf, ctx->dCounter, s );
+                                   ctx->dDbuf, ctx->dCounter, true, s );
         we.e[1] = nextEvent( ctx );
         ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, count, s );
         we.e[2] = nextEvent( ctx );
@@ -570,6 +617,9 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
         IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ) * count,
                                                cudaMemcpyDeviceToHost, s ) );
+        if ( pipelined ) {
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hRunning, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
+        }
         waveEvents.push_back( we );
     }
     uint64_t total = 0;
@@ -583,6 +633,18 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         }
     }
     *totalOut = total;
+    if ( pipelined ) {
+        const cudaEvent_t e0 = nextEvent( ctx );   /* on the decode stream: what is left of the copy after the last kernel */
+        const uint64_t produced = std::min<uint64_t>( total, outCapacity );
+        if ( produced > copied ) {
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( static_cast<uint8_t*>( hostOut ) + copied, dOut + copied, produced - copied,
+                                                   cudaMemcpyDeviceToHost, ctx->copyStream ) );
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->copyStream ) );
+        const cudaEvent_t e1 = nextEvent( ctx );
+        IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
+        ctx->timings.d2h_ms = elapsed( e0, e1 );
+    }
     for ( const auto& we : waveEvents ) {
         ctx->timings.huffman_ms += elapsed( we.e[0], we.e[1] );
         ctx->timings.bwt_prepare_ms += elapsed( we.e[1], we.e[2] );
@@ -780,11 +842,9 @@ ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
         if ( rc != IBZ2_OK ) {
             return rc;
         }
-        rc = decodeOnDevice( ctx, dData, nbytes, mine.data(), mine.size(), dOut, out_capacity, results, &total );
-        if ( rc != IBZ2_OK ) {
-            return rc;
-        }
-        rc = copyOutputToHost( ctx, out, out_capacity, out_mem, total );
+        const bool toHost = ( out != nullptr ) && ( out_mem == IBZ2_MEM_HOST );
+        rc = decodeOnDevice( ctx, dData, nbytes, mine.data(), mine.size(), dOut, out_capacity, results, &total,
+                             toHost ? out : nullptr );
         if ( rc != IBZ2_OK ) {
             return rc;
         }
@@ -855,7 +915,7 @@ ibz2_debug_decode_block( ibz2_ctx* ctx, const void* data, uint64_t nbytes, uint6
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dMeta, ctx->hMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyHostToDevice, s ) );
 
     ibz2::launchHuffmanDecode( ctx->dIn, nbytes, ctx->dMeta, 1, ctx->dLbytes, ctx->dSelectors, ctx->dTables, ctx->dDbuf,
-                               ctx->dCounter, s );
+                               ctx->dCounter, false, s );
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyDeviceToHost, s ) );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
     IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );

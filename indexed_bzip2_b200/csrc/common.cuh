@@ -148,17 +148,19 @@ crcMulMod( uint32_t a, uint32_t b )
 void launchFindMagics( const uint8_t* data, uint64_t nbytes, uint32_t which, uint64_t* found, uint32_t* foundCount,
                        uint32_t capacity, cudaStream_t stream );
 
-/* K2a..K2e; tables: BlockTables[nblocks]; scratch: the dbuf slots; counter: device u32[2 + nblocks] work counters / hand-over list. */
+/* K2a..K2e; tables: BlockTables[nblocks]; scratch: the dbuf slots; counter: device u32[16 + nblocks]: [0] = K2b's work
+ * counter, [16 + i] = the block K2b's i-th request gets (longest compressed block first) when `ordered` is set. */
+constexpr uint32_t K2B_ORDER_OFFSET = 16;
 void launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* lbytes, uint8_t* selectors, BlockTables* tables, uint32_t* scratch,
-                          uint32_t* counter, cudaStream_t stream );
+                          uint32_t* counter, bool ordered, cudaStream_t stream );
 constexpr uint32_t HUFFMAN_LAUNCHES = 7;
 
 void launchHuffmanHeader( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* selectors, BlockTables* tables, cudaStream_t stream );
 void launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                         const uint8_t* selectors, const BlockTables* tables, uint32_t* scratch, uint32_t* counter,
-                        cudaStream_t stream );
+                        bool ordered, cudaStream_t stream );
 void launchHuffmanCareful( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* lbytes,
                            uint8_t* selectors, cudaStream_t stream );
 void launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_t* scratch, uint8_t* lbytes,

@@ -163,7 +163,8 @@ template<int BITS_LANES>
 __global__ void __launch_bounds__( ( BITS_SLOTS / BITS_LANES ) * 32, 1 )
 huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks,
                    const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
-                   uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, uint32_t slotsPerCta )
+                   uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, const uint32_t* __restrict__ order,
+                   uint32_t slotsPerCta )
 {
     extern __shared__ __align__( 16 ) uint8_t lutShared[];
     constexpr int BITS_WARPS = BITS_SLOTS / BITS_LANES;
@@ -204,6 +205,9 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             block = atomicAdd( counter, 1U );
             if ( block >= nblocks ) {
                 break;
+            }
+            if ( order != nullptr ) {
+                block = order[block];   /* longest block first: the decoders then finish at about the same time */
             }
             const BlockMeta& bm = meta[block];
             if ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) {
@@ -502,7 +506,7 @@ resolveLongSymbolsKernel( const BlockMeta* __restrict__ meta, const BlockTables*
 
 void
 launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, const uint8_t* selectors,
-                   const BlockTables* tables, uint32_t* scratch, uint32_t* counter, cudaStream_t stream )
+                   const BlockTables* tables, uint32_t* scratch, uint32_t* counter, bool ordered, cudaStream_t stream )
 {
     const size_t shared = SH_TOTAL_BYTES;
     static const int lanes = [] () {
@@ -517,7 +521,7 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
     const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() ), nblocks ) );
     const uint32_t slotsPerCta = std::min<uint32_t>( BITS_SLOTS, ( nblocks + ctas - 1U ) / ctas );
     kernel<<<ctas, ( BITS_SLOTS / lanes ) * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables,
-                                                                 scratch, counter, slotsPerCta );
+                                                                 scratch, counter, ordered ? counter + K2B_ORDER_OFFSET : nullptr, slotsPerCta );
     const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
     resolveLongSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
 }

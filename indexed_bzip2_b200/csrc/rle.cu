@@ -24,27 +24,32 @@ namespace
 {
 constexpr int RLE_THREADS = 1024;
 constexpr uint32_t FULL = 0xFFFFFFFFU;
-constexpr uint32_t IDENT = 0U | ( 1U << 3 ) | ( 2U << 6 ) | ( 3U << 9 ) | ( 4U << 12 );
-constexpr uint32_t STEP_NE = 1U | ( 1U << 3 ) | ( 1U << 6 ) | ( 1U << 9 ) | ( 0U << 12 );
-constexpr uint32_t STEP_EQ = 1U | ( 2U << 3 ) | ( 3U << 6 ) | ( 4U << 9 ) | ( 0U << 12 );
+/* a transfer function {0..4} -> {0..4} as five nibbles: nibble s = f( s ) */
+constexpr uint32_t IDENT = 0x43210U;
+constexpr uint32_t STEP_NE = 0x01111U;
+constexpr uint32_t STEP_EQ = 0x04321U;
 constexpr uint32_t COUNT_FLAG = 0x80000000U;
 
 __device__ __forceinline__ uint32_t
 applyFn( uint32_t f, uint32_t state )
 {
-    return ( f >> ( 3U * state ) ) & 7U;
+    return ( f >> ( 4U * state ) ) & 0xFU;
 }
 
-/* first f, then g */
+/* first f, then g.  g becomes a byte table ( g(0) .. g(3) | g(4) ), f's nibbles are exactly the selector of a byte
+ * permute that looks them up in it: ~15 instructions instead of five nested shift-and-mask lookups. */
 __device__ __forceinline__ uint32_t
 composeFn( uint32_t f, uint32_t g )
 {
-    uint32_t h = 0;
-#pragma unroll
-    for ( uint32_t s = 0; s < 5U; ++s ) {
-        h |= applyFn( g, applyFn( f, s ) ) << ( 3U * s );
-    }
-    return h;
+    uint32_t table = g & 0xFFFFU;
+    table = ( table | ( table << 8 ) ) & 0x00FF00FFU;
+    table = ( table | ( table << 4 ) ) & 0x0F0F0F0FU;
+    const uint32_t g4 = g >> 16;
+    uint32_t h = __byte_perm( table, g4, f );                        /* bytes g(f(0)) .. g(f(3)) */
+    const uint32_t h4 = __byte_perm( table, g4, f >> 16 ) & 0xFU;    /* g(f(4)) */
+    h = ( h | ( h >> 4 ) ) & 0x00FF00FFU;
+    h = ( h | ( h >> 8 ) ) & 0xFFFFU;
+    return h | ( h4 << 16 );
 }
 
 __device__ __forceinline__ uint32_t
