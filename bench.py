@@ -209,12 +209,18 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------------------
 
 STAGES = ["find_ms", "huffman_ms", "bwt_prepare_ms", "bwt_traverse_ms", "rle_scan_ms", "rle_write_ms", "crc_ms"]
+# timings that cover ONE kernel launch per wave (CUDA events on the library's stream around that launch): the roofline
+# is quoted for the slowest of these
+KERNELS = {"find_ms": "K1 findMagicsKernel", "huffman_bits_ms": "K2b huffmanBitsKernel (+ its 2 ms resolve pass)",
+           "bwt_prepare_ms": "K4a bwtPrepareKernel", "bwt_walk_ms": "K4b bwtWalkKernel", "rle_scan_ms": "K5a rleScanKernel",
+           "rle_write_ms": "K5b rleWriteKernel", "crc_ms": "K6 crcKernel"}
 
 
 def algorithmic_bytes(stage: str, c: int, n: int, u: int) -> int:
     """per-step algorithmic HBM bytes of each kernel (DESIGN.md "Kernels": SURVEY.md section 8(d) per-block figures
     x the blocks one step processes): C compressed bytes, N BWT symbols, U decoded bytes"""
-    return {"find_ms": c, "huffman_ms": c + n, "bwt_prepare_ms": 5 * n, "bwt_traverse_ms": 5 * n,
+    return {"find_ms": c, "huffman_ms": c + n, "huffman_bits_ms": c + 2 * n, "bwt_prepare_ms": 5 * n,
+            "bwt_traverse_ms": 5 * n, "bwt_walk_ms": 5 * n,
             "rle_scan_ms": 5 * n, "rle_write_ms": 5 * n + u, "crc_ms": u}[stage]
 
 
@@ -277,14 +283,14 @@ def run_ours(args):
         results, total = step_resident()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    stage_ms = {s: 0.0 for s in STAGES}
+    stage_ms = {s: 0.0 for s in STAGES + ["huffman_bits_ms", "bwt_walk_ms"]}
     launches = 0
     ctx.timer_start()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         results, total = step_resident()
         t = ctx.timings()
-        for s in STAGES:
+        for s in stage_ms:
             stage_ms[s] += t[s]
         launches += t["launches"]
     dev_ms = ctx.timer_stop()
@@ -359,12 +365,12 @@ def run_ours(args):
             peak, peak_src = float(json.loads(peaks_path.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
         else:
             peak, peak_src = 6650.0, "fallback of B200_PROFILING.md"
-        per_step = {s: stage_ms[s] / args.steps for s in STAGES}
-        dominant = max(per_step, key=per_step.get)
+        per_step = {s: stage_ms[s] / args.steps for s in stage_ms}
+        dominant = max(KERNELS, key=lambda k: per_step[k])
         waves = max(1, -(-len(results) // (args.batch_blocks or 148 * 64)))
         alg = algorithmic_bytes(dominant, my_c, n_symbols, int(total))
         achieved = alg / (per_step[dominant] * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": dominant.replace("_ms", ""), "achieved": round(achieved, 2), "peak": peak,
+        roofline = {"bound": "hbm", "kernel": KERNELS[dominant], "achieved": round(achieved, 2), "peak": peak,
                     "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None, "peak_source": peak_src,
                     "launches_per_step": waves, "ms_per_launch": round(per_step[dominant] / waves, 4),
                     "algorithmic_bytes_per_step": alg, "rank": 0,

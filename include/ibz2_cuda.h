@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define IBZ2_ABI_VERSION 1
+#define IBZ2_ABI_VERSION 2
 
 #define IBZ2_MAGIC_BLOCK 0x314159265359ULL /* indexed_bzip2/bzip2.hpp:103 */
 #define IBZ2_MAGIC_EOS   0x177245385090ULL /* indexed_bzip2/bzip2.hpp:104 */
@@ -109,6 +109,8 @@ typedef struct ibz2_timings {
     float d2h_ms;          /* device -> host copy of the decoded bytes (0 for device output) */
     float total_ms;        /* first event to last event of the call */
     uint64_t launches;     /* kernels launched by the call */
+    float huffman_bits_ms; /* K2b alone (the bit-serial symbol loop inside huffman_ms) */
+    float bwt_walk_ms;     /* the walk kernel alone (inside bwt_traverse_ms) */
 } ibz2_timings;
 
 typedef struct ibz2_ctx ibz2_ctx;

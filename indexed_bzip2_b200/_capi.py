@@ -50,7 +50,8 @@ assert BLOCK_RESULT_DTYPE.itemsize == C.sizeof(BlockResult)
 class Timings(C.Structure):
     _fields_ = [(n, C.c_float) for n in (
         "h2d_ms", "find_ms", "huffman_ms", "bwt_prepare_ms", "bwt_traverse_ms", "rle_scan_ms", "rle_write_ms",
-        "crc_ms", "d2h_ms", "total_ms")] + [("launches", C.c_uint64)]
+        "crc_ms", "d2h_ms", "total_ms")] + [("launches", C.c_uint64), ("huffman_bits_ms", C.c_float),
+                                             ("bwt_walk_ms", C.c_float)]
 
     def as_dict(self) -> dict:
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -128,7 +129,7 @@ def load_library() -> C.CDLL:
     L.ibz2_read_block_header.argtypes = [vp, u64, u64, C.POINTER(BlockResult)]
     L.ibz2_stream_crc_fold.restype = u32
     L.ibz2_stream_crc_fold.argtypes = [u32, u32]
-    if L.ibz2_abi_version() != 1:
+    if L.ibz2_abi_version() != 2:
         raise ImportError("libibz2_cuda.so has an unexpected ABI version")
     _lib = L
     return L

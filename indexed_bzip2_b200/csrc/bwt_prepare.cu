@@ -105,18 +105,27 @@ bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ 
     }
     __syncthreads();
 
-    /* ---- pass 1: byte histogram of the block (bzip2.hpp:759,788) ---- */
+    /* ---- pass 1: byte histogram of the block (bzip2.hpp:759,788) ----
+     * L is the last column of a BWT: equal bytes come in runs.  A lane adds the length of the run of equal bytes that
+     * starts at its word's byte k within the row of 32 words-at-k (heads found with one ballot), so a run costs one
+     * shared-memory add and scattered equal bytes only meet as ordinary same-address atomics. */
     for ( uint32_t base = 0; base < n; base += PREP_THREADS * 4U ) {
         const uint32_t i = base + tid * 4U;
         /* LBYTES_STRIDE pads the last word of a block */
         const uint32_t word = i < n ? *reinterpret_cast<const uint32_t*>( lbytes + i ) : 0U;
-#pragma unroll
-        for ( uint32_t k = 0; k < 4U; ++k ) {
-            const uint32_t key = ( i + k < n ) ? ( ( word >> ( 8U * k ) ) & 0xFFU ) : INVALID_KEY;
-            const uint32_t same = matchKey( key );
-            if ( ( key != INVALID_KEY ) && ( ( same & ltMask ) == 0 ) ) {
-                atomicAdd( &sh.blockHist[key], static_cast<uint32_t>( __popc( same ) ) );
+        /* the lane's four bytes are consecutive: count its own runs first, then merge equal neighbours across lanes */
+        uint32_t k = 0;
+        while ( k < 4U ) {
+            if ( i + k >= n ) {
+                break;
             }
+            const uint32_t key = ( word >> ( 8U * k ) ) & 0xFFU;
+            uint32_t len = 1;
+            while ( ( k + len < 4U ) && ( i + k + len < n ) && ( ( ( word >> ( 8U * ( k + len ) ) ) & 0xFFU ) == key ) ) {
+                ++len;
+            }
+            atomicAdd( &sh.blockHist[key], len );
+            k += len;
         }
     }
     __syncthreads();

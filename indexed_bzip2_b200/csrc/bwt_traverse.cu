@@ -43,6 +43,7 @@ constexpr uint32_t SPACING_SHIFT = TRAV_SPACING_SHIFT;
 constexpr uint32_t MAX_SEGMENTS = TRAV_MAX_SEGMENTS;
 constexpr uint32_t SLOT = TRAV_SLOT_BYTES;
 constexpr uint32_t NIL = 0xFFFFU;
+constexpr uint32_t NOT_ON_CYCLE = 0xFFFFFFFFU;
 constexpr uint32_t FULL = 0xFFFFFFFFU;
 
 constexpr uint32_t TRAV_CHUNK = 64;                                              /* segments a warp takes at a time */
@@ -56,6 +57,7 @@ struct BlockStage
     uint32_t* segLen;    /* steps from the segment's splitter to the next splitter */
     uint32_t* ovfPos;    /* position reached after SLOT steps (only meaningful when segLen > SLOT) */
     uint16_t* segJump;   /* the splitter (segment index) the segment ends at */
+    uint32_t* segBase;   /* bwtRankKernel: output offset of the segment's first byte, NOT_ON_CYCLE for the others */
 };
 
 __device__ __forceinline__ BlockStage
@@ -67,6 +69,7 @@ blockStage( uint8_t* stageAll, uint32_t block )
     st.segLen = reinterpret_cast<uint32_t*>( base + TRAV_LEN_OFFSET );
     st.ovfPos = reinterpret_cast<uint32_t*>( base + TRAV_OVF_OFFSET );
     st.segJump = reinterpret_cast<uint16_t*>( base + TRAV_JUMP_OFFSET );
+    st.segBase = reinterpret_cast<uint32_t*>( base + TRAV_BASE_OFFSET );
     return st;
 }
 
@@ -185,68 +188,40 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
     }
 }
 
-/* ------------------------------------------------------------------ order ----------------------------------- */
-constexpr int ORDER_THREADS = 1024;
-constexpr uint32_t PER_THREAD = ( MAX_SEGMENTS + ORDER_THREADS - 1 ) / ORDER_THREADS;
+/* ------------------------------------------------------------------ rank ------------------------------------ */
+constexpr int RANK_THREADS = 1024;
+constexpr uint32_t PER_THREAD = ( MAX_SEGMENTS + RANK_THREADS - 1 ) / RANK_THREADS;
 
-struct OrderShared
+struct RankShared
 {
     uint32_t dist[MAX_SEGMENTS + 1];
     uint16_t jump[MAX_SEGMENTS + 1];
     uint32_t cycleLen;
 };
 
-/* len bytes of a segment: slot bytes srcFirst .. srcFirst + len - 1 -> prerle[dst ..], 4 bytes per store where aligned */
-__device__ __forceinline__ void
-copySlotBytes( const uint8_t* __restrict__ slot, uint32_t srcFirst, uint8_t* __restrict__ prerle, uint32_t dst,
-               uint32_t len )
-{
-    uint32_t k = 0;
-    while ( ( k < len ) && ( ( ( dst + k ) & 3U ) != 0 ) ) {
-        prerle[dst + k] = slot[srcFirst + k];
-        ++k;
-    }
-    if ( k + 4U <= len ) {
-        const uint32_t src = srcFirst + k;
-        const uint32_t* words = reinterpret_cast<const uint32_t*>( slot ) + ( src >> 2 );
-        const uint32_t shift = ( src & 3U ) * 8U;
-        uint32_t w0 = __ldg( words );
-        for ( ; k + 4U <= len; k += 4U ) {
-            /* one word past the last byte wanted may be read: still inside the block's staging area */
-            const uint32_t w1 = __ldg( ++words );
-            *reinterpret_cast<uint32_t*>( prerle + dst + k ) = __funnelshift_r( w0, w1, shift );
-            w0 = w1;
-        }
-    }
-    for ( ; k < len; ++k ) {
-        prerle[dst + k] = slot[srcFirst + k];
-    }
-}
-
-__global__ void __launch_bounds__( ORDER_THREADS, 2 )
-bwtOrderKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll, BlockMeta* __restrict__ meta,
-                uint8_t* __restrict__ stageAll )
+__global__ void __launch_bounds__( RANK_THREADS, 2 )
+bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll, BlockMeta* __restrict__ meta,
+               uint8_t* __restrict__ stageAll )
 {
     extern __shared__ __align__( 16 ) uint8_t sharedRaw[];
-    OrderShared& sh = *reinterpret_cast<OrderShared*>( sharedRaw );
+    RankShared& sh = *reinterpret_cast<RankShared*>( sharedRaw );
 
     BlockMeta& bm = meta[blockIdx.x];
     if ( ( bm.status != IBZ2_ST_OK ) || ( bm.n == 0 ) ) {
         return;
     }
     const uint32_t n = bm.n;
-    const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( blockIdx.x ) * DBUF_STRIDE;
-    uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
     const BlockStage st = blockStage( stageAll, blockIdx.x );
     const uint32_t tid = threadIdx.x;
     const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
-    const uint32_t p0 = bm.origPtr;
     const int sstar = bm.travStar;
-    uint32_t cycleLen = 0;
 
     if ( sstar < 0 ) {
         /* no splitter on the start cycle: serial walk of one lap by one thread */
         if ( tid == 0 ) {
+            const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( blockIdx.x ) * DBUF_STRIDE;
+            uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
+            const uint32_t p0 = bm.origPtr;
             uint32_t pos = p0;
             uint32_t k = 0;
             do {
@@ -254,113 +229,186 @@ bwtOrderKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prer
                 prerle[k++] = static_cast<uint8_t>( e );
                 pos = e >> 8;
             } while ( ( pos != p0 ) && ( k < n ) );
-            sh.cycleLen = k;
+            bm.cycleLen = k;
         }
-        __syncthreads();
-        cycleLen = sh.cycleLen;
-    } else {
-        for ( uint32_t s = tid; s < segments; s += ORDER_THREADS ) {
-            sh.dist[s] = st.segLen[s];
-            sh.jump[s] = st.segJump[s];
-        }
-        __syncthreads();
-        const uint32_t kstar = bm.travK;
-        const uint32_t lenStar = sh.dist[sstar];
-        const uint32_t first = sh.jump[sstar];  /* the splitter reached from p0 */
-        __syncthreads();
-        if ( tid == 0 ) {
-            sh.jump[sstar] = NIL;
-            sh.dist[sstar] = 0;
-        }
-        __syncthreads();
+        return;
+    }
 
-        /* ---- pointer jumping: dist[s] = sum of the segment lengths from s up to (excluding) sstar ---- */
-        for ( uint32_t span = 1; span < segments; span <<= 1 ) {
-            uint32_t newDist[PER_THREAD];
-            uint16_t newJump[PER_THREAD];
+    for ( uint32_t s = tid; s < segments; s += RANK_THREADS ) {
+        sh.dist[s] = st.segLen[s];
+        sh.jump[s] = st.segJump[s];
+    }
+    __syncthreads();
+    const uint32_t kstar = bm.travK;
+    const uint32_t lenStar = sh.dist[sstar];
+    const uint32_t first = sh.jump[sstar];  /* the splitter reached from p0 */
+    __syncthreads();
+    if ( tid == 0 ) {
+        sh.jump[sstar] = NIL;
+        sh.dist[sstar] = 0;
+    }
+    __syncthreads();
+
+    /* ---- pointer jumping: dist[s] = sum of the segment lengths from s up to (excluding) sstar ---- */
+    for ( uint32_t span = 1; span < segments; span <<= 1 ) {
+        uint32_t newDist[PER_THREAD];
+        uint16_t newJump[PER_THREAD];
 #pragma unroll
-            for ( uint32_t i = 0; i < PER_THREAD; ++i ) {
-                const uint32_t s = tid + i * ORDER_THREADS;
-                if ( s < segments ) {
-                    const uint32_t j = sh.jump[s];
-                    uint32_t d = sh.dist[s];
-                    uint32_t nj = j;
-                    if ( j != NIL ) {
-                        d += sh.dist[j];
-                        nj = sh.jump[j];
-                    }
-                    newDist[i] = d;
-                    newJump[i] = static_cast<uint16_t>( nj );
+        for ( uint32_t i = 0; i < PER_THREAD; ++i ) {
+            const uint32_t s = tid + i * RANK_THREADS;
+            if ( s < segments ) {
+                const uint32_t j = sh.jump[s];
+                uint32_t d = sh.dist[s];
+                uint32_t nj = j;
+                if ( j != NIL ) {
+                    d += sh.dist[j];
+                    nj = sh.jump[j];
                 }
+                newDist[i] = d;
+                newJump[i] = static_cast<uint16_t>( nj );
             }
-            __syncthreads();
-#pragma unroll
-            for ( uint32_t i = 0; i < PER_THREAD; ++i ) {
-                const uint32_t s = tid + i * ORDER_THREADS;
-                if ( s < segments ) {
-                    sh.dist[s] = newDist[i];
-                    sh.jump[s] = newJump[i];
-                }
-            }
-            __syncthreads();
         }
-
-        const uint32_t tailLen = lenStar - kstar;          /* p0 .. end of sstar's segment, output offset 0 */
-        const uint32_t ranked = sh.dist[first];            /* 0 when first == sstar */
-        cycleLen = ranked + lenStar;
-
-        /* ---- copy: every thread places its own segments ---- */
-        for ( uint32_t s = tid; s < segments; s += ORDER_THREADS ) {
-            if ( sh.jump[s] != NIL ) {
-                continue;   /* does not reach sstar: not on p0's cycle */
-            }
-            const uint32_t len = static_cast<int>( s ) == sstar ? lenStar : st.segLen[s];
-            const uint32_t base = tailLen + ranked - sh.dist[s];   /* output offset of the segment's first byte */
-            const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );
-            const uint32_t staged = min( len, SLOT );
-            if ( static_cast<int>( s ) == sstar ) {
-                /* steps kstar .. len - 1 open the output, steps 0 .. kstar - 1 close the lap */
-                for ( uint32_t k = 0; k < staged; ++k ) {
-                    const uint32_t idx = k >= kstar ? k - kstar : base + k;
-                    if ( idx < n ) {
-                        prerle[idx] = slot[k];
-                    }
-                }
-            } else if ( base < n ) {
-                copySlotBytes( slot, 0, prerle, base, min( staged, n - base ) );
-            }
-            if ( len > SLOT ) {
-                /* the rest of a long segment: walked again from where the slot ended */
-                const bool star = static_cast<int>( s ) == sstar;
-                uint32_t pos = st.ovfPos[s];
-                for ( uint32_t k = SLOT; k < len; ++k ) {
-                    const uint32_t e = __ldcg( dbuf + pos );
-                    const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( base + k );
-                    if ( idx < n ) {
-                        prerle[idx] = static_cast<uint8_t>( e );
-                    }
-                    pos = e >> 8;
-                }
+        __syncthreads();
+#pragma unroll
+        for ( uint32_t i = 0; i < PER_THREAD; ++i ) {
+            const uint32_t s = tid + i * RANK_THREADS;
+            if ( s < segments ) {
+                sh.dist[s] = newDist[i];
+                sh.jump[s] = newJump[i];
             }
         }
         __syncthreads();
     }
 
-    /* ---- periodic continuation when the start cycle is shorter than the block ---- */
-    if ( cycleLen < n ) {
-        for ( uint32_t j = cycleLen + tid; j < n; j += ORDER_THREADS ) {
-            prerle[j] = prerle[j % cycleLen];
-        }
+    const uint32_t tailLen = lenStar - kstar;          /* p0 .. end of sstar's segment, output offset 0 */
+    const uint32_t ranked = sh.dist[first];            /* 0 when first == sstar */
+    for ( uint32_t s = tid; s < segments; s += RANK_THREADS ) {
+        /* a segment that reaches sstar lies on p0's cycle */
+        st.segBase[s] = sh.jump[s] == NIL ? tailLen + ranked - sh.dist[s] : NOT_ON_CYCLE;
     }
     if ( tid == 0 ) {
-        bm.cycleLen = cycleLen;
+        bm.cycleLen = ranked + lenStar;
+    }
+}
+
+/* ------------------------------------------------------------------ place ----------------------------------- */
+constexpr int PLACE_THREADS = 256;
+constexpr uint32_t PLACE_CTAS_PER_BLOCK = ( MAX_SEGMENTS + PLACE_THREADS - 1 ) / PLACE_THREADS;
+
+/* len staged bytes of a segment (slot is 256-byte aligned) -> dst[0 .. len): bytes up to the first 4-byte boundary of
+ * dst, then whole words put together from two neighbouring slot words, 64 slot bytes per round of loads. */
+__device__ __forceinline__ void
+placeStaged( const uint8_t* __restrict__ slot, uint8_t* __restrict__ dst, uint32_t len )
+{
+    const uint32_t* const slotWords = reinterpret_cast<const uint32_t*>( slot );
+    const uint4* const slotQuads = reinterpret_cast<const uint4*>( slot );
+    const uint32_t head = min( len, ( 4U - static_cast<uint32_t>( reinterpret_cast<uintptr_t>( dst ) & 3U ) ) & 3U );
+    const uint32_t w0 = __ldg( slotWords );
+    for ( uint32_t k = 0; k < head; ++k ) {
+        dst[k] = static_cast<uint8_t>( w0 >> ( 8U * k ) );
+    }
+    const uint32_t shift = 8U * head;
+    const uint32_t outWords = ( len - head ) >> 2;
+    uint32_t* const out = reinterpret_cast<uint32_t*>( dst + head );
+    for ( uint32_t done = 0; done < outWords; done += 16U ) {
+        /* slot words done .. done + 16; what lies behind the bytes wanted is never used (and still inside the block's
+         * staging area) */
+        uint32_t w[17];
+#pragma unroll
+        for ( uint32_t q = 0; q < 4U; ++q ) {
+            uint4 v = make_uint4( 0, 0, 0, 0 );
+            if ( done + 4U * q <= outWords ) {
+                v = __ldg( slotQuads + ( done >> 2 ) + q );
+            }
+            w[4U * q + 0U] = v.x;
+            w[4U * q + 1U] = v.y;
+            w[4U * q + 2U] = v.z;
+            w[4U * q + 3U] = v.w;
+        }
+        w[16] = ( done + 16U <= outWords ) ? __ldg( slotWords + done + 16U ) : 0U;
+#pragma unroll
+        for ( uint32_t i = 0; i < 16U; ++i ) {
+            if ( done + i < outWords ) {
+                out[done + i] = __funnelshift_r( w[i], w[i + 1U], shift );
+            }
+        }
+    }
+    for ( uint32_t k = head + 4U * outWords; k < len; ++k ) {
+        dst[k] = slot[k];
+    }
+}
+
+__global__ void __launch_bounds__( PLACE_THREADS )
+bwtPlaceKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll,
+                const BlockMeta* __restrict__ meta, uint8_t* __restrict__ stageAll )
+{
+    const uint32_t block = blockIdx.y;
+    const BlockMeta& bm = meta[block];
+    if ( ( bm.status != IBZ2_ST_OK ) || ( bm.n == 0 ) || ( bm.travStar < 0 ) ) {
+        return;
+    }
+    const uint32_t n = bm.n;
+    const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
+    const uint32_t s = blockIdx.x * PLACE_THREADS + threadIdx.x;
+    if ( s >= segments ) {
+        return;
+    }
+    const BlockStage st = blockStage( stageAll, block );
+    const uint32_t base = st.segBase[s];
+    if ( base == NOT_ON_CYCLE ) {
+        return;
+    }
+    const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( block ) * DBUF_STRIDE;
+    uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( block ) * LBYTES_STRIDE;
+    const uint32_t len = st.segLen[s];
+    const bool star = static_cast<int32_t>( s ) == bm.travStar;
+    const uint32_t kstar = bm.travK;
+    const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );
+    const uint32_t staged = min( len, SLOT );
+    if ( star ) {
+        /* steps kstar .. len - 1 open the output, steps 0 .. kstar - 1 close the lap */
+        for ( uint32_t k = 0; k < staged; ++k ) {
+            const uint32_t idx = k >= kstar ? k - kstar : base + k;
+            if ( idx < n ) {
+                prerle[idx] = slot[k];
+            }
+        }
+    } else if ( base < n ) {
+        placeStaged( slot, prerle + base, min( staged, n - base ) );
+    }
+    if ( len > SLOT ) {
+        /* the rest of a long segment: walked again from where the slot ended */
+        uint32_t pos = st.ovfPos[s];
+        for ( uint32_t k = SLOT; k < len; ++k ) {
+            const uint32_t e = __ldcg( dbuf + pos );
+            const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( base + k );
+            if ( idx < n ) {
+                prerle[idx] = static_cast<uint8_t>( e );
+            }
+            pos = e >> 8;
+        }
+    }
+}
+
+/* ---- periodic continuation when the start cycle is shorter than the block ---- */
+__global__ void __launch_bounds__( PLACE_THREADS )
+bwtFillKernel( uint8_t* __restrict__ prerleAll, const BlockMeta* __restrict__ meta )
+{
+    const BlockMeta& bm = meta[blockIdx.x];
+    if ( ( bm.status != IBZ2_ST_OK ) || ( bm.n == 0 ) || ( bm.cycleLen >= bm.n ) || ( bm.cycleLen == 0 ) ) {
+        return;
+    }
+    uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
+    const uint32_t cycleLen = bm.cycleLen;
+    for ( uint32_t j = cycleLen + threadIdx.x; j < bm.n; j += PLACE_THREADS ) {
+        prerle[j] = prerle[j % cycleLen];
     }
 }
 }  // namespace
 
 void
 launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, uint8_t* stage,
-                   cudaStream_t stream )
+                   cudaStream_t stream, cudaEvent_t walkStop )
 {
     static const int walkThreads = [] () {
         const char* const env = std::getenv( "IBZ2_WALK_THREADS" );
@@ -373,8 +421,13 @@ launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint3
     const uint32_t ctas = static_cast<uint32_t>( std::min<uint64_t>( static_cast<uint64_t>( smCount() ),
                                                                    ( chunks * 32U + walkThreads - 1U ) / walkThreads ) );
     bwtWalkKernel<<<std::max( 1U, ctas ), walkThreads, 0, stream>>>( dbuf, meta, stage, nblocks );
-    cudaFuncSetAttribute( bwtOrderKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          static_cast<int>( sizeof( OrderShared ) ) );
-    bwtOrderKernel<<<nblocks, ORDER_THREADS, sizeof( OrderShared ), stream>>>( dbuf, prerle, meta, stage );
+    if ( walkStop != nullptr ) {
+        cudaEventRecord( walkStop, stream );
+    }
+    cudaFuncSetAttribute( bwtRankKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          static_cast<int>( sizeof( RankShared ) ) );
+    bwtRankKernel<<<nblocks, RANK_THREADS, sizeof( RankShared ), stream>>>( dbuf, prerle, meta, stage );
+    bwtPlaceKernel<<<dim3( PLACE_CTAS_PER_BLOCK, nblocks ), PLACE_THREADS, 0, stream>>>( dbuf, prerle, meta, stage );
+    bwtFillKernel<<<nblocks, PLACE_THREADS, 0, stream>>>( prerle, meta );
 }
 }  // namespace ibz2

@@ -87,6 +87,18 @@ nextEvent( ibz2_ctx* ctx )
     return e;
 }
 
+/* an event of the pool that the callee records */
+cudaEvent_t
+spareEvent( ibz2_ctx* ctx )
+{
+    if ( ctx->eventsUsed == ctx->events.size() ) {
+        cudaEvent_t e;
+        cudaEventCreate( &e );
+        ctx->events.push_back( e );
+    }
+    return ctx->events[ctx->eventsUsed++];
+}
+
 float
 elapsed( cudaEvent_t a, cudaEvent_t b )
 {
@@ -544,7 +556,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
     cudaStream_t s = ctx->stream;
     IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
 
-    struct WaveEvents { cudaEvent_t e[7]; };
+    struct WaveEvents { cudaEvent_t e[7]; cudaEvent_t bits[2]; cudaEvent_t walk; };
     std::vector<WaveEvents> waveEvents;
 
     for ( uint64_t first = 0; first < nblocks; first += wave ) {
@@ -591,18 +603,21 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         }
         WaveEvents we{};
         we.e[0] = nextEvent( ctx );
+        we.bits[0] = spareEvent( ctx );
+        we.bits[1] = spareEvent( ctx );
+        we.walk = spareEvent( ctx );
         ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, ctx->dTables,
-                                   ctx->dDbuf, ctx->dCounter, true, s );
+                                   ctx->dDbuf, ctx->dCounter, true, s, we.bits[0], we.bits[1] );
         we.e[1] = nextEvent( ctx );
         ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, count, s );
         we.e[2] = nextEvent( ctx );
-        ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, ctx->dStage, s );
+        ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, ctx->dStage, s, we.walk );
         we.e[3] = nextEvent( ctx );
         ibz2::launchRleScan( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, s );
         ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
                                   ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
         we.e[4] = nextEvent( ctx );
-        ctx->timings.launches += 5 + ibz2::HUFFMAN_LAUNCHES;
+        ctx->timings.launches += 7 + ibz2::HUFFMAN_LAUNCHES;
         if ( haveOutput ) {
             ibz2::launchRleWrite( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, dOut, s );
             we.e[5] = nextEvent( ctx );
@@ -649,6 +664,8 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         ctx->timings.huffman_ms += elapsed( we.e[0], we.e[1] );
         ctx->timings.bwt_prepare_ms += elapsed( we.e[1], we.e[2] );
         ctx->timings.bwt_traverse_ms += elapsed( we.e[2], we.e[3] );
+        ctx->timings.huffman_bits_ms += elapsed( we.bits[0], we.bits[1] );
+        ctx->timings.bwt_walk_ms += elapsed( we.e[2], we.walk );
         ctx->timings.rle_scan_ms += elapsed( we.e[3], we.e[4] );
         if ( haveOutput ) {
             ctx->timings.rle_write_ms += elapsed( we.e[4], we.e[5] );

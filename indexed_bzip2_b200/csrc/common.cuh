@@ -153,7 +153,8 @@ void launchFindMagics( const uint8_t* data, uint64_t nbytes, uint32_t which, uin
 constexpr uint32_t K2B_ORDER_OFFSET = 16;
 void launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* lbytes, uint8_t* selectors, BlockTables* tables, uint32_t* scratch,
-                          uint32_t* counter, bool ordered, cudaStream_t stream );
+                          uint32_t* counter, bool ordered, cudaStream_t stream,
+                          cudaEvent_t bitsStart = nullptr, cudaEvent_t bitsStop = nullptr );   /* recorded around K2b */
 constexpr uint32_t HUFFMAN_LAUNCHES = 7;
 
 void launchHuffmanHeader( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
@@ -170,8 +171,8 @@ void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, u
                        cudaStream_t stream );
 
 /* K4b staging, per block: one slot of TRAV_SLOT_BYTES per segment (the first bytes the segment's walk met), then per
- * segment its length (u32), its successor segment (u16) and the position at which a walk longer than the slot goes on
- * (u32).  The buffer starts with a TRAV_STAGE_HEADER holding the walk kernel's work counter. */
+ * segment its length (u32), the position at which a walk longer than the slot goes on (u32), its successor segment
+ * (u16) and, after ranking, its output offset (u32).  The buffer starts with a TRAV_STAGE_HEADER holding the walk kernel's work counter. */
 constexpr uint32_t TRAV_SPACING_SHIFT = 6;
 constexpr uint32_t TRAV_SPACING = 1U << TRAV_SPACING_SHIFT;                    /* a splitter every 64 positions */
 constexpr uint32_t TRAV_MAX_SEGMENTS = ( DBUF_SIZE + TRAV_SPACING - 1U ) / TRAV_SPACING;   /* 14063 */
@@ -181,11 +182,12 @@ constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /
 constexpr uint64_t TRAV_LEN_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;
 constexpr uint64_t TRAV_OVF_OFFSET = TRAV_LEN_OFFSET + TRAV_SEG_CAP * 4ULL;
 constexpr uint64_t TRAV_JUMP_OFFSET = TRAV_OVF_OFFSET + TRAV_SEG_CAP * 4ULL;
-constexpr uint64_t TRAV_STAGE_STRIDE = ( TRAV_JUMP_OFFSET + TRAV_SEG_CAP * 2ULL + 255ULL ) & ~255ULL;
+constexpr uint64_t TRAV_BASE_OFFSET = TRAV_JUMP_OFFSET + TRAV_SEG_CAP * 2ULL;   /* u32: output offset of the segment's first byte */
+constexpr uint64_t TRAV_STAGE_STRIDE = ( TRAV_BASE_OFFSET + TRAV_SEG_CAP * 4ULL + 255ULL ) & ~255ULL;
 constexpr uint64_t TRAV_STAGE_HEADER = 256;
 /* stage: device u8[TRAV_STAGE_HEADER + nblocks * TRAV_STAGE_STRIDE] */
 void launchBwtTraverse( const uint32_t* dbuf, uint8_t* prerle, BlockMeta* meta, uint32_t nblocks, uint8_t* stage,
-                        cudaStream_t stream );
+                        cudaStream_t stream, cudaEvent_t walkStop = nullptr );   /* recorded after the walk kernel */
 
 void launchRleScan( const uint8_t* prerle, uint32_t* offsets, uint32_t* warpBase, BlockMeta* meta,
                     uint32_t nblocks, cudaStream_t stream );

@@ -431,10 +431,17 @@ launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_
 
 void
 launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* lbytes,
-                     uint8_t* selectors, BlockTables* tables, uint32_t* scratch, uint32_t* counter, bool ordered, cudaStream_t stream )
+                     uint8_t* selectors, BlockTables* tables, uint32_t* scratch, uint32_t* counter, bool ordered, cudaStream_t stream,
+                     cudaEvent_t bitsStart, cudaEvent_t bitsStop )
 {
     launchHuffmanHeader( data, nbytes, meta, nblocks, selectors, tables, stream );
+    if ( bitsStart != nullptr ) {
+        cudaEventRecord( bitsStart, stream );
+    }
     launchHuffmanBits( data, nbytes, meta, nblocks, selectors, tables, scratch, counter, ordered, stream );
+    if ( bitsStop != nullptr ) {
+        cudaEventRecord( bitsStop, stream );
+    }
     launchMtf( meta, nblocks, tables, scratch, lbytes, stream );
     launchHuffmanCareful( data, nbytes, meta, nblocks, lbytes, selectors, stream );
 }
