@@ -93,7 +93,8 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
     /* the lane's segment */
     bool active = false;
     const uint32_t* dbuf = nullptr;
-    uint32_t* slotWords = nullptr;
+    uint4* slotQuads = nullptr;
+    uint4 quad = make_uint4( 0, 0, 0, 0 );
     uint32_t myBlock = 0;
     uint32_t s = 0;
     uint32_t p0 = 0;
@@ -136,7 +137,7 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
                 myBlock = poolBlock;
                 p0 = poolP0;
                 dbuf = dbufAll + static_cast<uint64_t>( poolBlock ) * DBUF_STRIDE;
-                slotWords = reinterpret_cast<uint32_t*>( stageAll + TRAV_STAGE_HEADER
+                slotQuads = reinterpret_cast<uint4*>( stageAll + TRAV_STAGE_HEADER
                                                          + static_cast<uint64_t>( poolBlock ) * TRAV_STAGE_STRIDE
                                                          + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT ) );
                 pos = s << SPACING_SHIFT;
@@ -165,8 +166,15 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
                 acc |= ( e & 0xFFU ) << ( 8U * ( steps & 3U ) );
                 ++steps;
                 if ( ( steps & 3U ) == 0 ) {
-                    if ( steps <= SLOT ) {
-                        slotWords[( steps >> 2 ) - 1U] = acc;
+                    /* four words make one 16-byte streaming store: the slots are written once and read once, they
+                     * should not push T vectors out of L2 */
+                    const uint32_t w = ( ( steps >> 2 ) - 1U ) & 3U;
+                    quad.x = w == 0 ? acc : quad.x;
+                    quad.y = w == 1 ? acc : quad.y;
+                    quad.z = w == 2 ? acc : quad.z;
+                    quad.w = w == 3 ? acc : quad.w;
+                    if ( ( w == 3 ) && ( steps <= SLOT ) ) {
+                        __stcs( slotQuads + ( steps >> 4 ) - 1U, quad );
                     }
                     acc = 0;
                 }
@@ -178,8 +186,14 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
                     const BlockStage st = blockStage( stageAll, myBlock );
                     st.segJump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
                     st.segLen[s] = steps;
-                    if ( ( ( steps & 3U ) != 0 ) && ( steps < SLOT ) ) {
-                        slotWords[steps >> 2] = acc;
+                    if ( ( ( steps & 15U ) != 0 ) && ( steps < SLOT ) ) {
+                        /* the last, partly filled quad (what lies behind the segment's bytes is never read) */
+                        const uint32_t w = ( steps >> 2 ) & 3U;
+                        quad.x = w == 0 ? acc : quad.x;
+                        quad.y = w == 1 ? acc : quad.y;
+                        quad.z = w == 2 ? acc : quad.z;
+                        quad.w = w == 3 ? acc : quad.w;
+                        __stcs( slotQuads + ( steps >> 4 ), quad );
                     }
                     active = false;
                 }
