@@ -7,7 +7,9 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <new>
 #include <string>
 #include <utility>
@@ -24,6 +26,10 @@ struct ibz2_ctx
     int sms = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copyStream = nullptr;   /* device -> host copies of finished waves, overlapped with the next wave */
+    cudaStream_t inStream = nullptr;     /* host -> device copy of the second half of the input, overlapped with wave 1 */
+    cudaEvent_t inFirstHalf = nullptr;
+    cudaEvent_t inSecondHalf = nullptr;
+    uint64_t pipelineCopied = 0;         /* output bytes already on their way to the host (split-input calls) */
     uint64_t* hRunning = nullptr;        /* pinned: output bytes produced up to the end of the last finished wave */
     std::string lastError;
     uint32_t batchBlocks = 0;
@@ -292,7 +298,10 @@ ibz2_create( int device, ibz2_ctx** out )
          || ( ( err = cudaGetDeviceProperties( &prop, device ) ) != cudaSuccess )
          || ( ( err = cudaStreamCreateWithFlags( &ctx->stream, cudaStreamNonBlocking ) ) != cudaSuccess )
          || ( ( err = cudaStreamCreateWithFlags( &ctx->copyStream, cudaStreamNonBlocking ) ) != cudaSuccess )
-         || ( ( err = cudaMallocHost( &ctx->hRunning, 2 * sizeof( uint64_t ) ) ) != cudaSuccess )
+         || ( ( err = cudaStreamCreateWithFlags( &ctx->inStream, cudaStreamNonBlocking ) ) != cudaSuccess )
+         || ( ( err = cudaEventCreateWithFlags( &ctx->inFirstHalf, cudaEventDefault ) ) != cudaSuccess )
+         || ( ( err = cudaEventCreateWithFlags( &ctx->inSecondHalf, cudaEventDefault ) ) != cudaSuccess )
+         || ( ( err = cudaMallocHost( &ctx->hRunning, 16 * sizeof( uint64_t ) ) ) != cudaSuccess )
          || ( ( err = cudaMalloc( &ctx->dRunning, 2 * sizeof( uint64_t ) ) ) != cudaSuccess ) ) {
         g_createError = std::string( "CUDA initialisation failed: " ) + cudaGetErrorString( err );
         delete ctx;
@@ -338,6 +347,15 @@ ibz2_destroy( ibz2_ctx* ctx )
     cudaFreeHost( ctx->hRunning );
     if ( ctx->copyStream != nullptr ) {
         cudaStreamDestroy( ctx->copyStream );
+    }
+    if ( ctx->inStream != nullptr ) {
+        cudaStreamDestroy( ctx->inStream );
+    }
+    if ( ctx->inFirstHalf != nullptr ) {
+        cudaEventDestroy( ctx->inFirstHalf );
+    }
+    if ( ctx->inSecondHalf != nullptr ) {
+        cudaEventDestroy( ctx->inSecondHalf );
     }
     for ( cudaEvent_t e : ctx->events ) {
         cudaEventDestroy( e );
@@ -525,16 +543,15 @@ findOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, uint32_t whi
 static int
 decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint64_t* offsets, uint64_t nblocks,
                 uint8_t* dOut, uint64_t outCapacity, ibz2_block_result* results, uint64_t* totalOut,
-                void* hostOut = nullptr )
+                void* hostOut = nullptr, bool continueOutput = false, bool finishCopy = true,
+                const std::function<int()>* afterFirstUpload = nullptr )
 {
     const bool haveOutput = dOut != nullptr;
     uint32_t wave = static_cast<uint32_t>( std::min<uint64_t>( nblocks, ctx->batchBlocks ) );
     const bool pipelined = haveOutput && ( hostOut != nullptr );
-    if ( pipelined ) {
-        /* host output: waves of one K2b round, so that a finished wave travels to the host while the next one decodes */
-        wave = std::min( wave, ctx->batchBlocks / 2U );
-    }
-    uint64_t copied = 0;   /* output bytes already on their way to the host */
+    /* output bytes already on their way to the host; a split-input call decodes its halves with two calls of this
+     * function that share one output: the second goes on where the first stopped */
+    uint64_t copied = continueOutput ? ctx->pipelineCopied : 0;
     if ( wave > ctx->scratchBlocks ) {
         /* scratch is about 6.7 MB per block in flight: stay inside what the device has left */
         size_t freeBytes = 0;
@@ -554,16 +571,19 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         }
     }
     cudaStream_t s = ctx->stream;
-    IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
+    if ( !continueOutput ) {
+        IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
+    }
 
     struct WaveEvents { cudaEvent_t e[7]; cudaEvent_t bits[2]; cudaEvent_t walk; };
-    std::vector<WaveEvents> waveEvents;
+    std::vector<WaveEvents> waveEvents;   /* K2 per wave: e[0], e[1], bits */
+    std::vector<WaveEvents> subEvents;    /* K4..K6 per sub-wave: e[1]..e[6], walk */
 
     for ( uint64_t first = 0; first < nblocks; first += wave ) {
         const uint32_t count = static_cast<uint32_t>( std::min<uint64_t>( wave, nblocks - first ) );
         /* the previous wave's results must have left the pinned mirror before it is refilled */
         IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
-        if ( pipelined && ( first > 0 ) ) {
+        if ( pipelined && ( ( first > 0 ) || continueOutput ) ) {
             const uint64_t produced = std::min<uint64_t>( ctx->hRunning[0], outCapacity );
             if ( produced > copied ) {
                 IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( static_cast<uint8_t*>( hostOut ) + copied, dOut + copied, produced - copied,
@@ -601,33 +621,81 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
             IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dCounter + ibz2::K2B_ORDER_OFFSET, ctx->hOrder, sizeof( uint32_t ) * count,
                                                    cudaMemcpyHostToDevice, s ) );
         }
+        if ( ( first == 0 ) && ( afterFirstUpload != nullptr ) ) {
+            /* bulk host -> device traffic of the caller goes behind this wave's own small uploads in the copy engine's
+             * queue, not in front of them */
+            const int rc = ( *afterFirstUpload )();
+            if ( rc != IBZ2_OK ) {
+                return rc;
+            }
+        }
         WaveEvents we{};
         we.e[0] = nextEvent( ctx );
         we.bits[0] = spareEvent( ctx );
         we.bits[1] = spareEvent( ctx );
-        we.walk = spareEvent( ctx );
         ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, ctx->dTables,
                                    ctx->dDbuf, ctx->dCounter, true, s, we.bits[0], we.bits[1] );
         we.e[1] = nextEvent( ctx );
-        ibz2::launchBwtPrepare( ctx->dLbytes, ctx->dDbuf, ctx->dMeta, count, s );
-        we.e[2] = nextEvent( ctx );
-        ibz2::launchBwtTraverse( ctx->dDbuf, ctx->dLbytes, ctx->dMeta, count, ctx->dStage, s, we.walk );
-        we.e[3] = nextEvent( ctx );
-        ibz2::launchRleScan( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, s );
-        ibz2::launchOutputLayout( ctx->dMeta, count, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
-                                  ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
-        we.e[4] = nextEvent( ctx );
-        ctx->timings.launches += 7 + ibz2::HUFFMAN_LAUNCHES;
-        if ( haveOutput ) {
-            ibz2::launchRleWrite( ctx->dLbytes, ctx->dDbuf, ctx->dWarpBase, ctx->dMeta, count, dOut, s );
-            we.e[5] = nextEvent( ctx );
-            ibz2::launchCrc( dOut, ctx->dMeta, count, ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
-            ibz2::launchCrcFinalize( dOut, ctx->dMeta, count, s );
-            we.e[6] = nextEvent( ctx );
-            ctx->timings.launches += 3;
-        } else {
-            we.e[5] = we.e[4];
-            we.e[6] = we.e[4];
+        waveEvents.push_back( we );
+        ctx->timings.launches += ibz2::HUFFMAN_LAUNCHES;
+
+        /* K4..K6 in sub-waves: with host output a finished sub-wave travels while the next one is computed, and the part
+         * of the copy that nothing hides shrinks to one sub-wave */
+        const uint32_t sub = pipelined ? std::max<uint32_t>( 1U, std::min<uint32_t>( count, ctx->batchBlocks / 8U ) ) : count;
+        cudaEvent_t previousDone = nullptr;
+        uint32_t previousSlot = 0;
+        uint32_t k = 0;
+        for ( uint32_t subFirst = 0; subFirst < count; subFirst += sub, ++k ) {
+            const uint32_t subCount = std::min<uint32_t>( sub, count - subFirst );
+            ibz2::BlockMeta* const meta = ctx->dMeta + subFirst;
+            uint8_t* const lbytes = ctx->dLbytes + static_cast<uint64_t>( subFirst ) * ibz2::LBYTES_STRIDE;
+            uint32_t* const dbuf = ctx->dDbuf + static_cast<uint64_t>( subFirst ) * ibz2::DBUF_STRIDE;
+            /* the walk's work counter sits in the 256 bytes in front of the first block's staging area: for a later
+             * sub-wave that is the (no longer needed) tail of its predecessor's */
+            uint8_t* const stage = ctx->dStage + static_cast<uint64_t>( subFirst ) * ibz2::TRAV_STAGE_STRIDE;
+            uint32_t* const warpBase = ctx->dWarpBase + static_cast<uint64_t>( subFirst ) * ibz2::RLE_RANGES;
+            WaveEvents se{};
+            se.e[1] = nextEvent( ctx );
+            se.walk = spareEvent( ctx );
+            ibz2::launchBwtPrepare( lbytes, dbuf, meta, subCount, s );
+            se.e[2] = nextEvent( ctx );
+            ibz2::launchBwtTraverse( dbuf, lbytes, meta, subCount, stage, s, se.walk );
+            se.e[3] = nextEvent( ctx );
+            ibz2::launchRleScan( lbytes, dbuf, warpBase, meta, subCount, s );
+            ibz2::launchOutputLayout( meta, subCount, ctx->dRunning, outCapacity, haveOutput ? 1 : 0,
+                                      ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
+            se.e[4] = nextEvent( ctx );
+            ctx->timings.launches += 7;
+            if ( haveOutput ) {
+                ibz2::launchRleWrite( lbytes, dbuf, warpBase, meta, subCount, dOut, s );
+                se.e[5] = nextEvent( ctx );
+                ibz2::launchCrc( dOut, meta, subCount, ctx->dPieceStart, ibz2::CRC_PIECE_BYTES, s );
+                ibz2::launchCrcFinalize( dOut, meta, subCount, s );
+                se.e[6] = nextEvent( ctx );
+                ctx->timings.launches += 3;
+            } else {
+                se.e[5] = se.e[4];
+                se.e[6] = se.e[4];
+            }
+            subEvents.push_back( se );
+            if ( pipelined ) {
+                /* the host learns how far the output has grown; it looks only after the NEXT sub-wave is queued */
+                const uint32_t slot = 1U + ( k % 8U );
+                IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hRunning + slot, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
+                const cudaEvent_t done = spareEvent( ctx );
+                IBZ2_CUDA_CHECK( ctx, cudaEventRecord( done, s ) );
+                if ( previousDone != nullptr ) {
+                    IBZ2_CUDA_CHECK( ctx, cudaEventSynchronize( previousDone ) );
+                    const uint64_t produced = std::min<uint64_t>( ctx->hRunning[previousSlot], outCapacity );
+                    if ( produced > copied ) {
+                        IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( static_cast<uint8_t*>( hostOut ) + copied, dOut + copied, produced - copied,
+                                                               cudaMemcpyDeviceToHost, ctx->copyStream ) );
+                        copied = produced;
+                    }
+                }
+                previousDone = done;
+                previousSlot = slot;
+            }
         }
         IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
         IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ) * count,
@@ -635,7 +703,6 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         if ( pipelined ) {
             IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hRunning, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
         }
-        waveEvents.push_back( we );
     }
     uint64_t total = 0;
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( &total, ctx->dRunning, sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) );
@@ -648,7 +715,8 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         }
     }
     *totalOut = total;
-    if ( pipelined ) {
+    ctx->pipelineCopied = copied;
+    if ( pipelined && finishCopy ) {
         const cudaEvent_t e0 = nextEvent( ctx );   /* on the decode stream: what is left of the copy after the last kernel */
         const uint64_t produced = std::min<uint64_t>( total, outCapacity );
         if ( produced > copied ) {
@@ -662,14 +730,16 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
     }
     for ( const auto& we : waveEvents ) {
         ctx->timings.huffman_ms += elapsed( we.e[0], we.e[1] );
-        ctx->timings.bwt_prepare_ms += elapsed( we.e[1], we.e[2] );
-        ctx->timings.bwt_traverse_ms += elapsed( we.e[2], we.e[3] );
         ctx->timings.huffman_bits_ms += elapsed( we.bits[0], we.bits[1] );
-        ctx->timings.bwt_walk_ms += elapsed( we.e[2], we.walk );
-        ctx->timings.rle_scan_ms += elapsed( we.e[3], we.e[4] );
+    }
+    for ( const auto& se : subEvents ) {
+        ctx->timings.bwt_prepare_ms += elapsed( se.e[1], se.e[2] );
+        ctx->timings.bwt_traverse_ms += elapsed( se.e[2], se.e[3] );
+        ctx->timings.bwt_walk_ms += elapsed( se.e[2], se.walk );
+        ctx->timings.rle_scan_ms += elapsed( se.e[3], se.e[4] );
         if ( haveOutput ) {
-            ctx->timings.rle_write_ms += elapsed( we.e[4], we.e[5] );
-            ctx->timings.crc_ms += elapsed( we.e[5], we.e[6] );
+            ctx->timings.rle_write_ms += elapsed( se.e[4], se.e[5] );
+            ctx->timings.crc_ms += elapsed( se.e[5], se.e[6] );
         }
     }
     return IBZ2_OK;
@@ -810,6 +880,150 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
     return IBZ2_OK;
 }
 
+/* Host-to-host calls of at least IBZ2_SPLIT_INPUT_BYTES input bytes upload the input in two halves.  Off unless the
+ * variable is set (the tests set it to run the golden files through this path): it hides half of the upload, but K2b then
+ * runs once per half, and a K2b launch never takes less than its longest block (measured on the 8 GB workload: 566 ms
+ * with the split, 563 ms without; with several GPUs per file it loses). */
+static uint64_t
+splitInputBytes()
+{
+    const char* const env = std::getenv( "IBZ2_SPLIT_INPUT_BYTES" );
+    return env != nullptr ? std::strtoull( env, nullptr, 10 ) : ~0ULL;
+}
+
+/* ibz2_decode_buffer for host input and host output: input in two halves.  *done = false (with IBZ2_OK) asks the caller
+ * to run the plain path instead. */
+static int
+decodeBufferSplit( ibz2_ctx* ctx, const uint8_t* data, uint64_t nbytes, uint64_t first_bit, uint64_t last_bit,
+                   void* out, uint64_t out_capacity, ibz2_block_result* results, uint64_t results_capacity,
+                   uint64_t* nblocks, uint64_t* total_out, bool* done )
+{
+    *done = false;
+    cudaStream_t s = ctx->stream;
+    int rc = ensureInput( ctx, nbytes );
+    if ( rc == IBZ2_OK ) {
+        rc = ensureOutput( ctx, out_capacity );
+    }
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const uint64_t half = ( nbytes / 2U ) & ~127ULL;
+    const cudaEvent_t e0 = nextEvent( ctx );
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, half, cudaMemcpyHostToDevice, s ) );
+    IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->inFirstHalf, s ) );
+    const cudaEvent_t e1 = nextEvent( ctx );
+    bool secondHalfQueued = false;
+    const std::function<int()> queueSecondHalf = [&] () -> int {
+        if ( !secondHalfQueued ) {
+            secondHalfQueued = true;
+            IBZ2_CUDA_CHECK( ctx, cudaStreamWaitEvent( ctx->inStream, ctx->inFirstHalf, 0 ) );
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn + half, data + half, nbytes - half, cudaMemcpyHostToDevice,
+                                                   ctx->inStream ) );
+            IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->inSecondHalf, ctx->inStream ) );
+        }
+        return IBZ2_OK;
+    };
+
+    /* ---- first half: every block whose successor also starts inside it is complete ---- */
+    std::vector<uint64_t> foundA;
+    rc = findOnDevice( ctx, ctx->dIn, half, IBZ2_FIND_BLOCK, foundA );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const bool haveCarry = !foundA.empty();
+    const uint64_t carry = haveCarry ? foundA.back() : 0;   /* may reach into the second half: decoded with it */
+    std::vector<uint64_t> mineA;
+    for ( size_t i = 0; i + 1 < foundA.size(); ++i ) {
+        if ( ( foundA[i] >= first_bit ) && ( foundA[i] < last_bit ) ) {
+            mineA.push_back( foundA[i] );
+        }
+    }
+    if ( mineA.size() > results_capacity ) {
+        ctx->lastError = "ibz2_decode_buffer: results array too small";
+        *nblocks = mineA.size();
+        return IBZ2_E_CAPACITY;
+    }
+    uint64_t total = 0;
+    ctx->pipelineCopied = 0;
+    IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
+    ctx->hRunning[0] = 0;
+    if ( !mineA.empty() ) {
+        rc = decodeOnDevice( ctx, ctx->dIn, half, mineA.data(), mineA.size(), ctx->dOut, out_capacity, results, &total, out,
+                             true, false, &queueSecondHalf );
+        if ( rc != IBZ2_OK ) {
+            cudaStreamSynchronize( ctx->inStream );
+            return rc;
+        }
+        for ( size_t i = 0; i < mineA.size(); ++i ) {
+            if ( results[i].status != IBZ2_ST_OK ) {
+                IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->copyStream ) );
+                IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->inStream ) );
+                return IBZ2_OK;   /* *done stays false */
+            }
+        }
+    }
+    rc = queueSecondHalf();   /* no block in the first half: nothing was queued yet */
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+
+    /* ---- second half ---- */
+    const cudaEvent_t eAfterA = nextEvent( ctx );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamWaitEvent( s, ctx->inSecondHalf, 0 ) );
+    const uint64_t lead = std::min<uint64_t>( half, 128U );   /* a magic may straddle the cut */
+    std::vector<uint64_t> foundB;
+    rc = findOnDevice( ctx, ctx->dIn + ( half - lead ), nbytes - ( half - lead ), IBZ2_FIND_BLOCK, foundB );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    std::vector<uint64_t> mineB;
+    if ( haveCarry && ( carry >= first_bit ) && ( carry < last_bit ) ) {
+        mineB.push_back( carry );
+    }
+    for ( const uint64_t f : foundB ) {
+        const uint64_t bit = f + ( half - lead ) * 8U;
+        if ( ( !haveCarry || ( bit > carry ) ) && ( bit >= first_bit ) && ( bit < last_bit ) ) {
+            mineB.push_back( bit );
+        }
+    }
+    *nblocks = mineA.size() + mineB.size();
+    if ( *nblocks > results_capacity ) {
+        cudaStreamSynchronize( ctx->copyStream );
+        ctx->lastError = "ibz2_decode_buffer: results array too small";
+        return IBZ2_E_CAPACITY;
+    }
+    const cudaEvent_t eBeforeB = nextEvent( ctx );
+    if ( !mineB.empty() ) {
+        rc = decodeOnDevice( ctx, ctx->dIn, nbytes, mineB.data(), mineB.size(), ctx->dOut, out_capacity,
+                             results + mineA.size(), &total, out, true, true );
+        if ( rc != IBZ2_OK ) {
+            return rc;
+        }
+    } else if ( !mineA.empty() ) {
+        /* nothing in the second half: the first half's last wave still has to reach the host */
+        const uint64_t produced = std::min<uint64_t>( total, out_capacity );
+        if ( produced > ctx->pipelineCopied ) {
+            IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( static_cast<uint8_t*>( out ) + ctx->pipelineCopied, ctx->dOut + ctx->pipelineCopied,
+                                                   produced - ctx->pipelineCopied, cudaMemcpyDeviceToHost, ctx->copyStream ) );
+        }
+        IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->copyStream ) );
+    }
+    if ( total_out != nullptr ) {
+        *total_out = total;
+    }
+    ctx->timings.h2d_ms = elapsed( e0, e1 );
+    if ( std::getenv( "IBZ2_DEBUG_TIMING" ) != nullptr ) {
+        const cudaEvent_t eAfterB = nextEvent( ctx );
+        cudaEventSynchronize( eAfterB );
+        std::fprintf( stderr, "[ibz2] split input: first half %.1f ms, second half %.1f ms, second half done %.1f ms after the call began; "
+                              "first half decoded at %.1f ms, second half started at %.1f ms, all done at %.1f ms (%zu + %zu blocks)\n",
+                      elapsed( e0, e1 ), elapsed( ctx->inFirstHalf, ctx->inSecondHalf ), elapsed( e0, ctx->inSecondHalf ),
+                      elapsed( e0, eAfterA ), elapsed( e0, eBeforeB ), elapsed( e0, eAfterB ), mineA.size(), mineB.size() );
+    }
+    *done = true;
+    return IBZ2_OK;
+}
+
 int
 ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem,
                     uint64_t first_bit, uint64_t last_bit,
@@ -829,6 +1043,24 @@ ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
     }
     beginCall( ctx );
     const cudaEvent_t eStart = nextEvent( ctx );
+    if ( ( data_mem == IBZ2_MEM_HOST ) && ( out != nullptr ) && ( out_mem == IBZ2_MEM_HOST ) && ( nbytes >= splitInputBytes() ) ) {
+        /* host to host: the second half of the input travels while the blocks of the first half decode */
+        bool done = false;
+        const int rcSplit = decodeBufferSplit( ctx, static_cast<const uint8_t*>( data ), nbytes, first_bit, last_bit, out,
+                                               out_capacity, results, results_capacity, nblocks, total_out, &done );
+        if ( ( rcSplit != IBZ2_OK ) || done ) {
+            if ( rcSplit == IBZ2_OK ) {
+                const cudaEvent_t eEnd = nextEvent( ctx );
+                IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
+                ctx->timings.total_ms = elapsed( eStart, eEnd );
+            }
+            return rcSplit;
+        }
+        /* a block of the first half did not decode cleanly: what the reference reports for it may depend on bytes behind
+         * the half, so the whole call is done again the plain way (the input is on the device by now) */
+        *nblocks = 0;
+        ctx->timings = ibz2_timings{};
+    }
     const uint8_t* dData = nullptr;
     int rc = stageInput( ctx, data, nbytes, data_mem, &dData, "ibz2_decode_buffer" );
     if ( rc != IBZ2_OK ) {

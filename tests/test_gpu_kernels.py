@@ -327,3 +327,28 @@ def test_truncations_match_oracle(ctx):
         out = np.zeros(1 << 20, dtype=np.uint8)
         results, _ = ctx.decode_blocks(data, [32], out)
         assert results["status"][0] == want.info.status, f"cut {cut}"
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# ibz2_decode_buffer with host buffers: one call, find + decode + copies (what bench.py times as e2e), also with the
+# input uploaded in two halves (the path large inputs take)
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("split", [False, True])
+@pytest.mark.parametrize("name", ALL)
+def test_decode_buffer_host(ctx, monkeypatch, name, split):
+    data = case(name)
+    blocks = data_blocks(ctx, data)
+    monkeypatch.setenv("IBZ2_SPLIT_INPUT_BYTES", "1" if split else str(1 << 62))
+    want_results, want_total = ctx.decode_blocks(data, blocks, None)       # sizes and statuses, block by block
+    cap = max(int(want_total), 1)
+    want_out = np.zeros(cap, dtype=np.uint8)
+    want_results, want_total = ctx.decode_blocks(data, blocks, want_out)
+    out = np.zeros(cap, dtype=np.uint8)
+    results, total = ctx.decode_buffer(np.frombuffer(data, dtype=np.uint8), out)
+    assert len(results) == len(blocks) and total == want_total
+    for field in ("status", "enc_offset_bits", "enc_size_bits", "expected_crc", "calculated_crc", "out_size"):
+        assert results[field].tolist() == want_results[field].tolist(), field
+    assert out[:total].tobytes() == want_out[:total].tobytes()
+    if name in VALID and (results["status"] == 0).all() and total == GOLDEN[name]["parallel"]["size"] and total > 0:
+        assert hashlib.sha256(out[:total].tobytes()).hexdigest() == GOLDEN[name]["parallel"]["sha256"]
