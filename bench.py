@@ -216,6 +216,12 @@ KERNELS = {"find_ms": "K1 findMagicsKernel", "huffman_bits_ms": "K2b huffmanBits
            "rle_write_ms": "K5b rleWriteKernel", "crc_ms": "K6 crcKernel"}
 
 
+# DRAM bytes (read + write) of one launch from the ncu capture of this same command on one B200
+# (profiles/r1_v13_launches.csv: dram__bytes_read.sum + dram__bytes_write.sum); only valid for the default workload at N=1
+NCU_TRAFFIC_8GB = {"find_ms": 4.9e9, "huffman_bits_ms": 16.5e9, "bwt_prepare_ms": 49.6e9, "bwt_walk_ms": 229.5e9,
+                   "rle_scan_ms": 48.0e9, "rle_write_ms": 48.2e9, "crc_ms": 8.0e9}
+
+
 def algorithmic_bytes(stage: str, c: int, n: int, u: int) -> int:
     """per-step algorithmic HBM bytes of each kernel (DESIGN.md "Kernels": SURVEY.md section 8(d) per-block figures
     x the blocks one step processes): C compressed bytes, N BWT symbols, U decoded bytes"""
@@ -372,7 +378,11 @@ def run_ours(args):
         alg = algorithmic_bytes(dominant, my_c, n_symbols, int(total))
         achieved = alg / (per_step[dominant] * 1e-3) / 1e9
         roofline = {"bound": "hbm", "kernel": KERNELS[dominant], "achieved": round(achieved, 2), "peak": peak,
-                    "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": round(achieved / peak, 5),
+                    "traffic": (NCU_TRAFFIC_8GB[dominant] if (world == 1 and args.kind == "mixed" and args.copies == 8
+                                                             and args.base_bytes == 1_000_000_000 and args.level == 9) else None),
+                    "traffic_source": "profiles/r1_v13_launches.csv (ncu, same command, per launch)",
+                    "peak_source": peak_src,
                     "launches_per_step": waves, "ms_per_launch": round(per_step[dominant] / waves, 4),
                     "algorithmic_bytes_per_step": alg, "rank": 0,
                     "whole_path": {"achieved": round((my_c + int(total)) / (ms_dev * 1e-3) / 1e9, 2),
