@@ -209,14 +209,32 @@ mtfListsKernel( BlockMeta* __restrict__ meta, uint32_t nblocks, const BlockTable
 constexpr int MTFE_WARPS = 4;
 constexpr uint32_t STAGE_BYTES = 4096;
 constexpr uint32_t PER_LANE = MTF_CHUNK / 32U;   /* 32 symbols per lane */
+/* A lane owns 32 CONSECUTIVE symbols, so with a dense layout the 32 lanes of one load sit 64 (or 32) bytes apart: two
+ * (four) banks for the whole warp.  Each lane's row gets one word of padding, which puts the rows of a warp in 32
+ * different banks, and the lane reads its row into registers once instead of once per pass. */
+constexpr uint32_t SYM16_ROW = PER_LANE / 2U + 1U;   /* words */
+constexpr uint32_t SYM8_ROW = PER_LANE / 4U + 1U;
+/* the assembled bytes: lanes write about 32 bytes apart, so one pad word goes in after every 8 */
+constexpr uint32_t STAGE_PHYS_BYTES = STAGE_BYTES + ( STAGE_BYTES >> 5 ) * 4U + 32U;
 
 struct ExpandShared
 {
-    uint16_t sym16[MTF_CHUNK];
-    uint8_t sym8[MTF_CHUNK];
+    uint32_t sym8[32U * SYM8_ROW];
     uint8_t list[256];
-    uint8_t stage[STAGE_BYTES + 16];
+    /* the symbols are condensed into two bit masks per lane before the first byte is staged, and the long-run path,
+     * which reads them again, does not stage */
+    union
+    {
+        uint32_t sym16[32U * SYM16_ROW];
+        uint8_t stage[STAGE_PHYS_BYTES];
+    };
 };
+
+__device__ __forceinline__ uint32_t
+stagePhys( uint32_t p )
+{
+    return p + ( ( p >> 5 ) << 2 );
+}
 
 __device__ __forceinline__ uint32_t
 runShare( uint32_t sym, uint32_t k )
@@ -254,15 +272,25 @@ mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict_
         const uint4* s16 = reinterpret_cast<const uint4*>( scratch + K2_SYM16_OFFSET + static_cast<uint64_t>( begin ) * 2U );
         const uint4* s8 = reinterpret_cast<const uint4*>( scratch + K2_SYM8_OFFSET + begin );
         const uint2* ls = reinterpret_cast<const uint2*>( scratch + K2_LISTS_OFFSET + static_cast<uint64_t>( chunk ) * 256U );
-        uint4* d16 = reinterpret_cast<uint4*>( sh.sym16 );
-        uint4* d8 = reinterpret_cast<uint4*>( sh.sym8 );
 #pragma unroll
         for ( uint32_t i = 0; i < 4U; ++i ) {
-            d16[i * 32U + lane] = s16[i * 32U + lane];
+            const uint32_t q = i * 32U + lane;   /* 16 bytes = 8 symbols; four of them per row */
+            const uint4 v = s16[q];
+            uint32_t* const d = sh.sym16 + ( q >> 2 ) * SYM16_ROW + ( q & 3U ) * 4U;
+            d[0] = v.x;
+            d[1] = v.y;
+            d[2] = v.z;
+            d[3] = v.w;
         }
 #pragma unroll
         for ( uint32_t i = 0; i < 2U; ++i ) {
-            d8[i * 32U + lane] = s8[i * 32U + lane];
+            const uint32_t q = i * 32U + lane;   /* 16 symbolic bytes; two of them per row */
+            const uint4 v = s8[q];
+            uint32_t* const d = sh.sym8 + ( q >> 1 ) * SYM8_ROW + ( q & 1U ) * 4U;
+            d[0] = v.x;
+            d[1] = v.y;
+            d[2] = v.z;
+            d[3] = v.w;
         }
         reinterpret_cast<uint2*>( sh.list )[lane] = ls[lane];
     }
@@ -272,15 +300,30 @@ mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict_
     /* lane l owns symbols [32 l, 32 l + 32) of the chunk */
     const uint32_t first = lane * PER_LANE;
     const uint32_t mine = first >= count ? 0U : min( PER_LANE, count - first );
+    const uint32_t valid = mine >= 32U ? FULL : ( ( 1U << mine ) - 1U );
+
+    /* bit i of runMask: symbol i is RUNA/RUNB; bit i of runB: it is RUNB */
+    uint32_t runMask = 0;
+    uint32_t runB = 0;
+    {
+        const uint32_t* const row = sh.sym16 + lane * SYM16_ROW;
+#pragma unroll 4
+        for ( uint32_t j = 0; j < PER_LANE / 2U; ++j ) {
+            const uint32_t pair = row[j];
+            const uint32_t isRun = ( ( ( pair & 0xFFFFU ) <= 1U ) ? 1U : 0U ) | ( ( ( pair >> 16 ) <= 1U ) ? 2U : 0U );
+            const uint32_t isB = ( pair & 1U ) | ( ( pair >> 15 ) & 2U );
+            runMask |= isRun << ( 2U * j );
+            runB |= isB << ( 2U * j );
+        }
+    }
+    runMask &= valid;
+    __syncwarp();   /* sym16 may be overwritten by stage from here on */
 
     /* position inside a RUNA/RUNB number at the lane's first symbol */
-    uint32_t trailing = 0;
-    bool allRun = true;
-    for ( uint32_t i = 0; i < mine; ++i ) {
-        const bool isRun = sh.sym16[first + i] <= 1U;
-        trailing = isRun ? trailing + 1U : 0U;
-        allRun = allRun && isRun;
-    }
+    const uint32_t notRun = ~runMask & valid;
+    const bool allRun = notRun == 0;
+    /* run symbols behind the lane's last non-run symbol (only read from lanes that have one) */
+    const uint32_t trailing = allRun ? mine : mine + static_cast<uint32_t>( __clz( static_cast<int>( notRun ) ) ) - 32U;
     const uint32_t allRunMask = __ballot_sync( FULL, allRun );
     uint32_t k0;
     {
@@ -291,19 +334,17 @@ mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict_
         k0 = below == 0 ? ck.runShift + PER_LANE * lane : t + PER_LANE * ( lane - 1U - src );
     }
 
-    /* bytes produced by the lane's symbols */
-    uint32_t total = 0;
+    /* bytes produced by the lane's symbols: one per ordinary symbol, ( digit + 1 ) << position per RUNA/RUNB */
+    uint32_t total = static_cast<uint32_t>( __popc( notRun ) );
     {
-        uint32_t k = k0;
-        for ( uint32_t i = 0; i < mine; ++i ) {
-            const uint32_t sym = sh.sym16[first + i];
-            if ( sym <= 1U ) {
-                total += runShare( sym, k );
-                ++k;
-            } else {
-                total += 1U;
-                k = 0;
-            }
+        uint32_t pending = runMask;
+        while ( pending != 0 ) {
+            const uint32_t i = static_cast<uint32_t>( __ffs( static_cast<int>( pending ) ) ) - 1U;
+            pending &= pending - 1U;
+            /* run symbols directly below i inside the lane; the number continues from k0 when they reach bit 0 */
+            const uint32_t lower = ~runMask & ( ( 1U << i ) - 1U );
+            const uint32_t k = lower == 0 ? k0 + i : i + static_cast<uint32_t>( __clz( static_cast<int>( lower ) ) ) - 32U;
+            total += runShare( ( runB >> i ) & 1U, k );
         }
     }
     uint32_t incl = total;
@@ -321,40 +362,42 @@ mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict_
     if ( chunkTotal <= STAGE_BYTES ) {
         /* common case: assemble the chunk's bytes in shared memory, then write 128-byte rows */
         uint32_t k = k0;
-        for ( uint32_t i = 0; i < mine; ++i ) {
-            const uint32_t sym = sh.sym16[first + i];
-            const uint8_t byte = sh.list[sh.sym8[first + i]];
-            uint32_t c = 1;
-            if ( sym <= 1U ) {
-                c = runShare( sym, k );
-                ++k;
-            } else {
-                k = 0;
+        const uint32_t* const row8 = sh.sym8 + lane * SYM8_ROW;
+#pragma unroll 1
+        for ( uint32_t j = 0; j < PER_LANE / 4U; ++j ) {
+            const uint32_t four = row8[j];
+#pragma unroll
+            for ( uint32_t t = 0; t < 4U; ++t ) {
+                const uint32_t i = 4U * j + t;
+                const uint8_t byte = sh.list[( four >> ( 8U * t ) ) & 0xFFU];
+                const bool isRun = ( ( runMask >> i ) & 1U ) != 0;
+                const uint32_t c = isRun ? runShare( ( runB >> i ) & 1U, k ) : ( ( valid >> i ) & 1U );
+                k = isRun ? k + 1U : 0U;
+                for ( uint32_t r = 0; r < c; ++r ) {
+                    sh.stage[stagePhys( pos + r )] = byte;
+                }
+                pos += c;
             }
-            for ( uint32_t r = 0; r < c; ++r ) {
-                sh.stage[pos + r] = byte;
-            }
-            pos += c;
         }
         __syncwarp();
         const uint32_t limit = chunkBase < n ? min( chunkTotal, n - chunkBase ) : 0U;
         uint8_t* const dst = lbytes + chunkBase;
         const uint32_t head = min( limit, ( 4U - ( chunkBase & 3U ) ) & 3U );
         if ( lane < head ) {
-            dst[lane] = sh.stage[lane];
+            dst[lane] = sh.stage[stagePhys( lane )];
         }
         const uint32_t words = ( limit - head ) >> 2;
         const uint32_t* const stageWords = reinterpret_cast<const uint32_t*>( sh.stage );
         uint32_t* const dstWords = reinterpret_cast<uint32_t*>( dst + head );
         for ( uint32_t w = lane; w < words; w += 32U ) {
             /* stage bytes head + 4 w .. + 3: unaligned in shared memory whenever head != 0 */
-            const uint32_t lo = stageWords[w];
-            const uint32_t hi = stageWords[w + 1U];
+            const uint32_t lo = stageWords[w + ( w >> 3 )];
+            const uint32_t hi = stageWords[( w + 1U ) + ( ( w + 1U ) >> 3 )];
             dstWords[w] = __funnelshift_r( lo, hi, 8U * head );
         }
         const uint32_t tail = head + 4U * words;
         if ( tail + lane < limit ) {
-            dst[tail + lane] = sh.stage[tail + lane];
+            dst[tail + lane] = sh.stage[stagePhys( tail + lane )];
         }
     } else {
         /* long runs: short shares are stored by their lane, long ones by the whole warp */
@@ -363,8 +406,8 @@ mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict_
             uint32_t c = 0;
             uint32_t byte = 0;
             if ( i < mine ) {
-                const uint32_t sym = sh.sym16[first + i];
-                byte = sh.list[sh.sym8[first + i]];
+                const uint32_t sym = ( sh.sym16[lane * SYM16_ROW + ( i >> 1 )] >> ( 16U * ( i & 1U ) ) ) & 0xFFFFU;
+                byte = sh.list[( sh.sym8[lane * SYM8_ROW + ( i >> 2 )] >> ( 8U * ( i & 3U ) ) ) & 0xFFU];
                 c = 1;
                 if ( sym <= 1U ) {
                     c = runShare( sym, k );
@@ -425,6 +468,7 @@ launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_
                                                                                              scratch );
     {
         const dim3 grid( ( MAX_CHUNKS + MTFE_WARPS - 1U ) / MTFE_WARPS, nblocks );
+        cudaFuncSetAttribute( mtfExpandKernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
         mtfExpandKernel<<<grid, MTFE_WARPS * 32, 0, stream>>>( meta, scratch, lbytes );
     }
 }
