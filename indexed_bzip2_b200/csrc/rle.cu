@@ -110,7 +110,7 @@ warpInclusiveCompose( uint32_t f, uint32_t lane )
     return f;
 }
 
-__global__ void __launch_bounds__( RLE_THREADS )
+__global__ void __launch_bounds__( RLE_THREADS, 2 )
 rleScanKernel( const uint8_t* __restrict__ prerleAll, uint32_t* __restrict__ offsetsAll,
                uint32_t* __restrict__ warpBaseAll, BlockMeta* __restrict__ meta )
 {
