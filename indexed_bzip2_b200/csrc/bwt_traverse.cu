@@ -17,7 +17,8 @@
  *                   block = 5.4 blocks = 19 MB -- fit L2 several times over.  Every line is then fetched from HBM
  *                   about once and hit 31 more times.
  *                   The bytes a segment meets go to the segment's own slot (TRAV_SLOT_BYTES, four at a time);
- *                   of a longer segment (1.8 %) only the position after TRAV_SLOT_BYTES steps is kept.
+ *                   of a longer segment (0.03 % at 512 bytes; 1.8 % at 256, whose re-walks made up most of the place
+ *                   kernel's time) only the position after TRAV_SLOT_BYTES steps is kept.
  *   bwtOrderKernel  one CTA per block: the successor list of the <= 14063 segments is ranked in shared memory by
  *                   pointer jumping (Wyllie), cut at the segment that passes through p0; that gives every segment on
  *                   p0's cycle its output offset; each thread then copies its segments' slots to their places

@@ -41,7 +41,8 @@ struct ibz2_ctx
     uint32_t* dDbuf = nullptr;
     uint8_t* dSelectors = nullptr;
     ibz2::BlockTables* dTables = nullptr;
-    uint8_t* dStage = nullptr;
+    uint8_t* dStage = nullptr;           /* K4b staging of ONE sub-wave (subWaveBlocks()), reused by the next */
+    uint32_t stageBlocks = 0;
     uint32_t* dCounter = nullptr;
     uint32_t* dWarpBase = nullptr;
     uint32_t* dPieceStart = nullptr;
@@ -133,6 +134,7 @@ freeScratch( ibz2_ctx* ctx )
     ctx->dSelectors = nullptr;
     ctx->dTables = nullptr;
     ctx->dStage = nullptr;
+    ctx->stageBlocks = 0;
     ctx->dCounter = nullptr;
     ctx->dWarpBase = nullptr;
     ctx->dPieceStart = nullptr;
@@ -141,11 +143,34 @@ freeScratch( ibz2_ctx* ctx )
     ctx->scratchBlocks = 0;
 }
 
+/* K4..K6 run over at most this many blocks at a time: an eighth of a wave when finished output travels to the host
+ * meanwhile (the copy nothing hides is then one sub-wave), half a wave otherwise (every sub-wave ends with a round of
+ * partly idle SMs: 6 ms per call on the 8 GB workload with eighths).  The K4b staging area holds one sub-wave. */
+uint32_t
+subWaveBlocks( const ibz2_ctx* ctx, bool pipelined = false )
+{
+    return std::max<uint32_t>( 1U, ctx->batchBlocks / ( pipelined ? 8U : 2U ) );
+}
+
+int
+ensureStage( ibz2_ctx* ctx, uint32_t blocks )
+{
+    if ( blocks <= ctx->stageBlocks ) {
+        return IBZ2_OK;
+    }
+    cudaFree( ctx->dStage );
+    ctx->dStage = nullptr;
+    ctx->stageBlocks = 0;
+    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dStage, ibz2::TRAV_STAGE_HEADER + static_cast<uint64_t>( blocks ) * ibz2::TRAV_STAGE_STRIDE ) );
+    ctx->stageBlocks = blocks;
+    return IBZ2_OK;
+}
+
 int
 ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
 {
     if ( blocks <= ctx->scratchBlocks ) {
-        return IBZ2_OK;
+        return ensureStage( ctx, std::min( blocks, subWaveBlocks( ctx ) ) );
     }
     freeScratch( ctx );
     const uint64_t b = blocks;
@@ -154,14 +179,13 @@ ensureScratch( ibz2_ctx* ctx, uint32_t blocks )
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dDbuf, b * ibz2::DBUF_STRIDE * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dSelectors, b * ibz2::SEL_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dTables, b * sizeof( ibz2::BlockTables ) ) );
-    IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dStage, ibz2::TRAV_STAGE_HEADER + b * ibz2::TRAV_STAGE_STRIDE ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dCounter, ( b + 16 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dWarpBase, b * ibz2::RLE_RANGES * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( &ctx->dPieceStart, ( b + 1 ) * sizeof( uint32_t ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMallocHost( &ctx->hMeta, b * sizeof( ibz2::BlockMeta ) ) );
     IBZ2_CUDA_CHECK( ctx, cudaMallocHost( &ctx->hOrder, b * sizeof( uint32_t ) ) );
     ctx->scratchBlocks = blocks;
-    return IBZ2_OK;
+    return ensureStage( ctx, std::min( blocks, subWaveBlocks( ctx ) ) );
 }
 
 int
@@ -553,14 +577,17 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
      * function that share one output: the second goes on where the first stopped */
     uint64_t copied = continueOutput ? ctx->pipelineCopied : 0;
     if ( wave > ctx->scratchBlocks ) {
-        /* scratch is about 6.7 MB per block in flight: stay inside what the device has left */
+        /* scratch is about 4.7 MB per block in flight plus the staging of one sub-wave: stay inside what the device has left */
         size_t freeBytes = 0;
         size_t totalBytes = 0;
         if ( cudaMemGetInfo( &freeBytes, &totalBytes ) == cudaSuccess ) {
             const uint64_t perBlock = ibz2::LBYTES_STRIDE + ibz2::DBUF_STRIDE * sizeof( uint32_t ) + ibz2::SEL_STRIDE
-                                      + sizeof( ibz2::BlockTables ) + ibz2::TRAV_STAGE_STRIDE + 4096U;
+                                      + sizeof( ibz2::BlockTables ) + 4096U;
             const uint64_t reusable = static_cast<uint64_t>( ctx->scratchBlocks ) * perBlock;
-            const uint64_t fit = ( static_cast<uint64_t>( freeBytes ) + reusable ) / 10U * 9U / perBlock;
+            const uint64_t stageNeed = ctx->stageBlocks >= subWaveBlocks( ctx ) ? 0U
+                                       : static_cast<uint64_t>( subWaveBlocks( ctx ) ) * ibz2::TRAV_STAGE_STRIDE;
+            const uint64_t usable = static_cast<uint64_t>( freeBytes ) + reusable;
+            const uint64_t fit = ( usable > stageNeed ? usable - stageNeed : 0U ) / 10U * 9U / perBlock;
             wave = static_cast<uint32_t>( std::max<uint64_t>( 1, std::min<uint64_t>( wave, fit ) ) );
         }
     }
@@ -641,7 +668,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
 
         /* K4..K6 in sub-waves: with host output a finished sub-wave travels while the next one is computed, and the part
          * of the copy that nothing hides shrinks to one sub-wave */
-        const uint32_t sub = pipelined ? std::max<uint32_t>( 1U, std::min<uint32_t>( count, ctx->batchBlocks / 8U ) ) : count;
+        const uint32_t sub = std::min<uint32_t>( count, subWaveBlocks( ctx, pipelined ) );
         cudaEvent_t previousDone = nullptr;
         uint32_t previousSlot = 0;
         uint32_t k = 0;
@@ -650,9 +677,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
             ibz2::BlockMeta* const meta = ctx->dMeta + subFirst;
             uint8_t* const lbytes = ctx->dLbytes + static_cast<uint64_t>( subFirst ) * ibz2::LBYTES_STRIDE;
             uint32_t* const dbuf = ctx->dDbuf + static_cast<uint64_t>( subFirst ) * ibz2::DBUF_STRIDE;
-            /* the walk's work counter sits in the 256 bytes in front of the first block's staging area: for a later
-             * sub-wave that is the (no longer needed) tail of its predecessor's */
-            uint8_t* const stage = ctx->dStage + static_cast<uint64_t>( subFirst ) * ibz2::TRAV_STAGE_STRIDE;
+            uint8_t* const stage = ctx->dStage;   /* every sub-wave stages in the same place */
             uint32_t* const warpBase = ctx->dWarpBase + static_cast<uint64_t>( subFirst ) * ibz2::RLE_RANGES;
             WaveEvents se{};
             se.e[1] = nextEvent( ctx );
@@ -880,15 +905,17 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
     return IBZ2_OK;
 }
 
-/* Host-to-host calls of at least IBZ2_SPLIT_INPUT_BYTES input bytes upload the input in two halves.  Off unless the
- * variable is set (the tests set it to run the golden files through this path): it hides half of the upload, but K2b then
- * runs once per half, and a K2b launch never takes less than its longest block (measured on the 8 GB workload: 566 ms
- * with the split, 563 ms without; with several GPUs per file it loses). */
+/* Host-to-host calls of at least IBZ2_SPLIT_INPUT_BYTES input bytes (default 4 GiB) upload the input in two parts, the
+ * first one IBZ2_SPLIT_PERCENT of it (default 25), and decode the blocks of the first part while the second one travels.
+ * It hides most of the upload, but K2b then runs once per part, and a K2b launch never takes less than its longest
+ * block (~50 ms), so it only pays when the second part still fills every decoder slot more than once.  Measured
+ * through bench.py's e2e (ms per call, no split / 25 %): 8 GB raw 539 / 520 (20 %: 529, 30 %: 541, 50 %: 566),
+ * 4 GB raw 302 / 320, 2 GB raw 187 / 209 -- hence the threshold; with several GPUs per file each rank's window decides. */
 static uint64_t
 splitInputBytes()
 {
     const char* const env = std::getenv( "IBZ2_SPLIT_INPUT_BYTES" );
-    return env != nullptr ? std::strtoull( env, nullptr, 10 ) : ~0ULL;
+    return env != nullptr ? std::strtoull( env, nullptr, 10 ) : ( 4ULL << 30 );
 }
 
 /* ibz2_decode_buffer for host input and host output: input in two halves.  *done = false (with IBZ2_OK) asks the caller
@@ -907,7 +934,11 @@ decodeBufferSplit( ibz2_ctx* ctx, const uint8_t* data, uint64_t nbytes, uint64_t
     if ( rc != IBZ2_OK ) {
         return rc;
     }
-    const uint64_t half = ( nbytes / 2U ) & ~127ULL;
+    const char* const percentEnv = std::getenv( "IBZ2_SPLIT_PERCENT" );
+    const uint64_t percent = percentEnv != nullptr
+                             ? std::min<uint64_t>( 95U, std::max<uint64_t>( 5U, std::strtoull( percentEnv, nullptr, 10 ) ) )
+                             : 25U;
+    const uint64_t half = ( nbytes / 100U * percent ) & ~127ULL;
     const cudaEvent_t e0 = nextEvent( ctx );
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->dIn, data, half, cudaMemcpyHostToDevice, s ) );
     IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->inFirstHalf, s ) );

@@ -177,8 +177,8 @@ constexpr uint32_t TRAV_SPACING_SHIFT = 6;
 constexpr uint32_t TRAV_SPACING = 1U << TRAV_SPACING_SHIFT;                    /* a splitter every 64 positions */
 constexpr uint32_t TRAV_MAX_SEGMENTS = ( DBUF_SIZE + TRAV_SPACING - 1U ) / TRAV_SPACING;   /* 14063 */
 constexpr uint32_t TRAV_SEG_CAP = ( TRAV_MAX_SEGMENTS + 63U ) & ~63U;          /* 14080 */
-constexpr uint32_t TRAV_SLOT_SHIFT = 8;
-constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 4 x the mean segment length */
+constexpr uint32_t TRAV_SLOT_SHIFT = 9;
+constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 8 x the mean segment length */
 constexpr uint64_t TRAV_LEN_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;
 constexpr uint64_t TRAV_OVF_OFFSET = TRAV_LEN_OFFSET + TRAV_SEG_CAP * 4ULL;
 constexpr uint64_t TRAV_JUMP_OFFSET = TRAV_OVF_OFFSET + TRAV_SEG_CAP * 4ULL;

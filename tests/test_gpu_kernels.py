@@ -331,15 +331,16 @@ def test_truncations_match_oracle(ctx):
 
 # ---------------------------------------------------------------------------------------------------------------
 # ibz2_decode_buffer with host buffers: one call, find + decode + copies (what bench.py times as e2e), also with the
-# input uploaded in two halves (the path large inputs take)
+# input uploaded in two parts (the path large inputs take)
 # ---------------------------------------------------------------------------------------------------------------
 
-@pytest.mark.parametrize("split", [False, True])
+@pytest.mark.parametrize("split", [0, 25, 50, 90])   # per cent of the input in the first part, 0 = one upload
 @pytest.mark.parametrize("name", ALL)
 def test_decode_buffer_host(ctx, monkeypatch, name, split):
     data = case(name)
     blocks = data_blocks(ctx, data)
     monkeypatch.setenv("IBZ2_SPLIT_INPUT_BYTES", "1" if split else str(1 << 62))
+    monkeypatch.setenv("IBZ2_SPLIT_PERCENT", str(split or 50))
     want_results, want_total = ctx.decode_blocks(data, blocks, None)       # sizes and statuses, block by block
     cap = max(int(want_total), 1)
     want_out = np.zeros(cap, dtype=np.uint8)
