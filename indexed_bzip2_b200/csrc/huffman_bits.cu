@@ -298,7 +298,8 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                  * longer than 9 bits, the end-of-block symbol, or no code) has length 0: the window stays where it
                  * is and every later lookup misses too, so one test at the end of the pair finds it, with the window
                  * still in front of the first symbol that needs the slow path.
-                 * Two raw words are kept in flight behind the window so that a load has a whole pair to land. */
+                 * Three raw words are kept behind the window and a word is loaded only when one is consumed, so that a load has
+                 * the time between two refills (about two pairs) to land before anything waits for its register. */
                 const uint32_t tableAddr = myLutAddr + table * LUT_ROW_BYTES;
                 const uint32_t limAddr = myLimAddr + table * ( LONG_LIMITS * BITS_SLOTS * 4U );
                 const uint32_t offAddr = myOffAddr + table * ( LONG_OFFSETS * BITS_SLOTS * 2U );
@@ -308,6 +309,7 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 prefetchL1( wbase + 64 );                            /* stays inside the file: see GROUP_MAX_WORDS */
                 uint32_t raw0 = __byte_perm( d.nextW, 0, 0x0123 );   /* back to memory order: swapped when used */
                 uint32_t raw1 = __ldg( wbase + 1 );
+                uint32_t raw2 = __ldg( wbase + 2 );
                 uint32_t hi = d.hi;
                 uint32_t lo = d.lo;
                 int nb = d.nb;
@@ -323,8 +325,11 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                         lo |= __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                         nb += rf ? 32 : 0;
                         raw0 = rf ? raw1 : raw0;
+                        raw1 = rf ? raw2 : raw1;
                         wofs += rf ? 1U : 0U;
-                        raw1 = __ldg( wbase + wofs + 1U );
+                        if ( rf ) {
+                            raw2 = __ldg( wbase + wofs + 2U );   /* a predicated load: nothing is fetched twice */
+                        }
                     }
                     /* at least 33 valid bits; a plain symbol takes at most 9 */
                     const uint32_t e0 = e;
@@ -349,8 +354,9 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                                 lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                                 nb += 32;
                                 raw0 = raw1;
+                                raw1 = raw2;
                                 ++wofs;
-                                raw1 = __ldg( wbase + wofs + 1U );
+                                raw2 = __ldg( wbase + wofs + 2U );
                             }
                             uint32_t ee = lookup( tableAddr, hi );
                             uint32_t out = ee >> 5;
@@ -396,8 +402,9 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                             lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
                             nb += 32;
                             raw0 = raw1;
+                            raw1 = raw2;
                             ++wofs;
-                            raw1 = __ldg( wbase + wofs + 1U );
+                            raw2 = __ldg( wbase + wofs + 2U );
                         }
                         e = lookup( tableAddr, hi );
                     }
