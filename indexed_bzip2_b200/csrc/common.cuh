@@ -205,7 +205,7 @@ void launchCrc( const uint8_t* out, BlockMeta* meta, uint32_t nblocks, const uin
 
 void launchCrcFinalize( const uint8_t* out, BlockMeta* meta, uint32_t nblocks, cudaStream_t stream );
 
-constexpr uint32_t CRC_PIECE_BYTES = 32768;
+constexpr uint32_t CRC_PIECE_BYTES = 131072;
 
 void initCrcConstants();
 

@@ -5,7 +5,9 @@
  * The reference updates the CRC one byte at a time inside the serial traversal loop.  Here the CRC is evaluated as a
  * polynomial over GF(2): for a message of 32-bit big-endian words w_i,
  *     R0(M) = ( sum_i w_i(x) * x^(32 * wordsAfter_i) ) * x^32  mod P,      CRC = ~( R0(M) ^ 0xFFFFFFFF * x^(8|M|) ).
- * The output buffer is cut into 32 KiB windows; a CTA of 8 warps takes one window of one block, each warp a 4 KiB span.
+ * The output buffer is cut into windows of CRC_PIECE_BYTES; a CTA of 8 warps takes one window of one block, each warp an
+ * eighth of it.  The window is large (128 KiB) because what follows the byte loop -- eight multiplications mod P per
+ * warp, five more and a power of x for the window -- costs as much as 100 rows of the loop.
  * Lane l accumulates the words l, l + 32, ... of its span (coalesced 128-byte loads); stepping the accumulator over the
  * 1024 bits between two of its words is four table lookups (shared-memory tables of  v * x^(1024 + 8k)).  Lanes, warps
  * and windows are then combined by multiplications with fixed powers of x; the window's weight relative to the end of
@@ -22,26 +24,50 @@ namespace ibz2
 namespace
 {
 constexpr uint32_t CRC_THREADS = 256;
+constexpr uint32_t CRC_WARPS = CRC_THREADS / 32U;
+constexpr uint32_t SPAN_BYTES = CRC_PIECE_BYTES / CRC_WARPS;   /* per warp */
+constexpr uint32_t SPAN_ROWS = SPAN_BYTES / 128U;
+static_assert( ( CRC_WARPS == 8 ) && ( SPAN_BYTES % 128U == 0 ), "three warp-combine steps, whole rows" );
 
 __device__ uint32_t g_shiftTables[4][256]; /* [k][v] = v * x^(8 * (3 - k)) * x^1024 mod P */
 __device__ uint32_t g_powBits[32];         /* x^(2^k) mod P */
 __device__ uint32_t g_laneWeights[5];      /* x^(32 * 2^k) */
-__device__ uint32_t g_warpWeights[3];      /* x^(8 * 4096 * 2^k) */
+__device__ uint32_t g_warpWeights[3];      /* x^(8 * SPAN_BYTES * 2^k) */
 
 /* x^e mod P for an exponent in bits; negative exponents through the group order 2^32 - 1 */
-__device__ uint32_t
-powX( int64_t exponentBits )
+__device__ __forceinline__ uint32_t
+reduceExponent( int64_t exponentBits )
 {
     const int64_t order = 0xFFFFFFFFLL;
     int64_t e = exponentBits % order;
     if ( e < 0 ) {
         e += order;
     }
+    return static_cast<uint32_t>( e );
+}
+
+__device__ uint32_t
+powX( int64_t exponentBits )
+{
+    const uint32_t e = reduceExponent( exponentBits );
     uint32_t r = 1;
     for ( int k = 0; k < 32; ++k ) {
         if ( ( e >> k ) & 1 ) {
             r = crcMulMod( r, g_powBits[k] );
         }
+    }
+    return r;
+}
+
+/* the same by a whole warp: lane k holds x^(2^k) or 1, five rounds of pairwise products (every lane gets the result) */
+__device__ __forceinline__ uint32_t
+powXWarp( int64_t exponentBits, uint32_t lane )
+{
+    const uint32_t e = reduceExponent( exponentBits );
+    uint32_t r = ( ( e >> lane ) & 1U ) != 0 ? g_powBits[lane] : 1U;
+#pragma unroll 1
+    for ( uint32_t d = 1; d < 32U; d <<= 1 ) {
+        r = crcMulMod( r, __shfl_xor_sync( 0xFFFFFFFFU, r, d ) );
     }
     return r;
 }
@@ -91,12 +117,12 @@ crcKernel( const uint8_t* __restrict__ out, BlockMeta* __restrict__ meta, uint32
         const uint64_t windowBegin = window * pieceBytes;
         const uint64_t windowEnd = windowBegin + pieceBytes;
 
-        /* span of this warp: 32 rows of 32 words */
-        const uint64_t spanBegin = windowBegin + static_cast<uint64_t>( warp ) * 4096U;
+        /* span of this warp: SPAN_ROWS rows of 32 words */
+        const uint64_t spanBegin = windowBegin + static_cast<uint64_t>( warp ) * SPAN_BYTES;
         uint32_t acc = 0;
-        if ( ( spanBegin < mainEnd ) && ( spanBegin + 4096U > start ) && ( bm.writeOutput != 0 ) ) {
+        if ( ( spanBegin < mainEnd ) && ( spanBegin + SPAN_BYTES > start ) && ( bm.writeOutput != 0 ) ) {
 #pragma unroll 4
-            for ( uint32_t row = 0; row < 32U; ++row ) {
+            for ( uint32_t row = 0; row < SPAN_ROWS; ++row ) {
                 const uint64_t offset = spanBegin + 128U * row + 4U * lane;
                 uint32_t w = 0;
                 if ( ( offset + 4U > start ) && ( offset < mainEnd ) ) {
@@ -134,7 +160,7 @@ crcKernel( const uint8_t* __restrict__ out, BlockMeta* __restrict__ meta, uint32
             }
             /* v (lane 7) is weighted relative to windowEnd; move it to mainEnd and append the x^32 factor */
             const int64_t exponent = 8 * ( static_cast<int64_t>( mainEnd ) - static_cast<int64_t>( windowEnd ) ) + 32;
-            const uint32_t weight = powX( exponent );
+            const uint32_t weight = powXWarp( exponent, lane );
             const uint32_t contribution = crcMulMod( v, weight );
             if ( ( lane == 7U ) && ( contribution != 0 ) ) {
                 atomicXor( &meta[b].crcAcc, contribution );
@@ -206,7 +232,7 @@ initCrcConstants()
     }
     uint32_t warpWeights[3];
     for ( uint32_t k = 0; k < 3; ++k ) {
-        warpWeights[k] = hostPowX( ( 8ULL * 4096ULL ) << k );
+        warpWeights[k] = hostPowX( ( 8ULL * SPAN_BYTES ) << k );
     }
     cudaMemcpyToSymbol( g_shiftTables, tables.data(), sizeof( uint32_t ) * tables.size() );
     cudaMemcpyToSymbol( g_powBits, powBits, sizeof( powBits ) );
