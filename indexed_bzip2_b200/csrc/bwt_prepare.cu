@@ -106,26 +106,46 @@ bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ 
     __syncthreads();
 
     /* ---- pass 1: byte histogram of the block (bzip2.hpp:759,788) ----
-     * L is the last column of a BWT: equal bytes come in runs.  A lane adds the length of the run of equal bytes that
-     * starts at its word's byte k within the row of 32 words-at-k (heads found with one ballot), so a run costs one
-     * shared-memory add and scattered equal bytes only meet as ordinary same-address atomics. */
+     * L is the last column of a BWT: equal bytes come in runs.  A lane adds the lengths of the runs inside its own four
+     * bytes (one to four shared-memory adds), a warp whose 128 bytes are one run adds once. */
     for ( uint32_t base = 0; base < n; base += PREP_THREADS * 4U ) {
         const uint32_t i = base + tid * 4U;
         /* LBYTES_STRIDE pads the last word of a block */
         const uint32_t word = i < n ? *reinterpret_cast<const uint32_t*>( lbytes + i ) : 0U;
-        /* the lane's four bytes are consecutive: count its own runs first, then merge equal neighbours across lanes */
-        uint32_t k = 0;
-        while ( k < 4U ) {
-            if ( i + k >= n ) {
-                break;
+        const uint32_t key0 = word & 0xFFU;
+        /* run heads and lengths from the three neighbour comparisons, no loop */
+        const bool whole = i + 4U <= n;
+        const uint32_t x = word ^ ( word >> 8 );
+        const bool e1 = ( x & 0xFFU ) == 0;
+        const bool e2 = ( x & 0xFF00U ) == 0;
+        const bool e3 = ( x & 0xFF0000U ) == 0;
+        /* a run that covers the warp's 128 bytes is one add instead of 32 adds to the same address */
+        const uint32_t first = __shfl_sync( FULL, word, 0 );
+        if ( __all_sync( FULL, whole && e1 && e2 && e3 && ( word == first ) ) ) {
+            if ( lane == 0 ) {
+                atomicAdd( &sh.blockHist[key0], 128U );
             }
-            const uint32_t key = ( word >> ( 8U * k ) ) & 0xFFU;
-            uint32_t len = 1;
-            while ( ( k + len < 4U ) && ( i + k + len < n ) && ( ( ( word >> ( 8U * ( k + len ) ) ) & 0xFFU ) == key ) ) {
-                ++len;
+            continue;
+        }
+        if ( whole ) {
+            const uint32_t len3 = 1U;
+            const uint32_t len2 = 1U + ( e3 ? len3 : 0U );
+            const uint32_t len1 = 1U + ( e2 ? len2 : 0U );
+            const uint32_t len0 = 1U + ( e1 ? len1 : 0U );
+            atomicAdd( &sh.blockHist[key0], len0 );
+            if ( !e1 ) {
+                atomicAdd( &sh.blockHist[( word >> 8 ) & 0xFFU], len1 );
             }
-            atomicAdd( &sh.blockHist[key], len );
-            k += len;
+            if ( !e2 ) {
+                atomicAdd( &sh.blockHist[( word >> 16 ) & 0xFFU], len2 );
+            }
+            if ( !e3 ) {
+                atomicAdd( &sh.blockHist[word >> 24], len3 );
+            }
+        } else {
+            for ( uint32_t k = 0; i + k < n; ++k ) {
+                atomicAdd( &sh.blockHist[( word >> ( 8U * k ) ) & 0xFFU], 1U );
+            }
         }
     }
     __syncthreads();
