@@ -85,16 +85,41 @@ loadRow( const uint8_t* __restrict__ prerle, uint32_t row, uint32_t end, uint32_
     const uint32_t b2 = ( in.bytes >> 16 ) & 0xFFU;
     const uint32_t b3 = in.bytes >> 24;
     in.eqMask = ( b0 == prev ? 1U : 0U ) | ( b1 == b0 ? 2U : 0U ) | ( b2 == b1 ? 4U : 0U ) | ( b3 == b2 ? 8U : 0U );
-    if ( in.valid == 4U ) {
-        in.fn = fnTable[in.eqMask];
-    } else {
-        uint32_t f = IDENT;
-        for ( uint32_t k = 0; k < in.valid; ++k ) {
-            f = composeFn( f, ( ( in.eqMask >> k ) & 1U ) ? STEP_EQ : STEP_NE );
-        }
-        in.fn = f;
-    }
+    in.fn = IDENT;
     return in;
+}
+
+/* transfer function of the lane's elements */
+__device__ __forceinline__ uint32_t
+laneFn( const RowInput& in, const uint32_t* __restrict__ fnTable )
+{
+    if ( in.valid == 4U ) {
+        return fnTable[in.eqMask];
+    }
+    uint32_t f = IDENT;
+    for ( uint32_t k = 0; k < in.valid; ++k ) {
+        f = composeFn( f, ( ( in.eqMask >> k ) & 1U ) ? STEP_EQ : STEP_NE );
+    }
+    return f;
+}
+
+/* A full row whose first element differs from its predecessor and that holds no three "equal" marks in a row cannot
+ * reach state 4 from the inside: the only possible count byte is its first element (when the state before the row is
+ * 4), every other element is one output byte, and the state behind the row is 1 + the number of marks at its end
+ * whatever the state before it was.  That is nearly every row of data without long runs, and it needs neither the
+ * scan of transfer functions nor the scan of output sizes.  Returns 1 + trailing marks, or 0 for "take the scan". */
+__device__ __forceinline__ uint32_t
+plainRowEndState( const RowInput& in, bool fullRow, uint32_t lane )
+{
+    const uint32_t up = __shfl_up_sync( FULL, in.eqMask, 1 );
+    const uint32_t window = ( in.eqMask << 2 ) | ( lane == 0 ? 0U : ( up >> 2 ) );   /* marks -2 .. 3 of the lane */
+    const bool triple = ( window & ( window >> 1 ) & ( window >> 2 ) ) != 0;
+    const bool firstMarked = ( lane == 0 ) && ( ( in.eqMask & 1U ) != 0 );
+    const uint32_t lastMask = __shfl_sync( FULL, in.eqMask, 31 );
+    if ( !fullRow || __any_sync( FULL, triple || firstMarked ) ) {
+        return 0;
+    }
+    return ( lastMask & 8U ) == 0 ? 1U : ( ( lastMask & 4U ) == 0 ? 2U : 3U );
 }
 
 __device__ __forceinline__ uint32_t
@@ -149,9 +174,14 @@ rleScanKernel( const uint8_t* __restrict__ prerleAll, uint32_t* __restrict__ off
         uint32_t carry = firstCarry;
         for ( uint32_t row = begin; row < end; row += 128U ) {
             const RowInput in = loadRow( prerle, row, end, lane, carry, fnTable );
-            const uint32_t incl = warpInclusiveCompose( in.fn, lane );
-            f = composeFn( f, __shfl_sync( FULL, incl, 31 ) );
             carry = __shfl_sync( FULL, in.bytes >> 24, 31 );
+            const uint32_t plainEnd = plainRowEndState( in, row + 128U <= end, lane );
+            if ( plainEnd != 0 ) {
+                f = plainEnd * 0x11111U;   /* a constant function swallows what came before it */
+                continue;
+            }
+            const uint32_t incl = warpInclusiveCompose( laneFn( in, fnTable ), lane );
+            f = composeFn( f, __shfl_sync( FULL, incl, 31 ) );
         }
         if ( lane == 0 ) {
             rangeFn[warp] = f;
@@ -174,7 +204,25 @@ rleScanKernel( const uint8_t* __restrict__ prerleAll, uint32_t* __restrict__ off
         uint32_t carry = firstCarry;
         for ( uint32_t row = begin; row < end; row += 128U ) {
             const RowInput in = loadRow( prerle, row, end, lane, carry, fnTable );
-            const uint32_t incl = warpInclusiveCompose( in.fn, lane );
+            carry = __shfl_sync( FULL, in.bytes >> 24, 31 );
+            const uint32_t plainEnd = plainRowEndState( in, row + 128U <= end, lane );
+            if ( plainEnd != 0 ) {
+                /* element 0 is a count byte when the row starts in state 4, everything else is one byte */
+                const bool countFirst = rowState == 4U;
+                const uint32_t firstByte = __shfl_sync( FULL, in.bytes & 0xFFU, 0 );
+                const uint32_t firstEmit = countFirst ? firstByte : 1U;
+                const uint32_t o = running + 4U * lane + firstEmit - 1U;   /* offset of the lane's element 0 when lane > 0 */
+                uint4 packed;
+                packed.x = lane == 0 ? ( running | ( countFirst ? COUNT_FLAG : 0U ) ) : o;
+                packed.y = o + 1U;
+                packed.z = o + 2U;
+                packed.w = o + 3U;
+                *reinterpret_cast<uint4*>( offsets + row + 4U * lane ) = packed;
+                running += 127U + firstEmit;
+                rowState = plainEnd;
+                continue;
+            }
+            const uint32_t incl = warpInclusiveCompose( laneFn( in, fnTable ), lane );
             uint32_t excl = __shfl_up_sync( FULL, incl, 1 );
             if ( lane == 0 ) {
                 excl = IDENT;
@@ -222,7 +270,6 @@ rleScanKernel( const uint8_t* __restrict__ prerleAll, uint32_t* __restrict__ off
             }
             running += __shfl_sync( FULL, scan, 31 );
             rowState = applyFn( __shfl_sync( FULL, incl, 31 ), rowState );
-            carry = __shfl_sync( FULL, in.bytes >> 24, 31 );
         }
         if ( lane == 0 ) {
             rangeTotal[warp] = running;
