@@ -29,6 +29,9 @@ constexpr uint32_t IDENT = 0x43210U;
 constexpr uint32_t STEP_NE = 0x01111U;
 constexpr uint32_t STEP_EQ = 0x04321U;
 constexpr uint32_t COUNT_FLAG = 0x80000000U;
+/* word 0 of a row's 128 offsets: the row is "plain" (plainRowEndState) and the next word holds all there is to know
+ * about it; offsets are relative to a range of one block's output and stay far below 2^30 */
+constexpr uint32_t PLAIN_FLAG = 0x40000000U;
 
 __device__ __forceinline__ uint32_t
 applyFn( uint32_t f, uint32_t state )
@@ -211,13 +214,12 @@ rleScanKernel( const uint8_t* __restrict__ prerleAll, uint32_t* __restrict__ off
                 const bool countFirst = rowState == 4U;
                 const uint32_t firstByte = __shfl_sync( FULL, in.bytes & 0xFFU, 0 );
                 const uint32_t firstEmit = countFirst ? firstByte : 1U;
-                const uint32_t o = running + 4U * lane + firstEmit - 1U;   /* offset of the lane's element 0 when lane > 0 */
-                uint4 packed;
-                packed.x = lane == 0 ? ( running | ( countFirst ? COUNT_FLAG : 0U ) ) : o;
-                packed.y = o + 1U;
-                packed.z = o + 2U;
-                packed.w = o + 3U;
-                *reinterpret_cast<uint4*>( offsets + row + 4U * lane ) = packed;
+                if ( lane == 0 ) {
+                    /* K5b works the offsets out itself: element 0 at `running` (firstEmit copies when it is a count
+                     * byte), element e > 0 at running + firstEmit - 1 + e */
+                    *reinterpret_cast<uint4*>( offsets + row ) =
+                        make_uint4( PLAIN_FLAG | running, firstEmit | ( countFirst ? COUNT_FLAG : 0U ), 0U, 0U );
+                }
                 running += 127U + firstEmit;
                 rowState = plainEnd;
                 continue;
@@ -398,7 +400,14 @@ rleWriteKernel( const uint8_t* __restrict__ prerleAll, const uint32_t* __restric
         const uint32_t valid = j >= end ? 0U : ( end - j >= 4U ? 4U : end - j );
         uint32_t bytes = 0;
         uint4 offs = make_uint4( 0, 0, 0, 0 );
-        if ( valid > 0 ) {
+        const uint4 head = *reinterpret_cast<const uint4*>( offsets + row );   /* the same 16 bytes for every lane */
+        if ( ( head.x & PLAIN_FLAG ) != 0 ) {
+            /* plain row (always a full one): see rleScanKernel */
+            bytes = *reinterpret_cast<const uint32_t*>( prerle + j );
+            const uint32_t base = head.x & ~PLAIN_FLAG;
+            const uint32_t o = base + ( head.y & ~COUNT_FLAG ) - 1U + 4U * lane;
+            offs = make_uint4( lane == 0 ? ( base | ( head.y & COUNT_FLAG ) ) : o, o + 1U, o + 2U, o + 3U );
+        } else if ( valid > 0 ) {
             bytes = *reinterpret_cast<const uint32_t*>( prerle + j );
             offs = *reinterpret_cast<const uint4*>( offsets + j );
         }
