@@ -42,6 +42,11 @@ namespace
 constexpr uint32_t SPACING = TRAV_SPACING;
 constexpr uint32_t SPACING_SHIFT = TRAV_SPACING_SHIFT;
 constexpr uint32_t MAX_SEGMENTS = TRAV_MAX_SEGMENTS;
+/* ranking works on every RATIO-th splitter ("coarse" segments: few enough for shared memory), the walk on all of them */
+constexpr uint32_t COARSE_SHIFT = TRAV_COARSE_SHIFT;
+constexpr uint32_t RATIO_SHIFT = COARSE_SHIFT - SPACING_SHIFT;
+constexpr uint32_t RATIO_MASK = ( 1U << RATIO_SHIFT ) - 1U;
+constexpr uint32_t MAX_COARSE = ( DBUF_SIZE + ( 1U << COARSE_SHIFT ) - 1U ) >> COARSE_SHIFT;   /* 14063 */
 constexpr uint32_t SLOT = TRAV_SLOT_BYTES;
 constexpr uint32_t NIL = 0xFFFFU;
 constexpr uint32_t NOT_ON_CYCLE = 0xFFFFFFFFU;
@@ -49,7 +54,7 @@ constexpr uint32_t FULL = 0xFFFFFFFFU;
 
 constexpr uint32_t TRAV_CHUNK = 64;                                              /* segments a warp takes at a time */
 constexpr uint32_t CHUNKS_PER_BLOCK = ( MAX_SEGMENTS + TRAV_CHUNK - 1U ) / TRAV_CHUNK;   /* 220 */
-constexpr int WALK_THREADS_DEFAULT = 512;                                        /* per SM */
+constexpr int WALK_THREADS_DEFAULT = 1024;                                       /* per SM */
 constexpr uint32_t WALK_STEPS = 4;                                               /* steps per look at the pool */
 
 struct BlockStage
@@ -205,13 +210,14 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
 
 /* ------------------------------------------------------------------ rank ------------------------------------ */
 constexpr int RANK_THREADS = 1024;
-constexpr uint32_t PER_THREAD = ( MAX_SEGMENTS + RANK_THREADS - 1 ) / RANK_THREADS;
+constexpr uint32_t PER_THREAD = ( MAX_COARSE + RANK_THREADS - 1 ) / RANK_THREADS;
 
 struct RankShared
 {
-    uint32_t dist[MAX_SEGMENTS + 1];
-    uint16_t jump[MAX_SEGMENTS + 1];
-    uint32_t cycleLen;
+    uint32_t dist[MAX_COARSE + 1];
+    uint16_t jump[MAX_COARSE + 1];
+    int starCoarse;       /* coarse segment whose chain of segments passes through origPtr, -1: none */
+    uint32_t starStep;    /* ... after this many steps */
 };
 
 __global__ void __launch_bounds__( RANK_THREADS, 2 )
@@ -228,11 +234,42 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
     const uint32_t n = bm.n;
     const BlockStage st = blockStage( stageAll, blockIdx.x );
     const uint32_t tid = threadIdx.x;
-    const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
-    const int sstar = bm.travStar;
+    const uint32_t fineSegments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
+    const uint32_t segments = ( n + ( 1U << COARSE_SHIFT ) - 1U ) >> COARSE_SHIFT;   /* coarse */
+    const int starFine = bm.travStar;
+
+    /* ---- coarse segments: from every RATIO-th splitter along the chain of (fine) segments to the next such splitter.
+     * The chain returns to where it started at the latest, so the loop ends; four hops on average, each one a pair of
+     * loads that hit L2 (the walk has just written them). ---- */
+    if ( tid == 0 ) {
+        sh.starCoarse = -1;
+        sh.starStep = 0;
+    }
+    for ( uint32_t f = tid; f < fineSegments; f += RANK_THREADS ) {
+        st.segBase[f] = NOT_ON_CYCLE;
+    }
+    __syncthreads();
+    if ( starFine >= 0 ) {
+        for ( uint32_t c = tid; c < segments; c += RANK_THREADS ) {
+            uint32_t f = c << RATIO_SHIFT;
+            uint32_t d = 0;
+            do {
+                if ( static_cast<int>( f ) == starFine ) {
+                    sh.starCoarse = static_cast<int>( c );
+                    sh.starStep = d + bm.travK;
+                }
+                d += st.segLen[f];
+                f = st.segJump[f];
+            } while ( ( f & RATIO_MASK ) != 0 );
+            sh.dist[c] = d;
+            sh.jump[c] = static_cast<uint16_t>( f >> RATIO_SHIFT );
+        }
+    }
+    __syncthreads();
+    const int sstar = sh.starCoarse;
 
     if ( sstar < 0 ) {
-        /* no splitter on the start cycle: serial walk of one lap by one thread */
+        /* no coarse splitter on the start cycle (it is a short one then): serial walk of one lap by one thread */
         if ( tid == 0 ) {
             const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( blockIdx.x ) * DBUF_STRIDE;
             uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( blockIdx.x ) * LBYTES_STRIDE;
@@ -245,16 +282,12 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
                 pos = e >> 8;
             } while ( ( pos != p0 ) && ( k < n ) );
             bm.cycleLen = k;
+            bm.travStar = -1;   /* tells the place kernel that there is nothing to place */
         }
         return;
     }
 
-    for ( uint32_t s = tid; s < segments; s += RANK_THREADS ) {
-        sh.dist[s] = st.segLen[s];
-        sh.jump[s] = st.segJump[s];
-    }
-    __syncthreads();
-    const uint32_t kstar = bm.travK;
+    const uint32_t kstar = sh.starStep;
     const uint32_t lenStar = sh.dist[sstar];
     const uint32_t first = sh.jump[sstar];  /* the splitter reached from p0 */
     __syncthreads();
@@ -297,9 +330,28 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
 
     const uint32_t tailLen = lenStar - kstar;          /* p0 .. end of sstar's segment, output offset 0 */
     const uint32_t ranked = sh.dist[first];            /* 0 when first == sstar */
-    for ( uint32_t s = tid; s < segments; s += RANK_THREADS ) {
-        /* a segment that reaches sstar lies on p0's cycle */
-        st.segBase[s] = sh.jump[s] == NIL ? tailLen + ranked - sh.dist[s] : NOT_ON_CYCLE;
+    __syncthreads();
+    for ( uint32_t c = tid; c < segments; c += RANK_THREADS ) {
+        /* a coarse segment that reaches sstar lies on p0's cycle; its first byte goes to ... */
+        sh.dist[c] = sh.jump[c] == NIL ? tailLen + ranked - sh.dist[c] : NOT_ON_CYCLE;
+    }
+    __syncthreads();
+    /* ---- ... and the segments of its chain follow one another from there.  In the chain that passes through p0 the
+     * output begins at p0: what comes after it is placed from offset 0, what comes before it closes the lap. ---- */
+    for ( uint32_t c = tid; c < segments; c += RANK_THREADS ) {
+        const uint32_t base = sh.dist[c];
+        if ( base == NOT_ON_CYCLE ) {
+            continue;
+        }
+        const bool starChain = static_cast<int>( c ) == sstar;
+        uint32_t f = c << RATIO_SHIFT;
+        uint32_t d = 0;
+        do {
+            const bool behindP0 = starChain && ( d >= kstar ) && ( static_cast<int>( f ) != starFine );
+            st.segBase[f] = behindP0 ? d - kstar : base + d;
+            d += st.segLen[f];
+            f = st.segJump[f];
+        } while ( ( f & RATIO_MASK ) != 0 );
     }
     if ( tid == 0 ) {
         bm.cycleLen = ranked + lenStar;
