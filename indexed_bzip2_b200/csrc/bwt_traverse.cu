@@ -60,9 +60,8 @@ constexpr uint32_t WALK_STEPS = 4;                                              
 struct BlockStage
 {
     uint8_t* slots;      /* [segment][SLOT] */
-    uint32_t* segLen;    /* steps from the segment's splitter to the next splitter */
+    uint2* segLink;      /* x: steps from the segment's splitter to the next splitter, y: that splitter (segment index) */
     uint32_t* ovfPos;    /* position reached after SLOT steps (only meaningful when segLen > SLOT) */
-    uint16_t* segJump;   /* the splitter (segment index) the segment ends at */
     uint32_t* segBase;   /* bwtRankKernel: output offset of the segment's first byte, NOT_ON_CYCLE for the others */
 };
 
@@ -72,9 +71,8 @@ blockStage( uint8_t* stageAll, uint32_t block )
     uint8_t* const base = stageAll + TRAV_STAGE_HEADER + static_cast<uint64_t>( block ) * TRAV_STAGE_STRIDE;
     BlockStage st;
     st.slots = base;
-    st.segLen = reinterpret_cast<uint32_t*>( base + TRAV_LEN_OFFSET );
+    st.segLink = reinterpret_cast<uint2*>( base + TRAV_LINK_OFFSET );
     st.ovfPos = reinterpret_cast<uint32_t*>( base + TRAV_OVF_OFFSET );
-    st.segJump = reinterpret_cast<uint16_t*>( base + TRAV_JUMP_OFFSET );
     st.segBase = reinterpret_cast<uint32_t*>( base + TRAV_BASE_OFFSET );
     return st;
 }
@@ -190,8 +188,7 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
                 }
                 if ( ( pos & ( SPACING - 1U ) ) == 0 ) {
                     const BlockStage st = blockStage( stageAll, myBlock );
-                    st.segJump[s] = static_cast<uint16_t>( pos >> SPACING_SHIFT );
-                    st.segLen[s] = steps;
+                    st.segLink[s] = make_uint2( steps, pos >> SPACING_SHIFT );
                     if ( ( ( steps & 15U ) != 0 ) && ( steps < SLOT ) ) {
                         /* the last, partly filled quad (what lies behind the segment's bytes is never read) */
                         const uint32_t w = ( steps >> 2 ) & 3U;
@@ -258,8 +255,9 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
                     sh.starCoarse = static_cast<int>( c );
                     sh.starStep = d + bm.travK;
                 }
-                d += st.segLen[f];
-                f = st.segJump[f];
+                const uint2 link = st.segLink[f];
+                d += link.x;
+                f = link.y;
             } while ( ( f & RATIO_MASK ) != 0 );
             sh.dist[c] = d;
             sh.jump[c] = static_cast<uint16_t>( f >> RATIO_SHIFT );
@@ -349,8 +347,9 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
         do {
             const bool behindP0 = starChain && ( d >= kstar ) && ( static_cast<int>( f ) != starFine );
             st.segBase[f] = behindP0 ? d - kstar : base + d;
-            d += st.segLen[f];
-            f = st.segJump[f];
+            const uint2 link = st.segLink[f];
+            d += link.x;
+            f = link.y;
         } while ( ( f & RATIO_MASK ) != 0 );
     }
     if ( tid == 0 ) {
@@ -427,7 +426,7 @@ bwtPlaceKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prer
     }
     const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( block ) * DBUF_STRIDE;
     uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( block ) * LBYTES_STRIDE;
-    const uint32_t len = st.segLen[s];
+    const uint32_t len = st.segLink[s].x;
     const bool star = static_cast<int32_t>( s ) == bm.travStar;
     const uint32_t kstar = bm.travK;
     const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );

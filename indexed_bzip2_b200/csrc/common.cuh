@@ -171,8 +171,9 @@ void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, u
                        cudaStream_t stream );
 
 /* K4b staging, per block: one slot of TRAV_SLOT_BYTES per segment (the first bytes the segment's walk met), then per
- * segment its length (u32), the position at which a walk longer than the slot goes on (u32), its successor segment
- * (u16) and, after ranking, its output offset (u32).  The buffer starts with a TRAV_STAGE_HEADER holding the walk kernel's work counter. */
+ * segment its length and successor segment (one uint2: the ranking follows chains of them, one load per hop; kept
+ * apart from the slots so that a block's 56 250 links are 450 KB that stay in L2), the position at which a walk longer
+ * than the slot goes on (u32) and, after ranking, its output offset (u32).  The buffer starts with a TRAV_STAGE_HEADER holding the walk kernel's work counter. */
 constexpr uint32_t TRAV_SPACING_SHIFT = 4;
 constexpr uint32_t TRAV_SPACING = 1U << TRAV_SPACING_SHIFT;                    /* a splitter every 16 positions */
 constexpr uint32_t TRAV_COARSE_SHIFT = 6;                                      /* every 64: the ones that get ranked */
@@ -180,10 +181,9 @@ constexpr uint32_t TRAV_MAX_SEGMENTS = ( DBUF_SIZE + TRAV_SPACING - 1U ) / TRAV_
 constexpr uint32_t TRAV_SEG_CAP = ( TRAV_MAX_SEGMENTS + 63U ) & ~63U;          /* 56256 */
 constexpr uint32_t TRAV_SLOT_SHIFT = 7;
 constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 8 x the mean segment length */
-constexpr uint64_t TRAV_LEN_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;
-constexpr uint64_t TRAV_OVF_OFFSET = TRAV_LEN_OFFSET + TRAV_SEG_CAP * 4ULL;
-constexpr uint64_t TRAV_JUMP_OFFSET = TRAV_OVF_OFFSET + TRAV_SEG_CAP * 4ULL;
-constexpr uint64_t TRAV_BASE_OFFSET = TRAV_JUMP_OFFSET + TRAV_SEG_CAP * 2ULL;   /* u32: output offset of the segment's first byte */
+constexpr uint64_t TRAV_LINK_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;   /* uint2: length, successor */
+constexpr uint64_t TRAV_OVF_OFFSET = TRAV_LINK_OFFSET + TRAV_SEG_CAP * 8ULL;
+constexpr uint64_t TRAV_BASE_OFFSET = TRAV_OVF_OFFSET + TRAV_SEG_CAP * 4ULL;    /* u32: output offset of the segment's first byte */
 constexpr uint64_t TRAV_STAGE_STRIDE = ( TRAV_BASE_OFFSET + TRAV_SEG_CAP * 4ULL + 255ULL ) & ~255ULL;
 constexpr uint64_t TRAV_STAGE_HEADER = 256;
 /* stage: device u8[TRAV_STAGE_HEADER + nblocks * TRAV_STAGE_STRIDE] */
