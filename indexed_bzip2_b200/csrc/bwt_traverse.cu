@@ -47,6 +47,9 @@ constexpr uint32_t COARSE_SHIFT = TRAV_COARSE_SHIFT;
 constexpr uint32_t RATIO_SHIFT = COARSE_SHIFT - SPACING_SHIFT;
 constexpr uint32_t RATIO_MASK = ( 1U << RATIO_SHIFT ) - 1U;
 constexpr uint32_t MAX_COARSE = ( DBUF_SIZE + ( 1U << COARSE_SHIFT ) - 1U ) >> COARSE_SHIFT;   /* 14063 */
+constexpr uint32_t STAR_COARSE_SLOT = MAX_COARSE + 1U;
+constexpr uint32_t STAR_STEP_SLOT = MAX_COARSE + 2U;
+static_assert( STAR_STEP_SLOT < TRAV_SEG_CAP, "kept in the segBase array" );
 constexpr uint32_t SLOT = TRAV_SLOT_BYTES;
 constexpr uint32_t NIL = 0xFFFFU;
 constexpr uint32_t NOT_ON_CYCLE = 0xFFFFFFFFU;
@@ -62,7 +65,9 @@ struct BlockStage
     uint8_t* slots;      /* [segment][SLOT] */
     uint2* segLink;      /* x: steps from the segment's splitter to the next splitter, y: that splitter (segment index) */
     uint32_t* ovfPos;    /* position reached after SLOT steps (only meaningful when segLen > SLOT) */
-    uint32_t* segBase;   /* bwtRankKernel: output offset of the segment's first byte, NOT_ON_CYCLE for the others */
+    uint32_t* segBase;   /* bwtRankKernel: output offset of the first byte of every COARSE segment on p0's cycle,
+                          * NOT_ON_CYCLE for the others; behind them the coarse segment whose chain passes through p0
+                          * and the step at which it does */
 };
 
 __device__ __forceinline__ BlockStage
@@ -231,7 +236,6 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
     const uint32_t n = bm.n;
     const BlockStage st = blockStage( stageAll, blockIdx.x );
     const uint32_t tid = threadIdx.x;
-    const uint32_t fineSegments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
     const uint32_t segments = ( n + ( 1U << COARSE_SHIFT ) - 1U ) >> COARSE_SHIFT;   /* coarse */
     const int starFine = bm.travStar;
 
@@ -241,9 +245,6 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
     if ( tid == 0 ) {
         sh.starCoarse = -1;
         sh.starStep = 0;
-    }
-    for ( uint32_t f = tid; f < fineSegments; f += RANK_THREADS ) {
-        st.segBase[f] = NOT_ON_CYCLE;
     }
     __syncthreads();
     if ( starFine >= 0 ) {
@@ -331,26 +332,11 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
     __syncthreads();
     for ( uint32_t c = tid; c < segments; c += RANK_THREADS ) {
         /* a coarse segment that reaches sstar lies on p0's cycle; its first byte goes to ... */
-        sh.dist[c] = sh.jump[c] == NIL ? tailLen + ranked - sh.dist[c] : NOT_ON_CYCLE;
+        st.segBase[c] = sh.jump[c] == NIL ? tailLen + ranked - sh.dist[c] : NOT_ON_CYCLE;
     }
-    __syncthreads();
-    /* ---- ... and the segments of its chain follow one another from there.  In the chain that passes through p0 the
-     * output begins at p0: what comes after it is placed from offset 0, what comes before it closes the lap. ---- */
-    for ( uint32_t c = tid; c < segments; c += RANK_THREADS ) {
-        const uint32_t base = sh.dist[c];
-        if ( base == NOT_ON_CYCLE ) {
-            continue;
-        }
-        const bool starChain = static_cast<int>( c ) == sstar;
-        uint32_t f = c << RATIO_SHIFT;
-        uint32_t d = 0;
-        do {
-            const bool behindP0 = starChain && ( d >= kstar ) && ( static_cast<int>( f ) != starFine );
-            st.segBase[f] = behindP0 ? d - kstar : base + d;
-            const uint2 link = st.segLink[f];
-            d += link.x;
-            f = link.y;
-        } while ( ( f & RATIO_MASK ) != 0 );
+    if ( tid == 0 ) {
+        st.segBase[STAR_COARSE_SLOT] = static_cast<uint32_t>( sstar );
+        st.segBase[STAR_STEP_SLOT] = kstar;
     }
     if ( tid == 0 ) {
         bm.cycleLen = ranked + lenStar;
@@ -359,7 +345,7 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
 
 /* ------------------------------------------------------------------ place ----------------------------------- */
 constexpr int PLACE_THREADS = 256;
-constexpr uint32_t PLACE_CTAS_PER_BLOCK = ( MAX_SEGMENTS + PLACE_THREADS - 1 ) / PLACE_THREADS;
+constexpr uint32_t PLACE_CTAS_PER_BLOCK = ( MAX_COARSE + PLACE_THREADS - 1 ) / PLACE_THREADS;
 
 /* len staged bytes of a segment (slot is 256-byte aligned) -> dst[0 .. len): bytes up to the first 4-byte boundary of
  * dst, then whole words put together from two neighbouring slot words, 64 slot bytes per round of loads. */
@@ -404,6 +390,9 @@ placeStaged( const uint8_t* __restrict__ slot, uint8_t* __restrict__ dst, uint32
     }
 }
 
+/* One thread per coarse segment on p0's cycle: its bytes are one contiguous stretch of the output, put together from the
+ * slots of the (four, on average) segments of its chain.  In the chain that passes through p0 the output begins at p0:
+ * what comes after it goes to offset 0, what comes before it closes the lap. */
 __global__ void __launch_bounds__( PLACE_THREADS )
 bwtPlaceKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerleAll,
                 const BlockMeta* __restrict__ meta, uint8_t* __restrict__ stageAll )
@@ -414,46 +403,59 @@ bwtPlaceKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prer
         return;
     }
     const uint32_t n = bm.n;
-    const uint32_t segments = ( n + SPACING - 1 ) >> SPACING_SHIFT;
-    const uint32_t s = blockIdx.x * PLACE_THREADS + threadIdx.x;
-    if ( s >= segments ) {
+    const uint32_t coarseSegments = ( n + ( 1U << COARSE_SHIFT ) - 1U ) >> COARSE_SHIFT;
+    const uint32_t c = blockIdx.x * PLACE_THREADS + threadIdx.x;
+    if ( c >= coarseSegments ) {
         return;
     }
     const BlockStage st = blockStage( stageAll, block );
-    const uint32_t base = st.segBase[s];
-    if ( base == NOT_ON_CYCLE ) {
+    const uint32_t coarseBase = st.segBase[c];
+    if ( coarseBase == NOT_ON_CYCLE ) {
         return;
     }
     const uint32_t* __restrict__ dbuf = dbufAll + static_cast<uint64_t>( block ) * DBUF_STRIDE;
     uint8_t* __restrict__ prerle = prerleAll + static_cast<uint64_t>( block ) * LBYTES_STRIDE;
-    const uint32_t len = st.segLink[s].x;
-    const bool star = static_cast<int32_t>( s ) == bm.travStar;
-    const uint32_t kstar = bm.travK;
-    const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );
-    const uint32_t staged = min( len, SLOT );
-    if ( star ) {
-        /* steps kstar .. len - 1 open the output, steps 0 .. kstar - 1 close the lap */
-        for ( uint32_t k = 0; k < staged; ++k ) {
-            const uint32_t idx = k >= kstar ? k - kstar : base + k;
-            if ( idx < n ) {
-                prerle[idx] = slot[k];
+    const uint32_t starFine = static_cast<uint32_t>( bm.travStar );
+    const uint32_t kstarFine = bm.travK;
+    const bool starChain = c == st.segBase[STAR_COARSE_SLOT];
+    const uint32_t kstarCoarse = st.segBase[STAR_STEP_SLOT];
+
+    uint32_t s = c << RATIO_SHIFT;
+    uint32_t d = 0;
+    do {
+        const uint2 link = st.segLink[s];
+        const uint32_t len = link.x;
+        const bool star = s == starFine;
+        const bool behindP0 = starChain && ( d >= kstarCoarse ) && !star;
+        const uint32_t base = behindP0 ? d - kstarCoarse : coarseBase + d;
+        const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );
+        const uint32_t staged = min( len, SLOT );
+        if ( star ) {
+            /* steps kstarFine .. len - 1 open the output, steps 0 .. kstarFine - 1 close the lap */
+            for ( uint32_t k = 0; k < staged; ++k ) {
+                const uint32_t idx = k >= kstarFine ? k - kstarFine : base + k;
+                if ( idx < n ) {
+                    prerle[idx] = slot[k];
+                }
+            }
+        } else if ( base < n ) {
+            placeStaged( slot, prerle + base, min( staged, n - base ) );
+        }
+        if ( len > SLOT ) {
+            /* the rest of a long segment: walked again from where the slot ended */
+            uint32_t pos = st.ovfPos[s];
+            for ( uint32_t k = SLOT; k < len; ++k ) {
+                const uint32_t e = __ldcg( dbuf + pos );
+                const uint32_t idx = ( star && ( k >= kstarFine ) ) ? ( k - kstarFine ) : ( base + k );
+                if ( idx < n ) {
+                    prerle[idx] = static_cast<uint8_t>( e );
+                }
+                pos = e >> 8;
             }
         }
-    } else if ( base < n ) {
-        placeStaged( slot, prerle + base, min( staged, n - base ) );
-    }
-    if ( len > SLOT ) {
-        /* the rest of a long segment: walked again from where the slot ended */
-        uint32_t pos = st.ovfPos[s];
-        for ( uint32_t k = SLOT; k < len; ++k ) {
-            const uint32_t e = __ldcg( dbuf + pos );
-            const uint32_t idx = ( star && ( k >= kstar ) ) ? ( k - kstar ) : ( base + k );
-            if ( idx < n ) {
-                prerle[idx] = static_cast<uint8_t>( e );
-            }
-            pos = e >> 8;
-        }
-    }
+        d += len;
+        s = link.y;
+    } while ( ( s & RATIO_MASK ) != 0 );
 }
 
 /* ---- periodic continuation when the start cycle is shorter than the block ---- */
