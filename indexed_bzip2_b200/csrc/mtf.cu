@@ -7,8 +7,8 @@
  * position p of the chunk's start list", and the list left behind is a permutation of start positions.  Permutations
  * compose, so a cheap serial pass over the chunk permutations recovers every chunk's real start list.
  *   K2c  mtfChunkKernel   one LANE per chunk of MTF_CHUNK symbols: symbolic move-to-front on a private list held in
- *                         the lane's own shared-memory bank (word w of lane t at [w][t]; the first four entries stay
- *                         in a register); writes one symbolic byte per symbol and the chunk's final permutation.
+ *                         the lane's own shared-memory column (16-byte quad q of lane t at [q][t]; the first 16 entries
+ *                         stay in registers); writes one symbolic byte per symbol and the chunk's final permutation.
  *   K2d  mtfListsKernel   one WARP per block: start list of chunk j+1 = start list of chunk j o permutation j, seeded
  *                         with symbolToByte; overwrites every permutation with the chunk's start list in place.
  *   K2e  mtfExpandKernel  one WARP per chunk: symbolic byte -> real byte through the start list, RUNA/RUNB symbol at
@@ -42,10 +42,50 @@ k2Scratch( uint32_t* scratchAll, uint32_t block )
 }
 
 /* ---------------------------------------------------------------- K2c ---------------------------------------- */
+/* The list as 16 quads of 16 entries: quad 0 lives in registers, quads 1..15 in the lane's own shared-memory column
+ * ([quad][thread], so the 32 lanes of a 16-byte access cover 512 contiguous bytes).  Shifting a whole quad per
+ * iteration instead of a word takes half the instructions per byte moved, and a quarter-warp none of whose lanes still
+ * has quads to shift costs no shared-memory wavefront -- with 32-bit accesses every iteration cost one as long as a
+ * single lane of the warp was still shifting (measured: 15 of 32 lanes active, the LSU pipe 96 % busy). */
+__device__ __forceinline__ uint32_t
+quadWord( const uint4& q, uint32_t w )
+{
+    return w == 0 ? q.x : ( w == 1 ? q.y : ( w == 2 ? q.z : q.w ) );
+}
+
+/* entries move up by one, `in` becomes entry 0; returns the entry pushed out */
+__device__ __forceinline__ uint32_t
+shiftQuad( uint4& q, uint32_t in )
+{
+    const uint32_t out = q.w >> 24;
+    q.w = __funnelshift_l( q.z, q.w, 8 );
+    q.z = __funnelshift_l( q.y, q.z, 8 );
+    q.y = __funnelshift_l( q.x, q.y, 8 );
+    q.x = ( q.x << 8 ) | in;
+    return out;
+}
+
+/* entries 0 .. e - 1 of the quad move up by one (entry e is overwritten), `in` becomes entry 0; e = 4 w + sh / 8 */
+__device__ __forceinline__ void
+shiftQuadBelow( uint4& q, uint32_t w, uint32_t sh, uint32_t in )
+{
+    uint4 y = q;
+    shiftQuad( y, in );
+    const uint32_t keep = ( sh == 24U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );   /* entries above e inside its word */
+    const uint32_t k0 = w == 0 ? keep : 0U;
+    const uint32_t k1 = w == 1 ? keep : ( w > 1 ? 0U : 0xFFFFFFFFU );
+    const uint32_t k2 = w == 2 ? keep : ( w > 2 ? 0U : 0xFFFFFFFFU );
+    const uint32_t k3 = w == 3 ? keep : 0xFFFFFFFFU;
+    q.x = ( q.x & k0 ) | ( y.x & ~k0 );
+    q.y = ( q.y & k1 ) | ( y.y & ~k1 );
+    q.z = ( q.z & k2 ) | ( y.z & ~k2 );
+    q.w = ( q.w & k3 ) | ( y.w & ~k3 );
+}
+
 __global__ void __launch_bounds__( MTFC_THREADS )
 mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scratchAll )
 {
-    __shared__ uint32_t lists[64][MTFC_THREADS];   /* [word][thread]: thread t only ever touches bank t % 32 */
+    __shared__ uint4 lists[16][MTFC_THREADS];   /* [quad][thread]; row 0 is not used (registers) */
 
     const uint32_t block = blockIdx.y;
     const BlockMeta& bm = meta[block];
@@ -62,7 +102,7 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
     uint8_t* const scratch = k2Scratch( scratchAll, block );
     const uint16_t* const sym16 = reinterpret_cast<const uint16_t*>( scratch + K2_SYM16_OFFSET ) + begin;
     uint32_t* const sym8 = reinterpret_cast<uint32_t*>( scratch + K2_SYM8_OFFSET + begin );
-    uint32_t* const listOut = reinterpret_cast<uint32_t*>( scratch + K2_LISTS_OFFSET + static_cast<uint64_t>( chunk ) * 256U );
+    uint4* const listOut = reinterpret_cast<uint4*>( scratch + K2_LISTS_OFFSET + static_cast<uint64_t>( chunk ) * 256U );
     ChunkCheckpoint* const ckpt = reinterpret_cast<ChunkCheckpoint*>( scratch + K2_CKPT_OFFSET ) + chunk;
 
     /* digits of a RUNA/RUNB number directly in front of the chunk (bzip2.hpp:726-743: runPos = 1 << digits) */
@@ -74,13 +114,14 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
     bool longRun = runDigits > MAX_RUN_DIGITS;
     uint32_t produced = 0;   /* bytes of L the chunk's symbols stand for */
 
-    uint32_t* const my = &lists[0][threadIdx.x];
+    uint4* const my = &lists[0][threadIdx.x];
     constexpr uint32_t STRIDE = MTFC_THREADS;
 #pragma unroll
-    for ( uint32_t w = 1; w < 64U; ++w ) {
-        my[w * STRIDE] = 0x03020100U + 0x04040404U * w;
+    for ( uint32_t q = 1; q < 16U; ++q ) {
+        const uint32_t first = 0x03020100U + 0x10101010U * q;
+        my[q * STRIDE] = make_uint4( first, first + 0x04040404U, first + 0x08080808U, first + 0x0C0C0C0CU );
     }
-    uint32_t r0 = 0x03020100U;   /* list entries 0..3 */
+    uint4 head = make_uint4( 0x03020100U, 0x07060504U, 0x0B0A0908U, 0x0F0E0D0CU );   /* list entries 0..15 */
 
     for ( uint32_t base = 0; base < count; base += 8U ) {
         /* 8 symbols per 16-byte load; `begin` is a multiple of 1024 symbols, so the loads are aligned */
@@ -90,7 +131,7 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
 #pragma unroll
         for ( uint32_t k = 0; k < 8U; ++k ) {
             const uint32_t sym = ( packed[k >> 1] >> ( 16U * ( k & 1U ) ) ) & 0xFFFFU;
-            uint32_t o = r0 & 0xFFU;
+            uint32_t o = head.x & 0xFFU;
             if ( base + k < count ) {
                 const bool isRun = sym <= 1U;
                 produced += isRun ? ( ( sym + 1U ) << min( runDigits, MAX_RUN_DIGITS ) ) : 1U;
@@ -99,26 +140,28 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
             }
             if ( ( sym >= 2U ) && ( base + k < count ) ) {
                 const uint32_t idx = sym - 1U;   /* 1..255 */
+                const uint32_t w = ( idx >> 2 ) & 3U;
+                const uint32_t sh = 8U * ( idx & 3U );
                 if ( idx < 4U ) {
-                    const uint32_t sh = 8U * idx;
-                    o = ( r0 >> sh ) & 0xFFU;
+                    o = ( head.x >> sh ) & 0xFFU;
                     const uint32_t keep = ( idx == 3U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );
-                    r0 = ( r0 & keep ) | ( ( ( r0 << 8 ) | o ) & ~keep );
+                    head.x = ( head.x & keep ) | ( ( ( head.x << 8 ) | o ) & ~keep );
+                } else if ( idx < 16U ) {
+                    o = ( quadWord( head, w ) >> sh ) & 0xFFU;
+                    shiftQuadBelow( head, w, sh, o );
                 } else {
-                    const uint32_t W = idx >> 2;
-                    const uint32_t sh = 8U * ( idx & 3U );
-                    const uint32_t last = my[W * STRIDE];
-                    o = ( last >> sh ) & 0xFFU;
-                    uint32_t carry = r0 >> 24;
-                    r0 = ( r0 << 8 ) | o;
-#pragma unroll 4
-                    for ( uint32_t w = 1; w < W; ++w ) {
-                        const uint32_t x = my[w * STRIDE];
-                        my[w * STRIDE] = ( x << 8 ) | carry;
-                        carry = x >> 24;
+                    const uint32_t Q = idx >> 4;
+                    uint4 last = my[Q * STRIDE];
+                    o = ( quadWord( last, w ) >> sh ) & 0xFFU;
+                    uint32_t carry = shiftQuad( head, o );
+#pragma unroll 2
+                    for ( uint32_t q = 1; q < Q; ++q ) {
+                        uint4 x = my[q * STRIDE];
+                        carry = shiftQuad( x, carry );
+                        my[q * STRIDE] = x;
                     }
-                    const uint32_t keep = ( sh == 24U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );
-                    my[W * STRIDE] = ( last & keep ) | ( ( ( last << 8 ) | carry ) & ~keep );
+                    shiftQuadBelow( last, w, sh, carry );
+                    my[Q * STRIDE] = last;
                 }
             }
             out[k >> 2] |= o << ( 8U * ( k & 3U ) );
@@ -128,10 +171,10 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
     }
 
     *ckpt = ChunkCheckpoint{ produced, runShift | ( longRun ? LONG_RUN_FLAG : 0U ) };
-    listOut[0] = r0;
-#pragma unroll 8
-    for ( uint32_t w = 1; w < 64U; ++w ) {
-        listOut[w] = my[w * STRIDE];
+    listOut[0] = head;
+#pragma unroll 5
+    for ( uint32_t q = 1; q < 16U; ++q ) {
+        listOut[q] = my[q * STRIDE];
     }
 }
 
