@@ -344,7 +344,7 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
 }
 
 /* ------------------------------------------------------------------ place ----------------------------------- */
-constexpr int PLACE_THREADS = 256;
+constexpr int PLACE_THREADS = 64;
 constexpr uint32_t PLACE_CTAS_PER_BLOCK = ( MAX_COARSE + PLACE_THREADS - 1 ) / PLACE_THREADS;
 
 /* len staged bytes of a segment (slot is 256-byte aligned) -> dst[0 .. len): bytes up to the first 4-byte boundary of
