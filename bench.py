@@ -217,9 +217,10 @@ KERNELS = {"find_ms": "K1 findMagicsKernel", "huffman_bits_ms": "K2b huffmanBits
 
 
 # DRAM bytes (read + write) of one launch from the ncu capture of this same command on one B200
-# (profiles/r1_v13_launches.csv: dram__bytes_read.sum + dram__bytes_write.sum); only valid for the default workload at N=1
-NCU_TRAFFIC_8GB = {"find_ms": 4.9e9, "huffman_bits_ms": 16.5e9, "bwt_prepare_ms": 49.6e9, "bwt_walk_ms": 229.5e9,
-                   "rle_scan_ms": 48.0e9, "rle_write_ms": 48.2e9, "crc_ms": 8.0e9}
+# (profiles/r1_v25_launches.csv: dram__bytes_read.sum + dram__bytes_write.sum, summed over the launches of a step);
+# only valid for the default workload at N=1
+NCU_TRAFFIC_8GB = {"find_ms": 4.9e9, "huffman_bits_ms": 16.5e9, "bwt_prepare_ms": 49.7e9, "bwt_walk_ms": 107.4e9,
+                   "rle_scan_ms": 20.2e9, "rle_write_ms": 24.3e9, "crc_ms": 8.0e9}
 
 
 def algorithmic_bytes(stage: str, c: int, n: int, u: int) -> int:
@@ -381,7 +382,7 @@ def run_ours(args):
                     "unit": "GB/s", "frac": round(achieved / peak, 5),
                     "traffic": (NCU_TRAFFIC_8GB[dominant] if (world == 1 and args.kind == "mixed" and args.copies == 8
                                                              and args.base_bytes == 1_000_000_000 and args.level == 9) else None),
-                    "traffic_source": "profiles/r1_v13_launches.csv (ncu, same command, per launch)",
+                    "traffic_source": "profiles/r1_v25_launches.csv (ncu, same command, launches of one step)",
                     "peak_source": peak_src,
                     "launches_per_step": waves, "ms_per_launch": round(per_step[dominant] / waves, 4),
                     "algorithmic_bytes_per_step": alg, "rank": 0,
