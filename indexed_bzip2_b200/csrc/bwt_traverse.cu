@@ -4,28 +4,30 @@
  * (BurrowsWheelerTransformData::decodeBlock, indexed_bzip2/bzip2.hpp:863-879, without its RLE1 / CRC half).
  *
  * The walk is a dependent-load chain, so it is broken up by list ranking: every position that is a multiple of
- * TRAV_SPACING is a "splitter", the stretch from one splitter to the next one met is a segment (geometric lengths, mean
- * TRAV_SPACING), segments are walked independently and put in order afterwards.
+ * TRAV_SPACING (16) is a "splitter", the stretch from one splitter to the next one met is a segment (geometric lengths,
+ * mean TRAV_SPACING), segments are walked independently and put in order afterwards.
  *
- *   bwtWalkKernel   ONE persistent grid for all blocks of the wave.  A random 4-byte read costs HBM a whole 128-byte
- *                   line (measured: 114 B of DRAM traffic per entry when the T vectors of ~300 blocks are walked at
- *                   once), but all 32 entries of a line are wanted eventually -- so the walk keeps the T vectors it
- *                   is working on INSIDE L2: segments are handed out in block order from one global counter (a warp
- *                   takes TRAV_CHUNK at a time, its lanes take the next one whenever they finish, nobody waits for a
- *                   slow lane), and the number of threads in flight is chosen so that the blocks being walked --
- *                   exponentially distributed behind the head of the queue with a mean of threads / segments per
- *                   block = 5.4 blocks = 19 MB -- fit L2 several times over.  Every line is then fetched from HBM
- *                   about once and hit 31 more times.
- *                   The bytes a segment meets go to the segment's own slot (TRAV_SLOT_BYTES, four at a time);
- *                   of a longer segment (0.03 % at 512 bytes; 1.8 % at 256, whose re-walks made up most of the place
- *                   kernel's time) only the position after TRAV_SLOT_BYTES steps is kept.
- *   bwtOrderKernel  one CTA per block: the successor list of the <= 14063 segments is ranked in shared memory by
- *                   pointer jumping (Wyllie), cut at the segment that passes through p0; that gives every segment on
- *                   p0's cycle its output offset; each thread then copies its segments' slots to their places
- *                   (aligned 4-byte stores) and re-walks what did not fit a slot.
- *           fill    if p0's cycle is shorter than N (periodic data such as b"A" * n, where T splits into many short
+ *   bwtWalkKernel   ONE persistent grid for all blocks of the (sub-)wave.  A random 4-byte read costs HBM a whole
+ *                   128-byte line (measured: 114 B of DRAM traffic per entry when the T vectors of ~300 blocks are
+ *                   walked at once), but all 32 entries of a line are wanted eventually -- so the walk keeps the T
+ *                   vectors it is working on INSIDE L2: segments are handed out in block order from one global counter
+ *                   (a warp takes TRAV_CHUNK at a time, its lanes take the next one whenever they finish, nobody waits
+ *                   for a slow lane), so the blocks being walked are exponentially distributed behind the head of the
+ *                   queue with a mean of threads in flight / segments per block = 151 552 / 56 250 = 2.7 blocks =
+ *                   10 MB of T.  (With a splitter every 64 entries it was 5.4 blocks at half the threads, and the walk
+ *                   took twice as long.)  What bounds it now is the L2 -> SM path: a 32-byte sector per 4-byte step.
+ *                   The bytes a segment meets go to the segment's own slot (TRAV_SLOT_BYTES, 16 at a time); of a
+ *                   longer segment (0.03 %) only the position after TRAV_SLOT_BYTES steps is kept.
+ *   bwtRankKernel   one CTA per block.  56 250 segments do not fit a shared-memory ranking, so only every fourth
+ *                   splitter is ranked: a thread follows the chain of segments from such a "coarse" splitter to the
+ *                   next one (one uint2 load per hop), the <= 14 063 chains are ranked in shared memory by pointer
+ *                   jumping (Wyllie), cut at the chain that passes through p0; that gives every chain on p0's cycle
+ *                   its output offset.
+ *   bwtPlaceKernel  one thread per chain: the slots of its segments go to one contiguous stretch of the output
+ *                   (aligned 4-byte stores); what did not fit a slot is walked again.
+ *   bwtFillKernel   if p0's cycle is shorter than N (periodic data such as b"A" * n, where T splits into many short
  *                   cycles) the walk laps its cycle; the remaining output is the periodic continuation of the first lap.
- * A block whose start cycle contains no splitter at all (only tiny cycles can) is walked serially by one thread.
+ * A block whose start cycle contains no coarse splitter at all (only short cycles can) is walked serially by one thread.
  *
  * The output is the block's byte string BEFORE RLE1 undo ("prerle"), N bytes, written over the block's L buffer.
  * Algorithmic HBM traffic per block: 4N bytes of T read once + N bytes staged, read back and written.
