@@ -42,12 +42,13 @@ struct PrepShared
 
 /* Lanes holding the same 9-bit key (what match.any returns), from one ballot per key bit: match.any itself costs a trip
  * per DISTINCT value in the warp, which is 32 trips per row on high-entropy data. */
+template<uint32_t BITS>
 __device__ __forceinline__ uint32_t
 matchKey( uint32_t key )
 {
     uint32_t same = FULL;
 #pragma unroll
-    for ( uint32_t bit = 0; bit < 9U; ++bit ) {
+    for ( uint32_t bit = 0; bit < BITS; ++bit ) {
         const bool set = ( ( key >> bit ) & 1U ) != 0;
         const uint32_t votes = __ballot_sync( FULL, set );
         same &= set ? votes : ~votes;
@@ -178,7 +179,10 @@ bwtPrepareKernel( const uint8_t* __restrict__ lbytesAll, uint32_t* __restrict__ 
         for ( uint32_t r = 0; r < ROWS; ++r ) {
             const uint32_t i = first + 32U * r;
             const uint32_t key = i < n ? lbytes[i] : INVALID_KEY;
-            const uint32_t same = matchKey( key );
+            /* L comes in runs: a row of one byte value needs no ballots at all; a row inside the block has 8-bit keys */
+            const uint32_t firstKey = __shfl_sync( FULL, key, 0 );
+            const uint32_t same = __all_sync( FULL, key == firstKey ) ? FULL
+                                  : ( ( first - lane + 32U * r + 32U <= n ) ? matchKey<8>( key ) : matchKey<9>( key ) );
             const uint32_t leader = static_cast<uint32_t>( __ffs( static_cast<int>( same ) ) ) - 1U;
             uint32_t before = 0;
             if ( ( lane == leader ) && ( key != INVALID_KEY ) ) {

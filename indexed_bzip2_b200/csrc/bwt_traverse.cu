@@ -60,7 +60,7 @@ constexpr uint32_t FULL = 0xFFFFFFFFU;
 constexpr uint32_t TRAV_CHUNK = 64;                                              /* segments a warp takes at a time */
 constexpr uint32_t CHUNKS_PER_BLOCK = ( MAX_SEGMENTS + TRAV_CHUNK - 1U ) / TRAV_CHUNK;   /* 220 */
 constexpr int WALK_THREADS_DEFAULT = 1024;                                       /* per SM */
-constexpr uint32_t WALK_STEPS = 4;                                               /* steps per look at the pool */
+constexpr uint32_t WALK_STEPS = 8;                                               /* steps per look at the pool */
 
 struct BlockStage
 {
