@@ -165,7 +165,7 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
         /* K4a stores ( T[k] << 8 ) | L[T[k]] (the byte of the NEXT position) instead of the reference's
          * ( T[k] << 8 ) | L[k], so the walk starts at origPtr itself and every load yields the output byte and the
          * next position at once (the reference first hops to T[origPtr], bzip2.hpp:835-838).
-         * WALK_STEPS steps between two looks at the pool: a lane that finishes early idles for at most three steps. */
+         * WALK_STEPS steps between two looks at the pool: a lane that finishes early idles for at most seven steps (2 / 4 / 8 steps: 48.1 / 45.6 / 44.7 ms). */
 #pragma unroll
         for ( uint32_t u = 0; u < WALK_STEPS; ++u ) {
             if ( active ) {
