@@ -16,8 +16,9 @@
  *                   queue with a mean of threads in flight / segments per block = 151 552 / 56 250 = 2.7 blocks =
  *                   10 MB of T.  (With a splitter every 64 entries it was 5.4 blocks at half the threads, and the walk
  *                   took twice as long.)  What bounds it now is the L2 -> SM path: a 32-byte sector per 4-byte step.
- *                   The bytes a segment meets go to the segment's own slot (TRAV_SLOT_BYTES, 16 at a time); of a
- *                   longer segment (0.03 %) only the position after TRAV_SLOT_BYTES steps is kept.
+ *                   The bytes a segment meets go to the segment's own slot (64 bytes, 16 at a time: two slots per
+ *                   line), those of the 1.8 % of longer segments go on in a second, 128-byte slot; of a segment longer
+ *                   than both only the position after 192 steps is kept.
  *   bwtRankKernel   one CTA per block.  56 250 segments do not fit a shared-memory ranking, so only every fourth
  *                   splitter is ranked: a thread follows the chain of segments from such a "coarse" splitter to the
  *                   next one (one uint2 load per hop), the <= 14 063 chains are ranked in shared memory by pointer
@@ -53,6 +54,8 @@ constexpr uint32_t STAR_COARSE_SLOT = MAX_COARSE + 1U;
 constexpr uint32_t STAR_STEP_SLOT = MAX_COARSE + 2U;
 static_assert( STAR_STEP_SLOT < TRAV_SEG_CAP, "kept in the segBase array" );
 constexpr uint32_t SLOT = TRAV_SLOT_BYTES;
+constexpr uint32_t SLOT2 = TRAV_SLOT2_BYTES;
+constexpr uint32_t STAGED_MAX = SLOT + SLOT2;   /* bytes of a segment that are staged; the rest is walked again */
 constexpr uint32_t NIL = 0xFFFFU;
 constexpr uint32_t NOT_ON_CYCLE = 0xFFFFFFFFU;
 constexpr uint32_t FULL = 0xFFFFFFFFU;
@@ -65,8 +68,9 @@ constexpr uint32_t WALK_STEPS = 8;                                              
 struct BlockStage
 {
     uint8_t* slots;      /* [segment][SLOT] */
+    uint8_t* slots2;     /* [segment][SLOT2]: bytes SLOT .. SLOT + SLOT2 - 1 of the segments that have them */
     uint2* segLink;      /* x: steps from the segment's splitter to the next splitter, y: that splitter (segment index) */
-    uint32_t* ovfPos;    /* position reached after SLOT steps (only meaningful when segLen > SLOT) */
+    uint32_t* ovfPos;    /* position reached after STAGED_MAX steps (only meaningful when the segment is longer) */
     uint32_t* segBase;   /* bwtRankKernel: output offset of the first byte of every COARSE segment on p0's cycle,
                           * NOT_ON_CYCLE for the others; behind them the coarse segment whose chain passes through p0
                           * and the step at which it does */
@@ -78,6 +82,7 @@ blockStage( uint8_t* stageAll, uint32_t block )
     uint8_t* const base = stageAll + TRAV_STAGE_HEADER + static_cast<uint64_t>( block ) * TRAV_STAGE_STRIDE;
     BlockStage st;
     st.slots = base;
+    st.slots2 = base + TRAV_SLOT2_OFFSET;
     st.segLink = reinterpret_cast<uint2*>( base + TRAV_LINK_OFFSET );
     st.ovfPos = reinterpret_cast<uint32_t*>( base + TRAV_OVF_OFFSET );
     st.segBase = reinterpret_cast<uint32_t*>( base + TRAV_BASE_OFFSET );
@@ -105,6 +110,7 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
     bool active = false;
     const uint32_t* dbuf = nullptr;
     uint4* slotQuads = nullptr;
+    uint4* slot2Quads = nullptr;
     uint4 quad = make_uint4( 0, 0, 0, 0 );
     uint32_t myBlock = 0;
     uint32_t s = 0;
@@ -148,9 +154,12 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
                 myBlock = poolBlock;
                 p0 = poolP0;
                 dbuf = dbufAll + static_cast<uint64_t>( poolBlock ) * DBUF_STRIDE;
-                slotQuads = reinterpret_cast<uint4*>( stageAll + TRAV_STAGE_HEADER
-                                                         + static_cast<uint64_t>( poolBlock ) * TRAV_STAGE_STRIDE
-                                                         + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT ) );
+                {
+                    uint8_t* const blockBase = stageAll + TRAV_STAGE_HEADER + static_cast<uint64_t>( poolBlock ) * TRAV_STAGE_STRIDE;
+                    slotQuads = reinterpret_cast<uint4*>( blockBase + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT ) );
+                    slot2Quads = reinterpret_cast<uint4*>( blockBase + TRAV_SLOT2_OFFSET
+                                                           + ( static_cast<uint64_t>( s ) << TRAV_SLOT2_SHIFT ) );
+                }
                 pos = s << SPACING_SHIFT;
                 steps = 0;
                 acc = 0;
@@ -184,26 +193,28 @@ bwtWalkKernel( const uint32_t* __restrict__ dbufAll, BlockMeta* __restrict__ met
                     quad.y = w == 1 ? acc : quad.y;
                     quad.z = w == 2 ? acc : quad.z;
                     quad.w = w == 3 ? acc : quad.w;
-                    if ( ( w == 3 ) && ( steps <= SLOT ) ) {
-                        __stcs( slotQuads + ( steps >> 4 ) - 1U, quad );
+                    if ( ( w == 3 ) && ( steps <= STAGED_MAX ) ) {
+                        const uint32_t q = ( steps >> 4 ) - 1U;
+                        __stcs( q < SLOT / 16U ? slotQuads + q : slot2Quads + ( q - SLOT / 16U ), quad );
                     }
                     acc = 0;
                 }
                 pos = e >> 8;
-                if ( steps == SLOT ) {
+                if ( steps == STAGED_MAX ) {
                     blockStage( stageAll, myBlock ).ovfPos[s] = pos;
                 }
                 if ( ( pos & ( SPACING - 1U ) ) == 0 ) {
                     const BlockStage st = blockStage( stageAll, myBlock );
                     st.segLink[s] = make_uint2( steps, pos >> SPACING_SHIFT );
-                    if ( ( ( steps & 15U ) != 0 ) && ( steps < SLOT ) ) {
+                    if ( ( ( steps & 15U ) != 0 ) && ( steps < STAGED_MAX ) ) {
                         /* the last, partly filled quad (what lies behind the segment's bytes is never read) */
                         const uint32_t w = ( steps >> 2 ) & 3U;
                         quad.x = w == 0 ? acc : quad.x;
                         quad.y = w == 1 ? acc : quad.y;
                         quad.z = w == 2 ? acc : quad.z;
                         quad.w = w == 3 ? acc : quad.w;
-                        __stcs( slotQuads + ( steps >> 4 ), quad );
+                        const uint32_t q = steps >> 4;
+                        __stcs( q < SLOT / 16U ? slotQuads + q : slot2Quads + ( q - SLOT / 16U ), quad );
                     }
                     active = false;
                 }
@@ -431,22 +442,27 @@ bwtPlaceKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prer
         const bool behindP0 = starChain && ( d >= kstarCoarse ) && !star;
         const uint32_t base = behindP0 ? d - kstarCoarse : coarseBase + d;
         const uint8_t* const slot = st.slots + ( static_cast<uint64_t>( s ) << TRAV_SLOT_SHIFT );
-        const uint32_t staged = min( len, SLOT );
+        const uint8_t* const slot2 = st.slots2 + ( static_cast<uint64_t>( s ) << TRAV_SLOT2_SHIFT );
+        const uint32_t staged = min( len, STAGED_MAX );
         if ( star ) {
             /* steps kstarFine .. len - 1 open the output, steps 0 .. kstarFine - 1 close the lap */
             for ( uint32_t k = 0; k < staged; ++k ) {
                 const uint32_t idx = k >= kstarFine ? k - kstarFine : base + k;
                 if ( idx < n ) {
-                    prerle[idx] = slot[k];
+                    prerle[idx] = k < SLOT ? slot[k] : slot2[k - SLOT];
                 }
             }
         } else if ( base < n ) {
-            placeStaged( slot, prerle + base, min( staged, n - base ) );
+            const uint32_t fits = min( staged, n - base );
+            placeStaged( slot, prerle + base, min( fits, SLOT ) );
+            if ( fits > SLOT ) {
+                placeStaged( slot2, prerle + base + SLOT, fits - SLOT );
+            }
         }
-        if ( len > SLOT ) {
-            /* the rest of a long segment: walked again from where the slot ended */
+        if ( len > STAGED_MAX ) {
+            /* the rest of a very long segment: walked again from where the second slot ended */
             uint32_t pos = st.ovfPos[s];
-            for ( uint32_t k = SLOT; k < len; ++k ) {
+            for ( uint32_t k = STAGED_MAX; k < len; ++k ) {
                 const uint32_t e = __ldcg( dbuf + pos );
                 const uint32_t idx = ( star && ( k >= kstarFine ) ) ? ( k - kstarFine ) : ( base + k );
                 if ( idx < n ) {

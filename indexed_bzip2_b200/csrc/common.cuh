@@ -179,9 +179,12 @@ constexpr uint32_t TRAV_SPACING = 1U << TRAV_SPACING_SHIFT;                    /
 constexpr uint32_t TRAV_COARSE_SHIFT = 6;                                      /* every 64: the ones that get ranked */
 constexpr uint32_t TRAV_MAX_SEGMENTS = ( DBUF_SIZE + TRAV_SPACING - 1U ) / TRAV_SPACING;   /* 56250 */
 constexpr uint32_t TRAV_SEG_CAP = ( TRAV_MAX_SEGMENTS + 63U ) & ~63U;          /* 56256 */
-constexpr uint32_t TRAV_SLOT_SHIFT = 7;
-constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 8 x the mean segment length */
-constexpr uint64_t TRAV_LINK_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;   /* uint2: length, successor */
+constexpr uint32_t TRAV_SLOT_SHIFT = 6;
+constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 4 x the mean segment length: two slots per line */
+constexpr uint32_t TRAV_SLOT2_SHIFT = 7;                                       /* where the 1.8 % of longer segments go on */
+constexpr uint32_t TRAV_SLOT2_BYTES = 1U << TRAV_SLOT2_SHIFT;
+constexpr uint64_t TRAV_SLOT2_OFFSET = static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT_BYTES;
+constexpr uint64_t TRAV_LINK_OFFSET = TRAV_SLOT2_OFFSET + static_cast<uint64_t>( TRAV_SEG_CAP ) * TRAV_SLOT2_BYTES;   /* uint2: length, successor */
 constexpr uint64_t TRAV_OVF_OFFSET = TRAV_LINK_OFFSET + TRAV_SEG_CAP * 8ULL;
 constexpr uint64_t TRAV_BASE_OFFSET = TRAV_OVF_OFFSET + TRAV_SEG_CAP * 4ULL;    /* u32: output offset of the segment's first byte */
 constexpr uint64_t TRAV_STAGE_STRIDE = ( TRAV_BASE_OFFSET + TRAV_SEG_CAP * 4ULL + 255ULL ) & ~255ULL;
