@@ -360,8 +360,8 @@ bwtRankKernel( const uint32_t* __restrict__ dbufAll, uint8_t* __restrict__ prerl
 constexpr int PLACE_THREADS = 64;
 constexpr uint32_t PLACE_CTAS_PER_BLOCK = ( MAX_COARSE + PLACE_THREADS - 1 ) / PLACE_THREADS;
 
-/* len staged bytes of a segment (slot is 256-byte aligned) -> dst[0 .. len): bytes up to the first 4-byte boundary of
- * dst, then whole words put together from two neighbouring slot words, 64 slot bytes per round of loads. */
+/* len staged bytes of a segment (slot is 64-byte aligned) -> dst[0 .. len): bytes up to the first 4-byte boundary of
+ * dst, then whole words put together from two neighbouring slot words, 16 slot bytes per round of loads. */
 __device__ __forceinline__ void
 placeStaged( const uint8_t* __restrict__ slot, uint8_t* __restrict__ dst, uint32_t len )
 {
@@ -375,24 +375,14 @@ placeStaged( const uint8_t* __restrict__ slot, uint8_t* __restrict__ dst, uint32
     const uint32_t shift = 8U * head;
     const uint32_t outWords = ( len - head ) >> 2;
     uint32_t* const out = reinterpret_cast<uint32_t*>( dst + head );
-    for ( uint32_t done = 0; done < outWords; done += 16U ) {
-        /* slot words done .. done + 16; what lies behind the bytes wanted is never used (and still inside the block's
-         * staging area) */
-        uint32_t w[17];
+    /* 16 slot bytes per round: most segments are done after one or two */
+    for ( uint32_t done = 0; done < outWords; done += 4U ) {
+        const uint4 v = __ldg( slotQuads + ( done >> 2 ) );
+        /* what lies behind the bytes wanted is never used (and still inside the block's staging area) */
+        const uint32_t next = __ldg( slotWords + done + 4U );
+        const uint32_t w[5] = { v.x, v.y, v.z, v.w, next };
 #pragma unroll
-        for ( uint32_t q = 0; q < 4U; ++q ) {
-            uint4 v = make_uint4( 0, 0, 0, 0 );
-            if ( done + 4U * q <= outWords ) {
-                v = __ldg( slotQuads + ( done >> 2 ) + q );
-            }
-            w[4U * q + 0U] = v.x;
-            w[4U * q + 1U] = v.y;
-            w[4U * q + 2U] = v.z;
-            w[4U * q + 3U] = v.w;
-        }
-        w[16] = ( done + 16U <= outWords ) ? __ldg( slotWords + done + 16U ) : 0U;
-#pragma unroll
-        for ( uint32_t i = 0; i < 16U; ++i ) {
+        for ( uint32_t i = 0; i < 4U; ++i ) {
             if ( done + i < outWords ) {
                 out[done + i] = __funnelshift_r( w[i], w[i + 1U], shift );
             }
