@@ -2,24 +2,29 @@
  * K2b -- the Huffman symbol loop of Block::readBlockData (indexed_bzip2/bzip2.hpp:709-723 and :766-768, with
  * huffman/HuffmanCodingShortBitsCached.hpp:98-150), one LANE per bzip2 block.
  *
- * The bit stream of a block is a dependent chain (window -> LUT -> code length -> shift); nothing inside one block can
- * shorten it, so the chip is filled with as many independent chains as shared memory allows:
- *   - every SM runs one persistent CTA of 32 / BITS_LANES warps with BITS_LANES active lanes each = 32 decoders per SM;
- *   - the six 9-bit LUTs of a decoder's block (K2a's BlockTables::lut, 6 KB) sit in shared memory as
- *     u16 lut[index][table][slot]: the decoders of one warp are neighbouring slots, i.e. they read different
- *     banks whatever they look up, and an entry's address is one shift and one multiply-add away from the window;
- *   - decoders pull block indices from a global counter; the unit of lockstep inside a warp is one GROUP of 50 symbols
- *     (the table switch of bzip2.hpp:710-721), so a decoder that finishes its block waits at most 49 symbols for its
- *     warp before it fetches the next block;
- *   - the loop does nothing but decode: refill (every second symbol), look up, shift, store the symbol, test for the
- *     end-of-block symbol.  The dbufCount / RUNA-RUNB bookkeeping of bzip2.hpp:726-790 is chunk-parallel work and
- *     happens in K2c..K2e (mtf.cu).
+ * The bit stream of a block is a dependent chain (window -> table -> code length -> shift); nothing inside one block can
+ * shorten it, so (a) the chip holds as many independent chains as possible and (b) the chain carries nothing but the
+ * code LENGTH:
+ *   - a decoder keeps six 9-bit tables of u8 code lengths in shared memory (3 KB, contiguous per decoder, so the address
+ *     of an entry is "table base + top nine bits": one LEA.HI away from the window) plus the 0.4 KB of per-length limits
+ *     that codes of 10..20 bits need: 3.5 KB per decoder, 32 decoders per CTA, two CTAs per SM = 64 chains per SM,
+ *     9472 per chip, i.e. every block of the 8 GB workload decodes in ONE round;
+ *   - what a decoder stores per symbol is the table entry it hit, ( table << 9 ) | index (or 0x8000 | table << 9 |
+ *     rank for a long code); the symbol itself is not needed to go on, and resolveSymbolsKernel turns the entries into
+ *     symbols afterwards at memory speed;
+ *   - the window is two big-endian words A:B and a bit position; three symbols are decoded per refill test (a symbol of
+ *     the table takes at most 9 bits and the position is below 32 when a triple starts), each one a shift of the first
+ *     symbol's 32 window bits.  A table entry of 0 (code longer than 9 bits, end-of-block symbol, no code) has length 0:
+ *     the window stays where it is, the rest of the triple misses too, and one test per triple finds it;
+ *   - decoders pull block indices from a global counter (longest compressed block first); the unit of lockstep inside a
+ *     warp is one GROUP of 50 symbols (the table switch of bzip2.hpp:710-721).
+ * The dbufCount / RUNA-RUNB bookkeeping of bzip2.hpp:726-790 is chunk-parallel work and happens in K2c..K2e (mtf.cu).
  * A block leaves this kernel as "clean" (status OK, nCoded symbols stored, endBit set) only when its symbol stream ends
  * with the end-of-block symbol inside the file.  Anything else -- a bit pattern without code, more groups than
- * selectors, the end of the file, more symbols than a block can hold -- marks the block ST_INTERNAL_CAREFUL and the
- * exact state machine in huffman_careful.cu decides what the reference would have thrown.
+ * selectors, the end of the file, more symbols than a block can hold, an empty symbol map -- marks the block
+ * ST_INTERNAL_CAREFUL and the exact state machine in huffman_careful.cu decides what the reference would have thrown.
  *
- * Algorithmic HBM traffic per block: C compressed bytes read, 2 bytes per coded symbol written.
+ * Algorithmic HBM traffic per block: C compressed bytes read, one entry per coded symbol written.
  */
 #include "common.cuh"
 
@@ -30,14 +35,27 @@ namespace ibz2
 {
 namespace
 {
-constexpr int BITS_SLOTS = 32;   /* decoders per SM: the LUT rows are 32 decoders wide */
-constexpr int BITS_LANES_DEFAULT = 4;   /* active lanes per warp; BITS_SLOTS / lanes warps per CTA.  Measured on the 8 GB workload
-                                         * once loads no longer stall the loop: 95.7 / 85.1 / 93.7 ms at 8 / 4 / 2 lanes */
-constexpr uint32_t LUT_ROW_BYTES = BITS_SLOTS * 2U;               /* one u16 per decoder */
-constexpr uint32_t LUT_IDX_STRIDE = MAX_GROUPS * LUT_ROW_BYTES;   /* u16 lut[index][table][decoder] */
-constexpr uint32_t LUT_ENTRIES = MAX_GROUPS * HUFF_LUT_SIZE;      /* 3072 rows */
+constexpr int BITS_SLOTS = 32;          /* decoders per CTA */
+constexpr int BITS_CTAS_PER_SM = 2;
+constexpr int BITS_LANES_DEFAULT = 4;   /* active lanes per warp; BITS_SLOTS / lanes warps per CTA */
 constexpr uint32_t SYM_LIMIT = DBUF_SIZE;                         /* a clean block has at most this many symbols */
 constexpr uint32_t GROUP_MAX_WORDS = ( GROUP_SIZE * MAX_CODE_LEN + 31U ) / 32U + 4U + 96U;   /* + prefetch distance */
+
+/* ---- shared memory of one decoder ---- */
+constexpr uint32_t LONG_FIRST_LEN = HUFF_LUT_BITS;                          /* limits are kept for lengths 9..20 */
+constexpr uint32_t LONG_LIMITS = MAX_CODE_LEN - LONG_FIRST_LEN + 1U;        /* 12 */
+constexpr uint32_t LONG_OFFSETS = MAX_CODE_LEN - LONG_FIRST_LEN;            /* lengths 10..20: 11 */
+constexpr uint32_t DEC_LUT_BYTES = MAX_GROUPS * HUFF_LUT_SIZE;              /* u8 [6][512] code lengths */
+constexpr uint32_t DEC_LIM_OFFSET = DEC_LUT_BYTES;                          /* u32 [6][12], 20-bit left-aligned code limits */
+constexpr uint32_t DEC_LIM_BYTES = MAX_GROUPS * LONG_LIMITS * 4U;
+constexpr uint32_t DEC_OFF_OFFSET = DEC_LIM_OFFSET + DEC_LIM_BYTES;         /* u16 [6][11], perm offset of each length */
+constexpr uint32_t DEC_OFF_BYTES = MAX_GROUPS * LONG_OFFSETS * 2U;
+constexpr uint32_t DEC_EOB_OFFSET = DEC_OFF_OFFSET + DEC_OFF_BYTES;         /* u16 [6], perm index of the end-of-block symbol */
+/* an odd number of words: the same entry of neighbouring decoders sits in different banks */
+constexpr uint32_t DEC_STRIDE = ( ( DEC_EOB_OFFSET + MAX_GROUPS * 2U + 3U ) / 4U | 1U ) * 4U;
+constexpr uint32_t SH_TOTAL_BYTES = BITS_SLOTS * DEC_STRIDE;
+static_assert( BITS_CTAS_PER_SM * ( SH_TOTAL_BYTES + 1024U ) <= 228U * 1024U, "two CTAs per SM" );
+static_assert( DEC_LUT_BYTES <= 0x8000U, "stored entries keep bit 15 for long codes" );
 
 __device__ __forceinline__ void
 prefetchL1( const void* p )
@@ -45,74 +63,19 @@ prefetchL1( const void* p )
     asm volatile( "prefetch.global.L1 [%0];" ::"l"( p ) );
 }
 
-struct Decoder
+__device__ __forceinline__ uint32_t
+ldsU8( uint32_t addr )
 {
-    uint32_t hi;        /* window: next bits, left aligned, 64 bits in hi:lo */
-    uint32_t lo;
-    int nb;             /* valid bits in the window */
-    uint32_t nextW;     /* big-endian word wordIdx of the file, already loaded */
-    uint64_t wordIdx;
-};
-
-__device__ __forceinline__ void
-refillChecked( Decoder& d, const uint8_t* __restrict__ data, uint64_t nbytes )
-{
-    if ( d.nb <= 32 ) {
-        /* d.lo is empty here */
-        d.hi |= d.nb == 32 ? 0U : ( d.nextW >> d.nb );
-        d.lo = d.nb == 0 ? 0U : ( d.nextW << ( 32 - d.nb ) );
-        d.nb += 32;
-        ++d.wordIdx;
-        d.nextW = loadWordBE( data, nbytes, d.wordIdx );
-    }
+    uint32_t v;   /* a wider destination is zero-extended: no separate mask on the dependent chain */
+    asm volatile( "ld.shared.u8 %0, [%1];" : "=r"( v ) : "r"( addr ) );
+    return v;
 }
-
-__device__ __forceinline__ void
-consume( Decoder& d, uint32_t len )
-{
-    d.hi = __funnelshift_l( d.lo, d.hi, len );
-    d.lo <<= len;
-    d.nb -= static_cast<int>( len );
-}
-
-/* Code longer than the LUT width, or no code at all (HuffmanCodingShortBitsCached.hpp:117-150).  Needs 20 valid bits.
- * The caller has established that no code of at most HUFF_LUT_BITS bits matches.  Canonical codes grow with their
- * length when left-aligned, so the length is the number of per-length limits the window has reached; the loads are
- * independent of each other (one L1 line).  Returns ( symbol << 5 ) | length like a LUT entry, 0 for "no code". */
-__device__ __noinline__ uint32_t
-decodeLong( const BlockTables* __restrict__ bt, uint32_t table, uint32_t hi )
-{
-    const uint64_t* const limit = bt->limit[table];
-    uint32_t len = HUFF_LUT_BITS + 1;
-#pragma unroll
-    for ( uint32_t l = HUFF_LUT_BITS + 1; l <= MAX_CODE_LEN; ++l ) {
-        len += ( static_cast<uint64_t>( hi ) >= limit[l] ) ? 1U : 0U;
-    }
-    if ( len > MAX_CODE_LEN ) {
-        return 0;
-    }
-    const uint32_t idx = ( hi >> ( 32U - len ) ) + static_cast<uint32_t>( bt->base[table][len] );
-    return ( static_cast<uint32_t>( bt->perm[table][idx] ) << 5 ) | len;
-}
-
-/* ---- shared memory of one CTA: everything a decoder looks at per symbol, one bank column per decoder ---- */
-constexpr uint32_t LONG_FIRST_LEN = HUFF_LUT_BITS;                          /* limits are kept for lengths 9..20 */
-constexpr uint32_t LONG_LIMITS = MAX_CODE_LEN - LONG_FIRST_LEN + 1U;        /* 12 */
-constexpr uint32_t LONG_OFFSETS = MAX_CODE_LEN - LONG_FIRST_LEN;            /* lengths 10..20: 11 */
-constexpr uint32_t SH_LUT_BYTES = LUT_ENTRIES * LUT_ROW_BYTES;              /* u16 [6 * 512][32] */
-constexpr uint32_t SH_LIM_OFFSET = SH_LUT_BYTES;                            /* u32 [6][12][32], 20-bit left-aligned code limits */
-constexpr uint32_t SH_LIM_BYTES = MAX_GROUPS * LONG_LIMITS * BITS_SLOTS * 4U;
-constexpr uint32_t SH_OFF_OFFSET = SH_LIM_OFFSET + SH_LIM_BYTES;            /* u16 [6][11][32], perm offset of each length */
-constexpr uint32_t SH_OFF_BYTES = MAX_GROUPS * LONG_OFFSETS * BITS_SLOTS * 2U;
-constexpr uint32_t SH_EOB_OFFSET = SH_OFF_OFFSET + SH_OFF_BYTES;            /* u16 [8][32], perm index of the end-of-block symbol */
-constexpr uint32_t SH_TOTAL_BYTES = SH_EOB_OFFSET + 8U * BITS_SLOTS * 2U;
-static_assert( SH_TOTAL_BYTES <= 227U * 1024U, "one CTA per SM" );
 
 __device__ __forceinline__ uint32_t
 ldsU16( uint32_t addr )
 {
-    uint32_t v;   /* a wider destination is zero-extended: no separate mask on the dependent chain */
-    asm volatile( "ld.volatile.shared.u16 %0, [%1];" : "=r"( v ) : "r"( addr ) );
+    uint32_t v;
+    asm volatile( "ld.shared.u16 %0, [%1];" : "=r"( v ) : "r"( addr ) );
     return v;
 }
 
@@ -124,11 +87,28 @@ ldsU32( uint32_t addr )
     return v;
 }
 
-/* LUT entry for the 9 bits on top of the window; tableAddr = shared address of lut[0][table][slot] */
+/* 32-bit word i of the byte stream in memory order (bytes past the end read as zero) */
 __device__ __forceinline__ uint32_t
-lookup( uint32_t tableAddr, uint32_t hi )
+loadWordRaw( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t wordIndex )
 {
-    return ldsU16( ( hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_IDX_STRIDE + tableAddr );   /* shift + multiply-add */
+    const uint64_t byte = wordIndex * 4U;
+    uint32_t w = 0;
+    if ( byte + 4U <= nbytes ) {
+        w = __ldg( reinterpret_cast<const uint32_t*>( data ) + wordIndex );
+    } else {
+        for ( uint32_t k = 0; k < 4U; ++k ) {
+            if ( byte + k < nbytes ) {
+                w |= static_cast<uint32_t>( data[byte + k] ) << ( 8U * k );
+            }
+        }
+    }
+    return w;
+}
+
+__device__ __forceinline__ uint32_t
+bswap( uint32_t raw )
+{
+    return __byte_perm( raw, 0, 0x0123 );
 }
 
 /* A code of more than 9 bits (HuffmanCodingShortBitsCached.hpp:117-150), entirely from shared memory and without the
@@ -142,7 +122,7 @@ decodeLongShared( uint32_t limAddr, uint32_t offAddr, uint32_t hi )
     uint32_t lim[LONG_LIMITS];
 #pragma unroll
     for ( uint32_t i = 0; i < LONG_LIMITS; ++i ) {
-        lim[i] = ldsU32( limAddr + i * ( BITS_SLOTS * 4U ) );
+        lim[i] = ldsU32( limAddr + i * 4U );
     }
     uint32_t len = LONG_FIRST_LEN + 1U;
     uint32_t lower = lim[0];
@@ -156,35 +136,73 @@ decodeLongShared( uint32_t limAddr, uint32_t offAddr, uint32_t hi )
         return 0;
     }
     const uint32_t rel = ( h20 - lower ) >> ( MAX_CODE_LEN - len );
-    const uint32_t idx = ldsU16( offAddr + ( len - LONG_FIRST_LEN - 1U ) * ( BITS_SLOTS * 2U ) ) + rel;
+    const uint32_t idx = ldsU16( offAddr + ( len - LONG_FIRST_LEN - 1U ) * 2U ) + rel;
     return ( idx << 5 ) | len;
 }
 
+/* The bit position of a decoder: A and B are the big-endian words wordIdx and wordIdx + 1 of the file, craw is word
+ * wordIdx + 2 in memory order (swapped when it moves up, so that nothing waits for its load), pos < 32 between symbols. */
+struct Decoder
+{
+    uint32_t A;
+    uint32_t B;
+    uint32_t craw;
+    uint32_t pos;
+    uint64_t wordIdx;
+};
+
+enum : uint32_t { SYM_PLAIN = 0, SYM_EOB = 1, SYM_FAIL = 2 };
+
+/* One symbol the careful way: any code length, the end-of-block symbol, no code at all.  The window must have been
+ * refilled (pos < 32).  *entry = what K2b stores for the symbol. */
+__device__ __forceinline__ uint32_t
+decodeOneSymbol( uint32_t A, uint32_t B, uint32_t& pos, uint32_t lutAddr, uint32_t table, const BlockTables* __restrict__ bt,
+                 uint32_t* entry )
+{
+    const uint32_t tableAddr = lutAddr + table * HUFF_LUT_SIZE;
+    const uint32_t hi = __funnelshift_l( B, A, pos );
+    const uint32_t idx = hi >> ( 32 - HUFF_LUT_BITS );
+    const uint32_t len = ldsU8( tableAddr + idx );
+    if ( len != 0 ) {
+        *entry = ( table << HUFF_LUT_BITS ) | idx;
+        pos += len;
+        return SYM_PLAIN;
+    }
+    const uint32_t limAddr = lutAddr + DEC_LIM_OFFSET + table * ( LONG_LIMITS * 4U );
+    if ( ( hi >> 12 ) < ldsU32( limAddr ) ) {
+        /* a code of at most 9 bits that is not in the shared-memory table: the end-of-block symbol (bzip2.hpp:766-768) */
+        pos += bt->lut[table][idx] & 31U;
+        return SYM_EOB;
+    }
+    const uint32_t r = decodeLongShared( limAddr, lutAddr + DEC_OFF_OFFSET + table * ( LONG_OFFSETS * 2U ), hi );
+    if ( r == 0 ) {
+        return SYM_FAIL;
+    }
+    pos += r & 31U;
+    *entry = 0x8000U | ( table << HUFF_LUT_BITS ) | ( r >> 5 );
+    return ( r >> 5 ) == ldsU16( lutAddr + DEC_EOB_OFFSET + table * 2U ) ? SYM_EOB : SYM_PLAIN;
+}
+
 template<int BITS_LANES>
-__global__ void __launch_bounds__( ( BITS_SLOTS / BITS_LANES ) * 32, 1 )
+__global__ void __launch_bounds__( ( BITS_SLOTS / BITS_LANES ) * 32, BITS_CTAS_PER_SM )
 huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks,
                    const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
                    uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, const uint32_t* __restrict__ order,
                    uint32_t slotsPerCta )
 {
-    extern __shared__ __align__( 16 ) uint8_t lutShared[];
+    extern __shared__ __align__( 16 ) uint8_t decShared[];
     constexpr int BITS_WARPS = BITS_SLOTS / BITS_LANES;
     const uint32_t lane = threadIdx.x & 31U;
     if ( lane >= static_cast<uint32_t>( BITS_LANES ) ) {
         return;
     }
-    /* the lanes of one warp are BITS_WARPS slots apart: different banks whatever they look up; a launch with few blocks
-     * (slotsPerCta < 32) leaves the second lane of every warp idle rather than whole SMs */
+    /* a launch with few blocks (slotsPerCta < 32) leaves the higher lanes of every warp idle rather than whole SMs */
     const uint32_t slot = lane * BITS_WARPS + ( threadIdx.x >> 5 );
     if ( slot >= slotsPerCta ) {
         return;
     }
-    uint8_t* const myLut = lutShared + slot * 2U;
-    const uint32_t sharedBase = static_cast<uint32_t>( __cvta_generic_to_shared( lutShared ) );
-    const uint32_t myLutAddr = sharedBase + slot * 2U;
-    const uint32_t myLimAddr = sharedBase + SH_LIM_OFFSET + slot * 4U;
-    const uint32_t myOffAddr = sharedBase + SH_OFF_OFFSET + slot * 2U;
-    const uint32_t myEobAddr = sharedBase + SH_EOB_OFFSET + slot * 2U;
+    uint8_t* const myDec = decShared + slot * DEC_STRIDE;
+    const uint32_t lutAddr = static_cast<uint32_t>( __cvta_generic_to_shared( decShared ) ) + slot * DEC_STRIDE;
     const uint64_t nbits = nbytes * 8U;
     const uint64_t fullWords = nbytes >> 2;   /* words that can be loaded without looking at the file end */
     const uint32_t* const dataWords = reinterpret_cast<const uint32_t*>( data );
@@ -194,7 +212,6 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
     const BlockTables* bt = nullptr;
     const uint8_t* selectors = nullptr;
     uint16_t* symOut = nullptr;
-    uint32_t symbolCount = 0;
     uint32_t selectorsCount = 0;
     Decoder d{};
     uint32_t nsym = 0;
@@ -210,66 +227,63 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             if ( order != nullptr ) {
                 block = order[block];   /* longest block first: the decoders then finish at about the same time */
             }
-            const BlockMeta& bm = meta[block];
+            BlockMeta& bm = meta[block];
             if ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) {
                 continue;
             }
             bt = tablesAll + block;
+            const uint32_t symbolCount = bt->symbolCount;
+            if ( symbolCount == 0 ) {
+                /* the end-of-block symbol would be 1 = RUNB, which the reference takes for a run symbol first
+                 * (bzip2.hpp:723): such a block never ends cleanly */
+                bm.status = ST_INTERNAL_CAREFUL;
+                continue;
+            }
             selectors = selectorsAll + static_cast<uint64_t>( block ) * SEL_STRIDE;
             symOut = reinterpret_cast<uint16_t*>( reinterpret_cast<uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE )
                                                   + K2_SYM16_OFFSET );
-            symbolCount = bt->symbolCount;
             selectorsCount = bt->selectorsCount;
             {
-                /* LUTs -> this decoder's column */
+                /* code lengths -> this decoder's tables.  The end-of-block symbol is left out: the hot loop then has ONE
+                 * exceptional entry value (0 = "not a plain symbol of at most 9 bits") to test for. */
                 const uint4* src = reinterpret_cast<const uint4*>( &bt->lut[0][0] );
                 const uint32_t groupCount = bt->groupCount;
                 const uint32_t quads = groupCount * ( HUFF_LUT_SIZE / 8U );
+                uint32_t* dst = reinterpret_cast<uint32_t*>( myDec );
                 for ( uint32_t q = 0; q < quads; ++q ) {
                     const uint4 v = __ldg( src + q );
-                    uint32_t w[4] = { v.x, v.y, v.z, v.w };
-                    /* The end-of-block symbol is taken out of the shared-memory copy: the hot loop then has ONE
-                     * exceptional entry value (0 = "not a plain symbol of at most 9 bits") to test for. */
+                    const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+                    uint32_t lens[2] = { 0, 0 };
 #pragma unroll
                     for ( uint32_t i = 0; i < 4U; ++i ) {
-                        const uint32_t a = ( ( w[i] & 0xFFFFU ) >> 5 ) > symbolCount ? 0U : ( w[i] & 0xFFFFU );
-                        const uint32_t b = ( w[i] >> 21 ) > symbolCount ? 0U : ( w[i] >> 16 );
-                        w[i] = a | ( b << 16 );
+                        const uint32_t a = ( ( w[i] & 0xFFFFU ) >> 5 ) > symbolCount ? 0U : ( w[i] & 31U );
+                        const uint32_t b = ( w[i] >> 21 ) > symbolCount ? 0U : ( ( w[i] >> 16 ) & 31U );
+                        lens[i >> 1] |= ( a | ( b << 8 ) ) << ( 16U * ( i & 1U ) );
                     }
-                    /* quad q holds entries 8 * ( q % 64 ) .. + 7 of table q / 64 */
-                    uint8_t* dst = myLut + ( q >> 6 ) * LUT_ROW_BYTES + ( ( q & 63U ) * 8U ) * LUT_IDX_STRIDE;
-#pragma unroll
-                    for ( uint32_t i = 0; i < 4U; ++i ) {
-                        *reinterpret_cast<uint16_t*>( dst ) = static_cast<uint16_t>( w[i] );
-                        *reinterpret_cast<uint16_t*>( dst + LUT_IDX_STRIDE ) = static_cast<uint16_t>( w[i] >> 16 );
-                        dst += 2U * LUT_IDX_STRIDE;
-                    }
+                    dst[2U * q] = lens[0];
+                    dst[2U * q + 1U] = lens[1];
                 }
                 /* what the codes of more than 9 bits need: limits as 20-bit left-aligned values, perm offsets, EOB index */
                 for ( uint32_t g = 0; g < groupCount; ++g ) {
                     for ( uint32_t i = 0; i < LONG_LIMITS; ++i ) {
                         const uint64_t limit = bt->limit[g][LONG_FIRST_LEN + i];   /* <= 2^32, a multiple of 2^12 */
-                        *reinterpret_cast<uint32_t*>( lutShared + SH_LIM_OFFSET + ( ( g * LONG_LIMITS + i ) * BITS_SLOTS + slot ) * 4U )
+                        *reinterpret_cast<uint32_t*>( myDec + DEC_LIM_OFFSET + ( g * LONG_LIMITS + i ) * 4U )
                             = static_cast<uint32_t>( limit >> 12 );
                     }
                     for ( uint32_t i = 0; i < LONG_OFFSETS; ++i ) {
-                        *reinterpret_cast<uint16_t*>( lutShared + SH_OFF_OFFSET + ( ( g * LONG_OFFSETS + i ) * BITS_SLOTS + slot ) * 2U )
+                        *reinterpret_cast<uint16_t*>( myDec + DEC_OFF_OFFSET + ( g * LONG_OFFSETS + i ) * 2U )
                             = bt->offset[g][LONG_FIRST_LEN + 1U + i];
                     }
-                    *reinterpret_cast<uint16_t*>( lutShared + SH_EOB_OFFSET + ( g * BITS_SLOTS + slot ) * 2U ) = bt->eobPerm[g];
+                    *reinterpret_cast<uint16_t*>( myDec + DEC_EOB_OFFSET + g * 2U ) = bt->eobPerm[g];
                 }
                 asm volatile( "" ::: "memory" );   /* the asm loads below read what was just stored */
             }
             const uint64_t startBit = bt->dataStartBit;
             d.wordIdx = startBit >> 5;
-            const uint32_t w0 = loadWordBE( data, nbytes, d.wordIdx );
-            const uint32_t w1 = loadWordBE( data, nbytes, d.wordIdx + 1U );
-            d.wordIdx += 2U;
-            d.nextW = loadWordBE( data, nbytes, d.wordIdx );
-            const uint32_t skipBits = static_cast<uint32_t>( startBit & 31U );
-            d.hi = __funnelshift_l( w1, w0, skipBits );
-            d.lo = w1 << skipBits;
-            d.nb = 64 - static_cast<int>( skipBits );
+            d.A = bswap( loadWordRaw( data, nbytes, d.wordIdx ) );
+            d.B = bswap( loadWordRaw( data, nbytes, d.wordIdx + 1U ) );
+            d.craw = loadWordRaw( data, nbytes, d.wordIdx + 2U );
+            d.pos = static_cast<uint32_t>( startBit & 31U );
             nsym = 0;
             selIdx = 0;
             haveBlock = true;
@@ -279,176 +293,163 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
         uint32_t outcome = 0;
 
         /* next group of 50 symbols: switch the table (bzip2.hpp:710-721) */
-        if ( ( selIdx >= selectorsCount ) || ( nsym >= SYM_LIMIT )
-             || ( d.wordIdx * 32U - static_cast<uint64_t>( d.nb ) > nbits ) ) {
+        if ( ( selIdx >= selectorsCount ) || ( nsym >= SYM_LIMIT ) || ( d.wordIdx * 32U + d.pos > nbits ) ) {
             outcome = 2;
         } else {
             if ( ( selIdx & 3U ) == 0 ) {
                 selWord = *reinterpret_cast<const uint32_t*>( selectors + selIdx );
             }
             const uint32_t table = ( selWord >> ( 8U * ( selIdx & 3U ) ) ) & 0xFFU;
-            const uint8_t* const tableLut = myLut + table * LUT_ROW_BYTES;
             ++selIdx;
-            uint32_t* const pairOut = reinterpret_cast<uint32_t*>( symOut + nsym );   /* nsym is a multiple of 50 */
 
             if ( d.wordIdx + GROUP_MAX_WORDS < fullWords ) {
-                /* ---- hot loop: two symbols per iteration, no file-end checks ----
-                 * A lane's instruction stream is what bounds a block (one warp instruction every ~5 cycles, nothing to
-                 * overlap it with inside the block), so the pair is ONE basic block with as few instructions as the
-                 * format allows: look up, shift the window by the entry's length, look up again.  An entry of 0 (code
-                 * longer than 9 bits, the end-of-block symbol, or no code) has length 0: the window stays where it
-                 * is and every later lookup misses too, so one test at the end of the pair finds it, with the window
-                 * still in front of the first symbol that needs the slow path.
-                 * Three raw words are kept behind the window and a word is loaded only when one is consumed, so that a load has
-                 * the time between two refills (about two pairs) to land before anything waits for its register. */
-                const uint32_t tableAddr = myLutAddr + table * LUT_ROW_BYTES;
-                const uint32_t limAddr = myLimAddr + table * ( LONG_LIMITS * BITS_SLOTS * 4U );
-                const uint32_t offAddr = myOffAddr + table * ( LONG_OFFSETS * BITS_SLOTS * 2U );
-                const uint32_t longTag = 0x8000U | ( table << 9 );
+                /* ---- hot loop: no file-end checks, three symbols per refill test ---- */
+                const uint32_t tableAddr = lutAddr + table * HUFF_LUT_SIZE;
                 const uint32_t* const wbase = dataWords + d.wordIdx;
-                uint32_t wofs = 0;                                   /* words consumed in this group */
-                prefetchL1( wbase + 64 );                            /* stays inside the file: see GROUP_MAX_WORDS */
-                uint32_t raw0 = __byte_perm( d.nextW, 0, 0x0123 );   /* back to memory order: swapped when used */
-                uint32_t raw1 = __ldg( wbase + 1 );
-                uint32_t raw2 = __ldg( wbase + 2 );
-                uint32_t hi = d.hi;
-                uint32_t lo = d.lo;
-                int nb = d.nb;
-                uint32_t g = 0;
-                uint32_t e = lookup( tableAddr, hi );   /* at least 15 valid bits here */
-#pragma unroll 5
-                for ( ; g < GROUP_SIZE / 2U; ++g ) {
-                    {
-                        /* refill as selects (no branch); lo is empty whenever rf holds */
-                        const bool rf = nb <= 32;
-                        const uint32_t x = rf ? __byte_perm( raw0, 0, 0x0123 ) : 0U;
-                        hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
-                        lo |= __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
-                        nb += rf ? 32 : 0;
-                        raw0 = rf ? raw1 : raw0;
-                        raw1 = rf ? raw2 : raw1;
-                        wofs += rf ? 1U : 0U;
-                        if ( rf ) {
-                            raw2 = __ldg( wbase + wofs + 2U );   /* a predicated load: nothing is fetched twice */
+                uint32_t* const outWords = reinterpret_cast<uint32_t*>( symOut + nsym );   /* nsym is a multiple of 50 */
+                const uint32_t packBias = lutAddr * 0x00010001U;
+                prefetchL1( wbase + 64 );   /* stays inside the file: see GROUP_MAX_WORDS */
+                uint32_t A = d.A;
+                uint32_t B = d.B;
+                uint32_t craw = d.craw;
+                uint32_t pos = d.pos;
+                uint32_t wofs = 0;          /* words consumed in this group */
+                uint32_t groupDone = 0;     /* symbols of the group in front of the end-of-block symbol */
+
+                /* branch-free: a select per register, a predicated load */
+#define IBZ2_REFILL()                                                     \
+    {                                                                     \
+        const bool rf = pos >= 32U;                                       \
+        if ( rf ) {                                                       \
+            A = B;                                                        \
+            B = bswap( craw );                                            \
+            ++wofs;                                                       \
+            craw = __ldg( wbase + wofs + 2U );                            \
+        }                                                                 \
+        pos &= 31U;                                                       \
+    }
+                /* COUNT symbols (at most three) from a refilled window; a0.. = shared-memory addresses of their entries.
+                 * ok = false when one of them was not a plain symbol of at most 9 bits: the position then stands in front of
+                 * it, and the lengths e0, e1 tell how many symbols were decoded before it. */
+#define IBZ2_FAST( COUNT, a0, a1, a2, e0, e1, ok )                                        \
+    {                                                                                     \
+        const uint32_t h0 = __funnelshift_l( B, A, pos );                                 \
+        a0 = tableAddr + ( h0 >> ( 32 - HUFF_LUT_BITS ) );                                \
+        e0 = ldsU8( a0 );                                                                 \
+        const uint32_t h1 = h0 << e0;                                                     \
+        a1 = tableAddr + ( h1 >> ( 32 - HUFF_LUT_BITS ) );                                \
+        e1 = ldsU8( a1 );                                                                 \
+        uint32_t e2 = e1;                                                                 \
+        if ( COUNT == 3 ) {                                                               \
+            const uint32_t h2 = h1 << e1;                                                 \
+            a2 = tableAddr + ( h2 >> ( 32 - HUFF_LUT_BITS ) );                            \
+            e2 = ldsU8( a2 );                                                             \
+            pos += e0 + e1 + e2;                                                          \
+        } else {                                                                          \
+            pos += e0 + e1;                                                               \
+        }                                                                                 \
+        ok = e2 != 0;                                                                     \
+    }
+                /* the rest of a triple whose fast path stopped in front of symbol `k` */
+#define IBZ2_SLOW( COUNT, a0, a1, a2, e0, e1, before )                                                    \
+    {                                                                                                     \
+        uint32_t kk = ( e0 != 0 ? 1U : 0U ) + ( ( ( COUNT == 3 ) && ( e1 != 0 ) ) ? 1U : 0U );             \
+        for ( ; kk < COUNT; ++kk ) {                                                       \
+            IBZ2_REFILL();                                                                                \
+            uint32_t entry = 0;                                                                           \
+            const uint32_t what = decodeOneSymbol( A, B, pos, lutAddr, table, bt, &entry );               \
+            if ( what == SYM_FAIL ) {                                                                     \
+                outcome = 2;                                                                              \
+                break;                                                                                    \
+            }                                                                                             \
+            if ( what == SYM_EOB ) {                                                                      \
+                outcome = 1;                                                                              \
+                groupDone = ( before ) + kk;                                                              \
+                break;                                                                                    \
+            }                                                                                             \
+            const uint32_t asAddr = entry + lutAddr;                                                      \
+            if ( kk == 0 ) {                                                                              \
+                a0 = asAddr;                                                                              \
+            } else if ( kk == 1 ) {                                                                       \
+                a1 = asAddr;                                                                              \
+            } else {                                                                                      \
+                a2 = asAddr;                                                                              \
+            }                                                                                             \
+        }                                                                                                 \
+    }
+
+                uint32_t it = 0;
+#pragma unroll 1
+                for ( ; it < GROUP_SIZE / 6U; ++it ) {
+                    uint32_t a0, a1, a2, a3, a4, a5;
+                    uint32_t e0, e1;
+                    bool ok;
+                    IBZ2_FAST( 3, a0, a1, a2, e0, e1, ok );
+                    if ( !ok ) {
+                        IBZ2_SLOW( 3, a0, a1, a2, e0, e1, 6U * it );
+                    }
+                    if ( outcome == 0 ) {
+                        IBZ2_REFILL();
+                        IBZ2_FAST( 3, a3, a4, a5, e0, e1, ok );
+                        if ( !ok ) {
+                            IBZ2_SLOW( 3, a3, a4, a5, e0, e1, 6U * it + 3U );
                         }
                     }
-                    /* at least 33 valid bits; a plain symbol takes at most 9 */
-                    const uint32_t e0 = e;
-                    hi = __funnelshift_l( lo, hi, e0 );   /* shifts by e0 & 31 = the length */
-                    lo <<= ( e0 & 31U );
-                    nb -= static_cast<int>( e0 & 31U );
-                    const uint32_t e1 = lookup( tableAddr, hi );
-                    hi = __funnelshift_l( lo, hi, e1 );
-                    lo <<= ( e1 & 31U );
-                    nb -= static_cast<int>( e1 & 31U );
-                    e = lookup( tableAddr, hi );          /* first symbol of the next pair: at least 15 valid bits */
-                    pairOut[g] = ( e0 >> 5 ) | ( ( e1 >> 5 ) << 16 );
-                    if ( e1 == 0 ) {
-                        /* ---- slow path: the window stands in front of symbol `k` of the pair ---- */
-                        uint32_t outFirst = e0 >> 5;
-                        uint32_t outSecond = 0;
-                        const uint32_t lim0 = ldsU32( limAddr );   /* codes of at most 9 bits are below it */
-                        for ( uint32_t k = ( e0 == 0 ) ? 0U : 1U; k < 2U; ++k ) {
-                            if ( nb <= 32 ) {
-                                const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                                hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
-                                lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
-                                nb += 32;
-                                raw0 = raw1;
-                                raw1 = raw2;
-                                ++wofs;
-                                raw2 = __ldg( wbase + wofs + 2U );
-                            }
-                            uint32_t ee = lookup( tableAddr, hi );
-                            uint32_t out = ee >> 5;
-                            bool isEob = false;
-                            if ( ee == 0 ) {
-                                if ( ( hi >> 12 ) < lim0 ) {
-                                    /* a code of at most 9 bits that is not in the shared-memory LUT: end of block */
-                                    ee = bt->lut[table][hi >> ( 32 - HUFF_LUT_BITS )];
-                                    isEob = true;
-                                } else {
-                                    const uint32_t r = decodeLongShared( limAddr, offAddr, hi );
-                                    if ( r == 0 ) {
-                                        outcome = 2;
-                                        break;
-                                    }
-                                    ee = r;
-                                    out = longTag | ( r >> 5 );
-                                    isEob = ( r >> 5 ) == ldsU16( myEobAddr + table * ( BITS_SLOTS * 2U ) );
-                                }
-                            }
-                            hi = __funnelshift_l( lo, hi, ee );
-                            lo <<= ( ee & 31U );
-                            nb -= static_cast<int>( ee & 31U );
-                            if ( isEob ) {
-                                /* end of block (bzip2.hpp:766-768) */
-                                outcome = 1;
-                                nsym += 2U * g + k;
-                                break;
-                            }
-                            if ( k == 0 ) {
-                                outFirst = out;
-                            } else {
-                                outSecond = out;
-                            }
-                        }
-                        pairOut[g] = outFirst | ( outSecond << 16 );
-                        if ( outcome != 0 ) {
-                            break;
-                        }
-                        if ( nb <= 32 ) {
-                            const uint32_t x = __byte_perm( raw0, 0, 0x0123 );
-                            hi |= __funnelshift_rc( x, 0U, static_cast<uint32_t>( nb ) );
-                            lo = __funnelshift_lc( 0U, x, static_cast<uint32_t>( 32 - nb ) );
-                            nb += 32;
-                            raw0 = raw1;
-                            raw1 = raw2;
-                            ++wofs;
-                            raw2 = __ldg( wbase + wofs + 2U );
-                        }
-                        e = lookup( tableAddr, hi );
-                    }
-                }
-                /* the window holds words [-2] and [-1] of wbase + wofs, raw0 = word [0]: hand the position back in file terms */
-                d.hi = hi;
-                d.lo = lo;
-                d.nb = nb;
-                d.wordIdx += wofs;
-                d.nextW = __byte_perm( raw0, 0, 0x0123 );
-                if ( outcome == 0 ) {
-                    nsym += GROUP_SIZE;
-                }
-            } else {
-                /* ---- the last groups before the end of the file: same loop with checked loads ---- */
-                uint32_t g = 0;
-                for ( ; g < GROUP_SIZE; ++g ) {
-                    refillChecked( d, data, nbytes );
-                    uint32_t e = *reinterpret_cast<const uint16_t*>( tableLut + ( d.hi >> ( 32 - HUFF_LUT_BITS ) ) * LUT_IDX_STRIDE );
-                    if ( e == 0 ) {
-                        e = bt->lut[table][d.hi >> ( 32 - HUFF_LUT_BITS )];   /* the end-of-block symbol, if short */
-                    }
-                    if ( e == 0 ) {
-                        e = decodeLong( bt, table, d.hi );
-                        if ( e == 0 ) {
-                            outcome = 2;
-                            break;
-                        }
-                    }
-                    consume( d, e & 31U );
-                    const uint32_t sym = e >> 5;
-                    if ( sym > symbolCount ) {
-                        outcome = 1;
+                    IBZ2_REFILL();
+                    /* entry = address - lutAddr < 2^15: both halves at once, modulo 2^32 */
+                    outWords[3U * it] = a0 + ( a1 << 16 ) - packBias;
+                    outWords[3U * it + 1U] = a2 + ( a3 << 16 ) - packBias;
+                    outWords[3U * it + 2U] = a4 + ( a5 << 16 ) - packBias;
+                    if ( outcome != 0 ) {
                         break;
                     }
-                    symOut[nsym + g] = static_cast<uint16_t>( sym );
+                }
+                if ( outcome == 0 ) {
+                    /* symbols 48 and 49 */
+                    uint32_t a0, a1, a2 = 0;
+                    uint32_t e0, e1;
+                    bool ok;
+                    IBZ2_FAST( 2, a0, a1, a2, e0, e1, ok );
+                    if ( !ok ) {
+                        IBZ2_SLOW( 2, a0, a1, a2, e0, e1, GROUP_SIZE - 2U );
+                    }
+                    IBZ2_REFILL();
+                    outWords[GROUP_SIZE / 2U - 1U] = a0 + ( a1 << 16 ) - packBias;
+                }
+#undef IBZ2_REFILL
+#undef IBZ2_FAST
+#undef IBZ2_SLOW
+                d.A = A;
+                d.B = B;
+                d.craw = craw;
+                d.pos = pos;
+                d.wordIdx += wofs;
+                nsym += outcome == 0 ? GROUP_SIZE : groupDone;
+            } else {
+                /* ---- the last groups before the end of the file: one symbol at a time with checked loads ---- */
+                uint32_t g = 0;
+                for ( ; g < GROUP_SIZE; ++g ) {
+                    uint32_t entry = 0;
+                    const uint32_t what = decodeOneSymbol( d.A, d.B, d.pos, lutAddr, table, bt, &entry );
+                    if ( d.pos >= 32U ) {
+                        d.A = d.B;
+                        d.B = bswap( d.craw );
+                        ++d.wordIdx;
+                        d.craw = loadWordRaw( data, nbytes, d.wordIdx + 2U );
+                        d.pos -= 32U;
+                    }
+                    if ( what != SYM_PLAIN ) {
+                        outcome = what == SYM_EOB ? 1U : 2U;
+                        break;
+                    }
+                    symOut[nsym + g] = static_cast<uint16_t>( entry );
                 }
                 nsym += g;
             }
         }
 
         if ( outcome != 0 ) {
-            const uint64_t endBit = d.wordIdx * 32U - static_cast<uint64_t>( d.nb );
+            const uint64_t endBit = d.wordIdx * 32U + d.pos;
             BlockMeta& bm = meta[block];
             if ( ( outcome == 1 ) && ( endBit <= nbits ) ) {
                 bm.nCoded = nsym;
@@ -461,14 +462,23 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
     }
 }
 
-/* Symbols that K2b left as ( 0x8000 | table << 9 | permIndex ) -> the symbol itself (HuffmanCodingSymbolsPerLength.hpp:
- * 105-124).  One pass over the symbol arrays with 16-byte accesses; about one symbol in a hundred is rewritten. */
+/* What K2b stored per symbol -> the symbol itself: ( table << 9 ) | index goes through K2a's 9-bit table, 0x8000 | table <<
+ * 9 | rank through perm (HuffmanCodingSymbolsPerLength.hpp:105-124).  One pass over the symbol arrays with 16-byte
+ * accesses; the 9 KB of tables of a block stay in L1. */
 constexpr int RESOLVE_THREADS = 256;
 constexpr uint32_t RESOLVE_PER_CTA = RESOLVE_THREADS * 8U * 8U;   /* symbols per CTA */
 
+__device__ __forceinline__ uint32_t
+resolveEntry( const BlockTables& bt, uint32_t v )
+{
+    const uint16_t* const flat = &bt.lut[0][0];
+    return ( v & 0x8000U ) != 0 ? static_cast<uint32_t>( __ldg( &bt.perm[( v >> 9 ) & 7U][v & 0x1FFU] ) )
+                                : static_cast<uint32_t>( __ldg( flat + ( v & 0x7FFFU ) ) ) >> 5;
+}
+
 __global__ void __launch_bounds__( RESOLVE_THREADS )
-resolveLongSymbolsKernel( const BlockMeta* __restrict__ meta, const BlockTables* __restrict__ tablesAll,
-                          uint32_t* __restrict__ scratchAll )
+resolveSymbolsKernel( const BlockMeta* __restrict__ meta, const BlockTables* __restrict__ tablesAll,
+                      uint32_t* __restrict__ scratchAll )
 {
     const uint32_t block = blockIdx.y;
     const BlockMeta& bm = meta[block];
@@ -484,27 +494,19 @@ resolveLongSymbolsKernel( const BlockMeta* __restrict__ meta, const BlockTables*
     uint4* const sym = reinterpret_cast<uint4*>( reinterpret_cast<uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE )
                                                  + K2_SYM16_OFFSET );
     const uint32_t quads = ( nCoded + 7U ) / 8U;   /* the slot is larger than any clean block: whole quads are ours */
-#pragma unroll
+#pragma unroll 2
     for ( uint32_t i = 0; i < 8U; ++i ) {
         const uint32_t q = ctaFirst / 8U + i * RESOLVE_THREADS + threadIdx.x;
         if ( q >= quads ) {
             break;
         }
-        uint4 v = sym[q];
-        if ( ( ( v.x | v.y | v.z | v.w ) & 0x80008000U ) == 0 ) {
-            continue;
-        }
+        const uint4 v = sym[q];
         uint32_t w[4] = { v.x, v.y, v.z, v.w };
+        const uint32_t remaining = nCoded - q * 8U;   /* entries behind the block's last symbol are not entries */
 #pragma unroll
         for ( uint32_t k = 0; k < 4U; ++k ) {
-            uint32_t a = w[k] & 0xFFFFU;
-            uint32_t b = w[k] >> 16;
-            if ( ( a & 0x8000U ) != 0 ) {
-                a = bt.perm[( a >> 9 ) & 7U][a & 0x1FFU];
-            }
-            if ( ( b & 0x8000U ) != 0 ) {
-                b = bt.perm[( b >> 9 ) & 7U][b & 0x1FFU];
-            }
+            const uint32_t a = ( 2U * k < remaining ) ? resolveEntry( bt, w[k] & 0xFFFFU ) : 0U;
+            const uint32_t b = ( 2U * k + 1U < remaining ) ? resolveEntry( bt, w[k] >> 16 ) : 0U;
             w[k] = a | ( b << 16 );
         }
         sym[q] = make_uint4( w[0], w[1], w[2], w[3] );
@@ -520,17 +522,18 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
     static const int lanes = [] () {
         const char* const env = std::getenv( "IBZ2_K2B_LANES" );
         const int v = env != nullptr ? std::atoi( env ) : BITS_LANES_DEFAULT;
-        return ( ( v == 1 ) || ( v == 2 ) || ( v == 4 ) || ( v == 8 ) ) ? v : BITS_LANES_DEFAULT;
+        return ( ( v == 1 ) || ( v == 2 ) || ( v == 4 ) || ( v == 8 ) || ( v == 16 ) ) ? v : BITS_LANES_DEFAULT;
     }();
     auto* const kernel = lanes == 1 ? huffmanBitsKernel<1> : lanes == 2 ? huffmanBitsKernel<2>
-                         : lanes == 4 ? huffmanBitsKernel<4> : huffmanBitsKernel<8>;
+                         : lanes == 4 ? huffmanBitsKernel<4> : lanes == 8 ? huffmanBitsKernel<8> : huffmanBitsKernel<16>;
     cudaFuncSetAttribute( kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>( shared ) );
+    cudaFuncSetAttribute( kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
     cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
-    const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() ), nblocks ) );
+    const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() * BITS_CTAS_PER_SM ), nblocks ) );
     const uint32_t slotsPerCta = std::min<uint32_t>( BITS_SLOTS, ( nblocks + ctas - 1U ) / ctas );
     kernel<<<ctas, ( BITS_SLOTS / lanes ) * 32, shared, stream>>>( data, nbytes, meta, nblocks, selectors, tables,
                                                                  scratch, counter, ordered ? counter + K2B_ORDER_OFFSET : nullptr, slotsPerCta );
     const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
-    resolveLongSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
+    resolveSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
 }
 }  // namespace ibz2
