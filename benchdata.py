@@ -342,6 +342,17 @@ def build_multistream(kind: str, seed: int, total_bytes: int, piece_bytes: int =
     return Workload(f"{kind}-multistream-l{level}", out, raw, 1, len(comp), None, meta)
 
 
+def build_multistream_repeated(kind: str, seed: int, base_bytes: int, copies: int, piece_bytes: int = 900_000,
+                               level: int = 9, log=None) -> Workload:
+    """config 5 at size: the streams of a unique base, the whole file repeated `copies` times (streams are byte
+    aligned and independent, so the copies are plain concatenation)"""
+    w = build_multistream(kind, seed, base_bytes, piece_bytes, level, log=log)
+    comp = np.tile(w.compressed, copies) if copies > 1 else w.compressed
+    meta = dict(w.meta, layout=w.meta["layout"] + f", unique base x {copies}", raw_bytes=int(w.raw_base.size) * copies,
+                compressed_bytes=int(comp.size), streams=w.blocks * copies)
+    return Workload(w.name, comp, w.raw_base, copies, w.blocks * copies, None, meta, sample=w.compressed)
+
+
 def _compress_piece(args):
     data, level = args
     return bz2.compress(data, level)

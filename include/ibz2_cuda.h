@@ -15,6 +15,8 @@
  *   ibz2_read_block_header indexed_bzip2/BZ2BlockFetcher.hpp:64-82 (readBlockHeader: EOS probe), host-side, no GPU
  *   ibz2_read_stream_header indexed_bzip2/bzip2.hpp:114-142 (readBzip2Header), host-side, no GPU
  *   ibz2_stream_crc_fold  indexed_bzip2/BZ2Reader.hpp:481-484 (fold of the per-block CRCs the GPU computed)
+ *   ibz2_fold_stream_crcs indexed_bzip2/BZ2Reader.hpp:406-416 (stream CRC check at the end-of-stream block), for a
+ *                         whole array of block results
  *
  * There is deliberately NO CPU decode behind this interface: if no CUDA device is usable, ibz2_create fails.
  */
@@ -28,7 +30,7 @@
 extern "C" {
 #endif
 
-#define IBZ2_ABI_VERSION 2
+#define IBZ2_ABI_VERSION 3
 
 #define IBZ2_MAGIC_BLOCK 0x314159265359ULL /* indexed_bzip2/bzip2.hpp:103 */
 #define IBZ2_MAGIC_EOS   0x177245385090ULL /* indexed_bzip2/bzip2.hpp:104 */
@@ -39,6 +41,11 @@ extern "C" {
 #define IBZ2_FIND_EOS   2U
 /* bit 63 of a reported offset marks an end-of-stream magic */
 #define IBZ2_OFFSET_EOS_FLAG ( 1ULL << 63 )
+
+/* ibz2_block_result.stream_flags */
+#define IBZ2_STREAM_FIRST_BLOCK 1U /* a stream header ("BZh1".."BZh9", bzip2.hpp:114-142) stands directly in front of the block */
+#define IBZ2_STREAM_LAST_BLOCK  2U /* an end-of-stream block follows the block directly; stream_crc_expected is its CRC field */
+#define IBZ2_STREAM_CRC_CHECKED 4U /* stream_crc_calculated holds the fold of the block CRCs of the whole stream */
 
 /* where a buffer passed through the ABI lives */
 #define IBZ2_MEM_HOST   0 /* pageable or pinned host memory; the call copies through the PCIe link */
@@ -92,6 +99,11 @@ typedef struct ibz2_block_result {
     uint32_t is_eof;          /* BlockHeaderData::isEndOfFile (EOS blocks only) */
     uint32_t n_symbols;       /* entries of the BWT vector (dbufCount, bzip2.hpp:793) */
     uint32_t orig_ptr;        /* bzip2.hpp:514 */
+    uint32_t stream_flags;    /* IBZ2_STREAM_*: where the streams of the file begin and end among the blocks of the call */
+    uint32_t stream_crc_expected;   /* last block of a stream: BlockHeader::headerCRC() of the EOS block behind it */
+    uint32_t stream_crc_calculated; /* last block of a stream whose first block is part of the same call and whose blocks
+                                     * were given in file order: the fold of BZ2Reader.hpp:481-484 over their CRCs */
+    uint32_t n_coded;         /* Huffman-coded symbols of the block without the end-of-block symbol (bzip2.hpp:709-723) */
     uint32_t reserved;
 } ibz2_block_result;
 
@@ -111,6 +123,7 @@ typedef struct ibz2_timings {
     uint64_t launches;     /* kernels launched by the call */
     float huffman_bits_ms; /* K2b alone (the bit-serial symbol loop inside huffman_ms) */
     float bwt_walk_ms;     /* the walk kernel alone (inside bwt_traverse_ms) */
+    float mtf_chunk_ms;    /* K2c alone (the chunk-parallel move-to-front inside huffman_ms) */
 } ibz2_timings;
 
 typedef struct ibz2_ctx ibz2_ctx;
@@ -124,6 +137,15 @@ const char* ibz2_last_error( const ibz2_ctx* ctx ); /* ctx may be NULL: error of
 int ibz2_get_timings( const ibz2_ctx* ctx, ibz2_timings* timings );
 /* Upper bound on the data blocks one ibz2_decode_blocks launch wave holds in flight (scratch is sized for it). */
 int ibz2_set_batch_blocks( ibz2_ctx* ctx, uint32_t blocks );
+/* Stream CRC (BZ2Reader.hpp:406-416, 481-484): ibz2_decode_blocks / ibz2_decode_buffer fold the block CRCs of every stream
+ * that lies completely inside the call and, when verify != 0 (the default), give the LAST block of a stream whose fold
+ * differs from the CRC field of its end-of-stream block the status IBZ2_ST_STREAM_CRC (its bytes are still delivered).
+ * With verify == 0 only stream_flags / stream_crc_expected / stream_crc_calculated are filled in. */
+int ibz2_set_verify_stream_crc( ibz2_ctx* ctx, int verify );
+/* The same fold over results of several calls laid end to end (blocks of one file in file order, e.g. the shares of
+ * several GPUs): fills stream_crc_calculated / IBZ2_STREAM_CRC_CHECKED and, when verify != 0, sets IBZ2_ST_STREAM_CRC.
+ * Returns the number of streams whose CRC did not match.  Host-side, no GPU work. */
+uint64_t ibz2_fold_stream_crcs( ibz2_block_result* results, uint64_t nblocks, int verify );
 
 /* ---- device memory helpers (so that FFI callers can keep inputs/outputs resident in HBM) ---- */
 int ibz2_device_alloc( ibz2_ctx* ctx, uint64_t nbytes, void** dptr );

@@ -73,6 +73,8 @@ def _load():
         "ibz2r_block_offsets": (ll, [vp, C.POINTER(C.c_uint64), sz, i32]),
         "ibz2r_set_block_offsets": (i32, [vp, C.POINTER(C.c_uint64), sz]),
         "ibz2r_join_threads": (i32, [vp]),
+        "ibz2r_set_verify_stream_crc": (i32, [vp, i32]),
+        "ibz2r_set_open_device": (None, [i32]),
         "ibz2r_cli": (i32, [i32, C.POINTER(C.c_char_p)]),
     }
     for name, (restype, argtypes) in sigs.items():
@@ -100,12 +102,13 @@ def _hasValidFileno(file):
 class _Reader:
     """What _IndexedBzip2File / _IndexedBzip2FileParallel are in the reference: a thin object around the C++ reader."""
 
-    def __init__(self, file, parallelization):
+    def __init__(self, file, parallelization, device=None, verify_stream_crc=True):
         if not isinstance(parallelization, int):
             raise TypeError(f"Parallelization argument must be an integer not '{parallelization}'!")
         lib = _load()
         self._lib = lib
         self._handle = None
+        lib.ibz2r_set_open_device(-1 if device is None else int(device))   # None: $IBZ2_DEVICE, else device 0
         if isinstance(file, int) and not isinstance(file, bool):
             handle = lib.ibz2r_open_fd(file, parallelization)
         elif _hasValidFileno(file):
@@ -119,6 +122,8 @@ class _Reader:
             file.seek(0)
             data = file.read()
             file.seek(position)
+            if not isinstance(data, bytes):
+                data = bytes(data)   # bytearray / memoryview from a custom file object
             handle = lib.ibz2r_open_memory(C.cast(C.c_char_p(data), C.c_void_p), len(data), parallelization)
         elif isinstance(file, str):
             handle = lib.ibz2r_open_path(os.fsencode(file), parallelization)
@@ -128,6 +133,8 @@ class _Reader:
             self._raise(None)
         self._handle = handle
         self._parallel = parallelization != 1
+        if not verify_stream_crc:
+            lib.ibz2r_set_verify_stream_crc(handle, 0)
 
     def _raise(self, handle):
         kind = self._lib.ibz2r_last_error_kind(handle)
@@ -183,7 +190,11 @@ class _Reader:
 
     def size(self):
         # std::optional::value_or( 0 ) like the reference: 0 until the block map is complete
-        return max(0, self._lib.ibz2r_size(self._require(), 0))
+        handle = self._require()
+        value = self._lib.ibz2r_size(handle, 0)
+        if value < 0 and self._lib.ibz2r_last_error_kind(handle) != 0:
+            self._raise(handle)   # -1 is also what a caught exception returns
+        return max(0, value)
 
     def tell_compressed(self):
         return self._checked(self._lib.ibz2r_tell_compressed(self._require()))
@@ -217,8 +228,8 @@ class _Reader:
 
 
 class IndexedBzip2FileRaw(io.RawIOBase):
-    def __init__(self, filename, parallelization=1):
-        self.bz2reader = _Reader(filename, parallelization)
+    def __init__(self, filename, parallelization=1, **options):
+        self.bz2reader = _Reader(filename, parallelization, **options)
         self.name = filename
         self.mode = "rb"
         self.readinto = self.bz2reader.readinto
@@ -240,8 +251,8 @@ class IndexedBzip2FileRaw(io.RawIOBase):
 
 
 class IndexedBzip2File(io.BufferedReader):
-    def __init__(self, filename, parallelization=1):
-        fobj = IndexedBzip2FileRaw(filename, parallelization)
+    def __init__(self, filename, parallelization=1, **options):
+        fobj = IndexedBzip2FileRaw(filename, parallelization, **options)
         self.bz2reader = fobj.bz2reader
         self.tell_compressed = self.bz2reader.tell_compressed
         self.block_offsets = self.bz2reader.block_offsets
@@ -275,12 +286,15 @@ class IndexedBzip2File(io.BufferedReader):
         self.set_block_offsets(offsets)
 
 
-def open(filename, parallelization=1):
+def open(filename, parallelization=1, *, device=None, verify_stream_crc=True):
     """
     filename: can be a file path, a file descriptor, or a file object
               with suitable read, seekable, seek, and tell methods.
+    device: CUDA device index (default: $IBZ2_DEVICE, else 0).  New next to the reference.
+    verify_stream_crc: the parallel reader checks the CRC of every bzip2 stream while it builds the block map, which
+              the reference only does in its serial reader; False restores the reference's behaviour.
     """
-    return IndexedBzip2File(filename, parallelization)
+    return IndexedBzip2File(filename, parallelization, device=device, verify_stream_crc=verify_stream_crc)
 
 
 def cli(args=None):

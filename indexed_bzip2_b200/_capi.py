@@ -35,14 +35,17 @@ class BlockResult(C.Structure):
         ("enc_offset_bits", C.c_uint64), ("enc_size_bits", C.c_uint64), ("out_offset", C.c_uint64),
         ("out_size", C.c_uint64), ("expected_crc", C.c_uint32), ("calculated_crc", C.c_uint32),
         ("status", C.c_uint32), ("is_eos", C.c_uint32), ("is_eof", C.c_uint32), ("n_symbols", C.c_uint32),
-        ("orig_ptr", C.c_uint32), ("reserved", C.c_uint32),
+        ("orig_ptr", C.c_uint32), ("stream_flags", C.c_uint32),
+        ("stream_crc_expected", C.c_uint32), ("stream_crc_calculated", C.c_uint32),
+        ("n_coded", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
 BLOCK_RESULT_DTYPE = np.dtype([
     ("enc_offset_bits", "<u8"), ("enc_size_bits", "<u8"), ("out_offset", "<u8"), ("out_size", "<u8"),
     ("expected_crc", "<u4"), ("calculated_crc", "<u4"), ("status", "<u4"), ("is_eos", "<u4"), ("is_eof", "<u4"),
-    ("n_symbols", "<u4"), ("orig_ptr", "<u4"), ("reserved", "<u4"),
+    ("n_symbols", "<u4"), ("orig_ptr", "<u4"), ("stream_flags", "<u4"),
+    ("stream_crc_expected", "<u4"), ("stream_crc_calculated", "<u4"), ("n_coded", "<u4"), ("reserved", "<u4"),
 ])
 assert BLOCK_RESULT_DTYPE.itemsize == C.sizeof(BlockResult)
 
@@ -51,7 +54,7 @@ class Timings(C.Structure):
     _fields_ = [(n, C.c_float) for n in (
         "h2d_ms", "find_ms", "huffman_ms", "bwt_prepare_ms", "bwt_traverse_ms", "rle_scan_ms", "rle_write_ms",
         "crc_ms", "d2h_ms", "total_ms")] + [("launches", C.c_uint64), ("huffman_bits_ms", C.c_float),
-                                             ("bwt_walk_ms", C.c_float)]
+                                             ("bwt_walk_ms", C.c_float), ("mtf_chunk_ms", C.c_float)]
 
     def as_dict(self) -> dict:
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -68,7 +71,7 @@ EXPORTS = [
     "ibz2_set_batch_blocks", "ibz2_device_alloc", "ibz2_device_free", "ibz2_host_alloc_pinned",
     "ibz2_host_free_pinned", "ibz2_memcpy_h2d", "ibz2_memcpy_d2h", "ibz2_synchronize", "ibz2_find_magics",
     "ibz2_decode_blocks", "ibz2_decode_buffer", "ibz2_timer_start", "ibz2_timer_stop", "ibz2_debug_decode_block", "ibz2_read_stream_header", "ibz2_read_block_header",
-    "ibz2_stream_crc_fold",
+    "ibz2_stream_crc_fold", "ibz2_set_verify_stream_crc", "ibz2_fold_stream_crcs",
 ]
 
 _lib = None
@@ -129,7 +132,11 @@ def load_library() -> C.CDLL:
     L.ibz2_read_block_header.argtypes = [vp, u64, u64, C.POINTER(BlockResult)]
     L.ibz2_stream_crc_fold.restype = u32
     L.ibz2_stream_crc_fold.argtypes = [u32, u32]
-    if L.ibz2_abi_version() != 2:
+    L.ibz2_set_verify_stream_crc.restype = i32
+    L.ibz2_set_verify_stream_crc.argtypes = [vp, i32]
+    L.ibz2_fold_stream_crcs.restype = u64
+    L.ibz2_fold_stream_crcs.argtypes = [vp, u64, i32]
+    if L.ibz2_abi_version() != 3:
         raise ImportError("libibz2_cuda.so has an unexpected ABI version")
     _lib = L
     return L
@@ -228,6 +235,9 @@ class Context:
 
     def set_batch_blocks(self, blocks: int):
         self._check(self.lib.ibz2_set_batch_blocks(self.handle, blocks))
+
+    def set_verify_stream_crc(self, verify: bool):
+        self._check(self.lib.ibz2_set_verify_stream_crc(self.handle, 1 if verify else 0))
 
     def timings(self) -> dict:
         t = Timings()
@@ -346,3 +356,10 @@ def read_block_header(data, bit_offset: int) -> BlockResult:
 
 def stream_crc_fold(stream_crc: int, block_crc: int) -> int:
     return int(load_library().ibz2_stream_crc_fold(stream_crc, block_crc))
+
+
+def fold_stream_crcs(results: np.ndarray, verify: bool = True) -> int:
+    """BZ2Reader.hpp:406-416 / :481-484 over an array of block results in file order (in place); returns the number of
+    streams whose CRC did not match."""
+    assert results.dtype == BLOCK_RESULT_DTYPE and results.flags.c_contiguous
+    return int(load_library().ibz2_fold_stream_crcs(results.ctypes.data, len(results), 1 if verify else 0))

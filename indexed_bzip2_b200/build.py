@@ -58,7 +58,8 @@ def build_native(force: bool = False, verbose: bool = False) -> Path:
 
     def compile_one(job):
         src, obj = job
-        cmd = [cc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+        # IBZ2_NVCC_EXTRA: extra flags for experiments (-D switches of the kernels), e.g. on the GPU box
+        cmd = [cc, *NVCC_FLAGS, *os.environ.get("IBZ2_NVCC_EXTRA", "").split(), "-c", str(src), "-o", str(obj)]
         res = subprocess.run(cmd, capture_output=True, text=True)
         (BUILD / (src.stem + ".ptxas.log")).write_text(res.stderr)
         if res.returncode != 0:

@@ -33,6 +33,7 @@ struct ibz2_ctx
     uint64_t* hRunning = nullptr;        /* pinned: output bytes produced up to the end of the last finished wave */
     std::string lastError;
     uint32_t batchBlocks = 0;
+    bool verifyStreamCrc = true;
 
     /* per-wave scratch */
     uint32_t scratchBlocks = 0;
@@ -224,6 +225,11 @@ fillResult( const ibz2::BlockMeta& m, ibz2_block_result* r )
     r->out_offset = m.outOffset;
     r->out_size = ( ( m.status == IBZ2_ST_OK ) || ( m.status == IBZ2_ST_OUTPUT_CAPACITY ) || ( m.status == IBZ2_ST_CRC ) )
                   ? m.outSize : 0;
+    r->stream_flags = m.streamFlags & ( IBZ2_STREAM_FIRST_BLOCK | IBZ2_STREAM_LAST_BLOCK );
+    r->stream_crc_expected = m.eosCrc;
+    r->stream_crc_calculated = 0;
+    r->n_coded = m.nCoded;
+    r->reserved = 0;
     r->expected_crc = m.headerCrc;
     r->calculated_crc = m.calcCrc;
     r->status = m.status;
@@ -231,7 +237,6 @@ fillResult( const ibz2::BlockMeta& m, ibz2_block_result* r )
     r->is_eof = m.isEof;
     r->n_symbols = m.n;
     r->orig_ptr = m.origPtr;
-    r->reserved = 0;
 }
 
 /* MSB-first bit extraction on the host, for the two header probes only. */
@@ -410,6 +415,60 @@ ibz2_set_batch_blocks( ibz2_ctx* ctx, uint32_t blocks )
     }
     ctx->batchBlocks = blocks;
     return IBZ2_OK;
+}
+
+int
+ibz2_set_verify_stream_crc( ibz2_ctx* ctx, int verify )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    ctx->verifyStreamCrc = verify != 0;
+    return IBZ2_OK;
+}
+
+uint64_t
+ibz2_fold_stream_crcs( ibz2_block_result* results, uint64_t nblocks, int verify )
+{
+    /* BZ2Reader.hpp:481-484 per data block, :406-416 at the end-of-stream block.  A fold is only trusted from a block that
+     * directly follows a stream header on, over blocks that follow one another without a gap and decoded cleanly. */
+    uint64_t mismatches = 0;
+    bool tracking = false;
+    uint32_t crc = 0;
+    uint64_t expectedNext = 0;
+    for ( uint64_t i = 0; i < nblocks; ++i ) {
+        ibz2_block_result& r = results[i];
+        r.stream_flags &= ~IBZ2_STREAM_CRC_CHECKED;
+        if ( r.is_eos != 0 ) {
+            tracking = false;
+            continue;
+        }
+        if ( ( r.stream_flags & IBZ2_STREAM_FIRST_BLOCK ) != 0 ) {
+            tracking = true;
+            crc = 0;
+        } else if ( tracking && ( r.enc_offset_bits != expectedNext ) ) {
+            tracking = false;
+        }
+        const bool clean = ( ( r.status == IBZ2_ST_OK ) || ( r.status == IBZ2_ST_OUTPUT_CAPACITY ) || ( r.status == IBZ2_ST_STREAM_CRC ) )
+                           && ( r.calculated_crc == r.expected_crc );
+        tracking = tracking && clean;
+        if ( tracking ) {
+            crc = ibz2_stream_crc_fold( crc, r.calculated_crc );
+            expectedNext = r.enc_offset_bits + r.enc_size_bits;
+            if ( ( r.stream_flags & IBZ2_STREAM_LAST_BLOCK ) != 0 ) {
+                r.stream_flags |= IBZ2_STREAM_CRC_CHECKED;
+                r.stream_crc_calculated = crc;
+                if ( crc != r.stream_crc_expected ) {
+                    ++mismatches;
+                    if ( ( verify != 0 ) && ( r.status == IBZ2_ST_OK ) ) {
+                        r.status = IBZ2_ST_STREAM_CRC;
+                    }
+                }
+                tracking = false;
+            }
+        }
+    }
+    return mismatches;
 }
 
 int
@@ -602,7 +661,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         IBZ2_CUDA_CHECK( ctx, cudaMemsetAsync( ctx->dRunning, 0, 2 * sizeof( uint64_t ), s ) );
     }
 
-    struct WaveEvents { cudaEvent_t e[7]; cudaEvent_t bits[2]; cudaEvent_t walk; };
+    struct WaveEvents { cudaEvent_t e[7]; cudaEvent_t bits[3]; cudaEvent_t walk; };
     std::vector<WaveEvents> waveEvents;   /* K2 per wave: e[0], e[1], bits */
     std::vector<WaveEvents> subEvents;    /* K4..K6 per sub-wave: e[1]..e[6], walk */
 
@@ -660,8 +719,9 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
         we.e[0] = nextEvent( ctx );
         we.bits[0] = spareEvent( ctx );
         we.bits[1] = spareEvent( ctx );
+        we.bits[2] = spareEvent( ctx );
         ibz2::launchHuffmanDecode( dData, nbytes, ctx->dMeta, count, ctx->dLbytes, ctx->dSelectors, ctx->dTables,
-                                   ctx->dDbuf, ctx->dCounter, true, s, we.bits[0], we.bits[1] );
+                                   ctx->dDbuf, ctx->dCounter, true, s, we.bits[0], we.bits[1], we.bits[2] );
         we.e[1] = nextEvent( ctx );
         waveEvents.push_back( we );
         ctx->timings.launches += ibz2::HUFFMAN_LAUNCHES;
@@ -756,6 +816,7 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
     for ( const auto& we : waveEvents ) {
         ctx->timings.huffman_ms += elapsed( we.e[0], we.e[1] );
         ctx->timings.huffman_bits_ms += elapsed( we.bits[0], we.bits[1] );
+        ctx->timings.mtf_chunk_ms += elapsed( we.bits[1], we.bits[2] );
     }
     for ( const auto& se : subEvents ) {
         ctx->timings.bwt_prepare_ms += elapsed( se.e[1], se.e[2] );
@@ -893,6 +954,7 @@ ibz2_decode_blocks( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
     if ( rc != IBZ2_OK ) {
         return rc;
     }
+    ibz2_fold_stream_crcs( results, nblocks, ctx->verifyStreamCrc ? 1 : 0 );
     if ( total_out != nullptr ) {
         *total_out = total;
     }
@@ -1051,6 +1113,7 @@ decodeBufferSplit( ibz2_ctx* ctx, const uint8_t* data, uint64_t nbytes, uint64_t
                       elapsed( e0, e1 ), elapsed( ctx->inFirstHalf, ctx->inSecondHalf ), elapsed( e0, ctx->inSecondHalf ),
                       elapsed( e0, eAfterA ), elapsed( e0, eBeforeB ), elapsed( e0, eAfterB ), mineA.size(), mineB.size() );
     }
+    ibz2_fold_stream_crcs( results, *nblocks, ctx->verifyStreamCrc ? 1 : 0 );
     *done = true;
     return IBZ2_OK;
 }
@@ -1128,6 +1191,7 @@ ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_m
         if ( rc != IBZ2_OK ) {
             return rc;
         }
+        ibz2_fold_stream_crcs( results, mine.size(), ctx->verifyStreamCrc ? 1 : 0 );
     }
     if ( total_out != nullptr ) {
         *total_out = total;

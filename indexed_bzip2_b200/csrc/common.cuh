@@ -55,7 +55,11 @@ struct BlockMeta
     uint32_t nCoded;      /* K2b: Huffman symbols stored for K2c..K2e (run symbols and MTF symbols, without EOB) */
     int32_t travStar;     /* K4b walk: the segment that passes through origPtr (-1: none), set to -1 by K2a */
     uint32_t travK;       /* K4b walk: number of steps from that segment's start to origPtr */
+    uint32_t streamFlags; /* stream probe: STREAM_FIRST_BLOCK | STREAM_LAST_BLOCK */
+    uint32_t eosCrc;      /* stream probe: CRC field of the end-of-stream block that follows the block directly */
 };
+constexpr uint32_t STREAM_FIRST_BLOCK = IBZ2_STREAM_FIRST_BLOCK;   /* a stream header stands directly in front of the block */
+constexpr uint32_t STREAM_LAST_BLOCK = IBZ2_STREAM_LAST_BLOCK;     /* an end-of-stream block follows the block directly */
 
 /* ---- K2 intermediates (see huffman_header.cu / huffman_bits.cu / mtf.cu) ----
  * K2a writes one BlockTables per block; K2b reads it (the LUTs go to shared memory, the rest stays in L1/L2). */
@@ -154,8 +158,9 @@ constexpr uint32_t K2B_ORDER_OFFSET = 16;
 void launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* lbytes, uint8_t* selectors, BlockTables* tables, uint32_t* scratch,
                           uint32_t* counter, bool ordered, cudaStream_t stream,
-                          cudaEvent_t bitsStart = nullptr, cudaEvent_t bitsStop = nullptr );   /* recorded around K2b */
-constexpr uint32_t HUFFMAN_LAUNCHES = 7;
+                          cudaEvent_t bitsStart = nullptr, cudaEvent_t bitsStop = nullptr,   /* recorded around K2b + resolve */
+                          cudaEvent_t chunkStop = nullptr );                                  /* ... and behind K2c */
+constexpr uint32_t HUFFMAN_LAUNCHES = 8;   /* K2a, K2b, resolve, K2c, K2d, K2e, K2x, stream probe */
 
 void launchHuffmanHeader( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks,
                           uint8_t* selectors, BlockTables* tables, cudaStream_t stream );
@@ -165,7 +170,7 @@ void launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, u
 void launchHuffmanCareful( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* lbytes,
                            uint8_t* selectors, cudaStream_t stream );
 void launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_t* scratch, uint8_t* lbytes,
-                cudaStream_t stream );
+                cudaStream_t stream, cudaEvent_t chunkStop = nullptr );
 
 void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, uint32_t nblocks,
                        cudaStream_t stream );
@@ -208,6 +213,10 @@ void launchCrc( const uint8_t* out, BlockMeta* meta, uint32_t nblocks, const uin
                 uint32_t pieceBytes, cudaStream_t stream );
 
 void launchCrcFinalize( const uint8_t* out, BlockMeta* meta, uint32_t nblocks, cudaStream_t stream );
+
+/* Where the streams of the file begin and end among the decoded blocks (BZ2Reader.hpp:406-416 needs the CRC field of the
+ * end-of-stream block behind a stream's last block); runs once K2 has set every block's endBit. */
+void launchStreamProbe( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, cudaStream_t stream );
 
 constexpr uint32_t CRC_PIECE_BYTES = 131072;
 

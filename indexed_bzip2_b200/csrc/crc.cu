@@ -210,7 +210,56 @@ hostPowX( uint64_t exponentBits )
     }
     return r;
 }
+/* ---- stream boundaries: one thread per block ---- */
+__device__ __forceinline__ uint64_t
+readBitsAt( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t bit, uint32_t count )   /* count <= 48 */
+{
+    const uint64_t word = bit >> 5;
+    const uint32_t skip = static_cast<uint32_t>( bit & 31U );
+    const uint64_t w0 = loadWordBE( data, nbytes, word );
+    const uint64_t w1 = loadWordBE( data, nbytes, word + 1U );
+    const uint64_t w2 = loadWordBE( data, nbytes, word + 2U );
+    const uint64_t hi = ( w0 << 32 ) | w1;                                   /* bits word * 32 .. + 63 */
+    const uint64_t window = skip == 0 ? hi : ( ( hi << skip ) | ( w2 >> ( 32U - skip ) ) );
+    return window >> ( 64U - count );
+}
+
+__global__ void
+streamProbeKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks )
+{
+    const uint32_t block = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( block >= nblocks ) {
+        return;
+    }
+    BlockMeta& bm = meta[block];
+    uint32_t flags = 0;
+    uint32_t eosCrc = 0;
+    if ( ( bm.status == IBZ2_ST_OK ) && ( bm.isEos == 0 ) ) {
+        const uint64_t nbits = nbytes * 8U;
+        /* "BZh1" .. "BZh9" (bzip2.hpp:114-142) in the 32 bits in front of the block magic */
+        if ( bm.bitOffset >= 32U ) {
+            const uint32_t header = static_cast<uint32_t>( readBitsAt( data, nbytes, bm.bitOffset - 32U, 32 ) );
+            if ( ( ( header >> 8 ) == 0x425A68U ) && ( ( header & 0xFFU ) >= '1' ) && ( ( header & 0xFFU ) <= '9' ) ) {
+                flags |= STREAM_FIRST_BLOCK;
+            }
+        }
+        if ( ( bm.endBit > bm.bitOffset ) && ( bm.endBit + 80U <= nbits ) && ( readBitsAt( data, nbytes, bm.endBit, 48 ) == MAGIC_EOS ) ) {
+            flags |= STREAM_LAST_BLOCK;
+            eosCrc = static_cast<uint32_t>( readBitsAt( data, nbytes, bm.endBit + 48U, 32 ) );
+        }
+    }
+    bm.streamFlags = flags;
+    bm.eosCrc = eosCrc;
+}
 }  // namespace
+
+void
+launchStreamProbe( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, cudaStream_t stream )
+{
+    if ( nblocks > 0 ) {
+        streamProbeKernel<<<( nblocks + 127U ) / 128U, 128, 0, stream>>>( data, nbytes, meta, nblocks );
+    }
+}
 
 void
 initCrcConstants()

@@ -38,6 +38,10 @@ namespace
 constexpr int BITS_SLOTS = 32;          /* decoders per CTA */
 constexpr int BITS_CTAS_PER_SM = 2;
 constexpr int BITS_LANES_DEFAULT = 4;   /* active lanes per warp; BITS_SLOTS / lanes warps per CTA */
+/* experiment switches (the defaults are what the measurements in DESIGN.md chose) */
+#ifndef IBZ2_K2B_PREFETCH_WORDS
+#define IBZ2_K2B_PREFETCH_WORDS 40
+#endif
 constexpr uint32_t SYM_LIMIT = DBUF_SIZE;                         /* a clean block has at most this many symbols */
 constexpr uint32_t GROUP_MAX_WORDS = ( GROUP_SIZE * MAX_CODE_LEN + 31U ) / 32U + 4U + 96U;   /* + prefetch distance */
 
@@ -57,10 +61,19 @@ constexpr uint32_t SH_TOTAL_BYTES = BITS_SLOTS * DEC_STRIDE;
 static_assert( BITS_CTAS_PER_SM * ( SH_TOTAL_BYTES + 1024U ) <= 228U * 1024U, "two CTAs per SM" );
 static_assert( DEC_LUT_BYTES <= 0x8000U, "stored entries keep bit 15 for long codes" );
 
+#ifndef IBZ2_K2B_PREFETCH_KIND
+#define IBZ2_K2B_PREFETCH_KIND 1   /* 0 = none, 1 = into L1, 2 = into L2 */
+#endif
 __device__ __forceinline__ void
-prefetchL1( const void* p )
+prefetchStream( const void* p )
 {
+#if IBZ2_K2B_PREFETCH_KIND == 1
     asm volatile( "prefetch.global.L1 [%0];" ::"l"( p ) );
+#elif IBZ2_K2B_PREFETCH_KIND == 2
+    asm volatile( "prefetch.global.L2 [%0];" ::"l"( p ) );
+#else
+    (void) p;
+#endif
 }
 
 __device__ __forceinline__ uint32_t
@@ -303,35 +316,40 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             ++selIdx;
 
             if ( d.wordIdx + GROUP_MAX_WORDS < fullWords ) {
-                /* ---- hot loop: no file-end checks, three symbols per refill test ---- */
+                /* ---- hot loop: no file-end checks, three symbols per refill test ----
+                 * Six symbols per iteration; when all six were plain symbols of at most 9 bits their entries leave as three
+                 * 32-bit stores back to back (stores to one line that follow one another directly merge in L1; the same
+                 * stores spread over the iteration cost 16 ms more on the 8 GB workload).  Otherwise the careful path
+                 * stores what the fast path had decoded and goes on one symbol at a time; nothing it computes flows back
+                 * into the registers of the fast path except the bit position. */
                 const uint32_t tableAddr = lutAddr + table * HUFF_LUT_SIZE;
                 const uint32_t* const wbase = dataWords + d.wordIdx;
-                uint32_t* const outWords = reinterpret_cast<uint32_t*>( symOut + nsym );   /* nsym is a multiple of 50 */
+                uint16_t* const groupOut = symOut + nsym;   /* nsym is a multiple of 50: 4-byte aligned */
                 const uint32_t packBias = lutAddr * 0x00010001U;
-                prefetchL1( wbase + 64 );   /* stays inside the file: see GROUP_MAX_WORDS */
+                prefetchStream( wbase + IBZ2_K2B_PREFETCH_WORDS );   /* stays inside the file: see GROUP_MAX_WORDS */
                 uint32_t A = d.A;
                 uint32_t B = d.B;
                 uint32_t craw = d.craw;
                 uint32_t pos = d.pos;
                 uint32_t wofs = 0;          /* words consumed in this group */
-                uint32_t groupDone = 0;     /* symbols of the group in front of the end-of-block symbol */
+                uint32_t groupDone = GROUP_SIZE;   /* symbols of the group in front of the end-of-block symbol */
 
                 /* branch-free: a select per register, a predicated load */
 #define IBZ2_REFILL()                                                     \
     {                                                                     \
         const bool rf = pos >= 32U;                                       \
+        A = rf ? B : A;                                                   \
+        B = rf ? bswap( craw ) : B;                                       \
+        wofs += rf ? 1U : 0U;                                             \
         if ( rf ) {                                                       \
-            A = B;                                                        \
-            B = bswap( craw );                                            \
-            ++wofs;                                                       \
             craw = __ldg( wbase + wofs + 2U );                            \
         }                                                                 \
         pos &= 31U;                                                       \
     }
-                /* COUNT symbols (at most three) from a refilled window; a0.. = shared-memory addresses of their entries.
-                 * ok = false when one of them was not a plain symbol of at most 9 bits: the position then stands in front of
-                 * it, and the lengths e0, e1 tell how many symbols were decoded before it. */
-#define IBZ2_FAST( COUNT, a0, a1, a2, e0, e1, ok )                                        \
+                /* COUNT symbols (2 or 3) from a refilled window; a0.. = shared-memory addresses of their entries.  A symbol
+                 * that is not a plain one of at most 9 bits has length 0: the position stays in front of it and the rest
+                 * of the triple reads the same entry again, so `last` == 0 tells, and e0, e1 say how many were decoded. */
+#define IBZ2_FAST( COUNT, a0, a1, a2, e0, e1, last )                                      \
     {                                                                                     \
         const uint32_t h0 = __funnelshift_l( B, A, pos );                                 \
         a0 = tableAddr + ( h0 >> ( 32 - HUFF_LUT_BITS ) );                                \
@@ -339,67 +357,66 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
         const uint32_t h1 = h0 << e0;                                                     \
         a1 = tableAddr + ( h1 >> ( 32 - HUFF_LUT_BITS ) );                                \
         e1 = ldsU8( a1 );                                                                 \
-        uint32_t e2 = e1;                                                                 \
+        last = e1;                                                                        \
+        pos += e0 + e1;                                                                   \
         if ( COUNT == 3 ) {                                                               \
             const uint32_t h2 = h1 << e1;                                                 \
             a2 = tableAddr + ( h2 >> ( 32 - HUFF_LUT_BITS ) );                            \
-            e2 = ldsU8( a2 );                                                             \
-            pos += e0 + e1 + e2;                                                          \
-        } else {                                                                          \
-            pos += e0 + e1;                                                               \
+            last = ldsU8( a2 );                                                           \
+            pos += last;                                                                  \
         }                                                                                 \
-        ok = e2 != 0;                                                                     \
     }
-                /* the rest of a triple whose fast path stopped in front of symbol `k` */
-#define IBZ2_SLOW( COUNT, a0, a1, a2, e0, e1, before )                                                    \
-    {                                                                                                     \
-        uint32_t kk = ( e0 != 0 ? 1U : 0U ) + ( ( ( COUNT == 3 ) && ( e1 != 0 ) ) ? 1U : 0U );             \
-        for ( ; kk < COUNT; ++kk ) {                                                       \
-            IBZ2_REFILL();                                                                                \
-            uint32_t entry = 0;                                                                           \
-            const uint32_t what = decodeOneSymbol( A, B, pos, lutAddr, table, bt, &entry );               \
-            if ( what == SYM_FAIL ) {                                                                     \
-                outcome = 2;                                                                              \
-                break;                                                                                    \
-            }                                                                                             \
-            if ( what == SYM_EOB ) {                                                                      \
-                outcome = 1;                                                                              \
-                groupDone = ( before ) + kk;                                                              \
-                break;                                                                                    \
-            }                                                                                             \
-            const uint32_t asAddr = entry + lutAddr;                                                      \
-            if ( kk == 0 ) {                                                                              \
-                a0 = asAddr;                                                                              \
-            } else if ( kk == 1 ) {                                                                       \
-                a1 = asAddr;                                                                              \
-            } else {                                                                                      \
-                a2 = asAddr;                                                                              \
-            }                                                                                             \
-        }                                                                                                 \
+                /* the careful path: symbols [valid, COUNT) of the iteration that starts at symbol FIRST of the group */
+#define IBZ2_CAREFUL( COUNT, FIRST, valid )                                                                  \
+    {                                                                                                        \
+        for ( uint32_t kk = valid; kk < COUNT; ++kk ) {                                                      \
+            IBZ2_REFILL();                                                                                   \
+            uint32_t entry = 0;                                                                              \
+            const uint32_t what = decodeOneSymbol( A, B, pos, lutAddr, table, bt, &entry );                  \
+            if ( what != SYM_PLAIN ) {                                                                       \
+                outcome = what == SYM_EOB ? 1U : 2U;                                                         \
+                groupDone = ( FIRST ) + kk;                                                                  \
+                break;                                                                                       \
+            }                                                                                                \
+            groupOut[( FIRST ) + kk] = static_cast<uint16_t>( entry );                                       \
+        }                                                                                                    \
+        IBZ2_REFILL();                                                                                       \
     }
 
-                uint32_t it = 0;
 #pragma unroll 1
-                for ( ; it < GROUP_SIZE / 6U; ++it ) {
-                    uint32_t a0, a1, a2, a3, a4, a5;
-                    uint32_t e0, e1;
-                    bool ok;
-                    IBZ2_FAST( 3, a0, a1, a2, e0, e1, ok );
-                    if ( !ok ) {
-                        IBZ2_SLOW( 3, a0, a1, a2, e0, e1, 6U * it );
-                    }
-                    if ( outcome == 0 ) {
+                for ( uint32_t first = 0; first < GROUP_SIZE - 2U; first += 6U ) {
+                    uint32_t a0, a1, a2, a3 = 0, a4 = 0, a5 = 0;
+                    uint32_t e0, e1, last;
+                    uint32_t valid = 6;
+                    IBZ2_FAST( 3, a0, a1, a2, e0, e1, last );
+                    if ( last == 0 ) {
+                        valid = ( e0 != 0 ? 1U : 0U ) + ( e1 != 0 ? 1U : 0U );
+                    } else {
                         IBZ2_REFILL();
-                        IBZ2_FAST( 3, a3, a4, a5, e0, e1, ok );
-                        if ( !ok ) {
-                            IBZ2_SLOW( 3, a3, a4, a5, e0, e1, 6U * it + 3U );
+                        IBZ2_FAST( 3, a3, a4, a5, e0, e1, last );
+                        if ( last == 0 ) {
+                            valid = 3U + ( e0 != 0 ? 1U : 0U ) + ( e1 != 0 ? 1U : 0U );
                         }
                     }
-                    IBZ2_REFILL();
-                    /* entry = address - lutAddr < 2^15: both halves at once, modulo 2^32 */
-                    outWords[3U * it] = a0 + ( a1 << 16 ) - packBias;
-                    outWords[3U * it + 1U] = a2 + ( a3 << 16 ) - packBias;
-                    outWords[3U * it + 2U] = a4 + ( a5 << 16 ) - packBias;
+                    if ( valid == 6U ) {
+                        IBZ2_REFILL();
+                        /* entry = address - lutAddr < 2^15: both halves at once, modulo 2^32 */
+                        uint32_t* const out = reinterpret_cast<uint32_t*>( groupOut + first );
+                        out[0] = a0 + ( a1 << 16 ) - packBias;
+                        out[1] = a2 + ( a3 << 16 ) - packBias;
+                        out[2] = a4 + ( a5 << 16 ) - packBias;
+                        continue;
+                    }
+                    {
+                        const uint32_t a[6] = { a0, a1, a2, a3, a4, a5 };
+#pragma unroll
+                        for ( uint32_t k = 0; k < 5U; ++k ) {
+                            if ( k < valid ) {
+                                groupOut[first + k] = static_cast<uint16_t>( a[k] - lutAddr );
+                            }
+                        }
+                    }
+                    IBZ2_CAREFUL( 6U, first, valid );
                     if ( outcome != 0 ) {
                         break;
                     }
@@ -407,18 +424,22 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 if ( outcome == 0 ) {
                     /* symbols 48 and 49 */
                     uint32_t a0, a1, a2 = 0;
-                    uint32_t e0, e1;
-                    bool ok;
-                    IBZ2_FAST( 2, a0, a1, a2, e0, e1, ok );
-                    if ( !ok ) {
-                        IBZ2_SLOW( 2, a0, a1, a2, e0, e1, GROUP_SIZE - 2U );
+                    uint32_t e0, e1, last;
+                    IBZ2_FAST( 2, a0, a1, a2, e0, e1, last );
+                    if ( last != 0 ) {
+                        IBZ2_REFILL();
+                        *reinterpret_cast<uint32_t*>( groupOut + GROUP_SIZE - 2U ) = a0 + ( a1 << 16 ) - packBias;
+                    } else {
+                        const uint32_t valid = e0 != 0 ? 1U : 0U;
+                        if ( valid != 0 ) {
+                            groupOut[GROUP_SIZE - 2U] = static_cast<uint16_t>( a0 - lutAddr );
+                        }
+                        IBZ2_CAREFUL( 2U, GROUP_SIZE - 2U, valid );
                     }
-                    IBZ2_REFILL();
-                    outWords[GROUP_SIZE / 2U - 1U] = a0 + ( a1 << 16 ) - packBias;
                 }
 #undef IBZ2_REFILL
 #undef IBZ2_FAST
-#undef IBZ2_SLOW
+#undef IBZ2_CAREFUL
                 d.A = A;
                 d.B = B;
                 d.craw = craw;
@@ -522,10 +543,11 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
     static const int lanes = [] () {
         const char* const env = std::getenv( "IBZ2_K2B_LANES" );
         const int v = env != nullptr ? std::atoi( env ) : BITS_LANES_DEFAULT;
-        return ( ( v == 1 ) || ( v == 2 ) || ( v == 4 ) || ( v == 8 ) || ( v == 16 ) ) ? v : BITS_LANES_DEFAULT;
+        return ( ( v == 2 ) || ( v == 4 ) || ( v == 8 ) || ( v == 16 ) ) ? v : BITS_LANES_DEFAULT;
     }();
-    auto* const kernel = lanes == 1 ? huffmanBitsKernel<1> : lanes == 2 ? huffmanBitsKernel<2>
-                         : lanes == 4 ? huffmanBitsKernel<4> : lanes == 8 ? huffmanBitsKernel<8> : huffmanBitsKernel<16>;
+    /* one lane per warp would need 64 warps per SM: 32 registers per thread, not enough for this loop */
+    auto* const kernel = lanes == 2 ? huffmanBitsKernel<2> : lanes == 4 ? huffmanBitsKernel<4>
+                         : lanes == 8 ? huffmanBitsKernel<8> : huffmanBitsKernel<16>;
     cudaFuncSetAttribute( kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>( shared ) );
     cudaFuncSetAttribute( kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
     cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );

@@ -498,7 +498,7 @@ mtfExpandKernel( const BlockMeta* __restrict__ meta, const uint32_t* __restrict_
 
 void
 launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_t* scratch, uint8_t* lbytes,
-           cudaStream_t stream )
+           cudaStream_t stream, cudaEvent_t chunkStop )
 {
     if ( nblocks == 0 ) {
         return;
@@ -506,6 +506,9 @@ launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_
     {
         const dim3 grid( ( MAX_CHUNKS + MTFC_THREADS - 1U ) / MTFC_THREADS, nblocks );
         mtfChunkKernel<<<grid, MTFC_THREADS, 0, stream>>>( meta, scratch );
+    }
+    if ( chunkStop != nullptr ) {
+        cudaEventRecord( chunkStop, stream );
     }
     mtfListsKernel<<<( nblocks + MTFL_WARPS - 1U ) / MTFL_WARPS, MTFL_WARPS * 32, 0, stream>>>( meta, nblocks, tables,
                                                                                              scratch );
@@ -519,7 +522,7 @@ launchMtf( BlockMeta* meta, uint32_t nblocks, const BlockTables* tables, uint32_
 void
 launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, uint8_t* lbytes,
                      uint8_t* selectors, BlockTables* tables, uint32_t* scratch, uint32_t* counter, bool ordered, cudaStream_t stream,
-                     cudaEvent_t bitsStart, cudaEvent_t bitsStop )
+                     cudaEvent_t bitsStart, cudaEvent_t bitsStop, cudaEvent_t chunkStop )
 {
     launchHuffmanHeader( data, nbytes, meta, nblocks, selectors, tables, stream );
     if ( bitsStart != nullptr ) {
@@ -529,7 +532,8 @@ launchHuffmanDecode( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint
     if ( bitsStop != nullptr ) {
         cudaEventRecord( bitsStop, stream );
     }
-    launchMtf( meta, nblocks, tables, scratch, lbytes, stream );
+    launchMtf( meta, nblocks, tables, scratch, lbytes, stream, chunkStop );
     launchHuffmanCareful( data, nbytes, meta, nblocks, lbytes, selectors, stream );
+    launchStreamProbe( data, nbytes, meta, nblocks, stream );
 }
 }  // namespace ibz2

@@ -89,6 +89,8 @@ public:
             throw std::runtime_error( std::string( "Cannot open the CUDA bzip2 decoder (there is no CPU fallback): " )
                                       + ibz2_last_error( nullptr ) );
         }
+        /* the readers fold the block CRCs themselves, in file order across all their batches */
+        ibz2_set_verify_stream_crc( m_ctx, 0 );
     }
 
     ~GpuDecoder()

@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <iostream>
 #include <memory>
+#include <sstream>
 #include <vector>
 
 #include "BlockIndex.hpp"
@@ -118,6 +119,7 @@ public:
 
         size_t nBytesDecoded = 0;
         while ( ( nBytesDecoded < nBytesToRead ) && !eof() ) {
+            throwDeferredStreamError();
             BlockSource::Block block;
 
             auto span = m_index.locate( m_currentPosition );
@@ -129,9 +131,11 @@ public:
                     m_atEndOfFile = true;
                     break;
                 }
+                /* the stream CRC is folded over the blocks in file order, exactly once each (BZ2Reader.hpp:481-484) */
                 const auto encodedOffsetInBits = m_source.finderOffsets()[dataBlockIndex];
                 block = m_source.fetch( encodedOffsetInBits, dataBlockIndex );
                 m_index.append( block.result->enc_offset_bits, block.result->enc_size_bits, block.result->out_size );
+                m_calculatedStreamCRC = ibz2_stream_crc_fold( m_calculatedStreamCRC, block.result->calculated_crc );
                 probeAfter( *block.result );
 
                 span = m_index.locate( m_currentPosition );
@@ -155,6 +159,9 @@ public:
             }
             nBytesDecoded += nBytesToDecode;
             m_currentPosition += nBytesToDecode;
+        }
+        if ( eof() ) {
+            throwDeferredStreamError();
         }
         return nBytesDecoded;
     }
@@ -295,6 +302,18 @@ public:
         setBlockOffsets( std::move( offsets ) );
     }
 
+    /**
+     * New next to the reference, whose parallel reader never looks at the stream CRC (only BZ2Reader does,
+     * BZ2Reader.hpp:406-416): while the block map is being built, the CRCs of the blocks are folded per stream and
+     * compared with the CRC field of the end-of-stream block.  A mismatch throws what BZ2Reader throws, after the bytes
+     * of the stream's last block have been delivered.  On by default; switch it off for the reference's exact behaviour.
+     */
+    void
+    setVerifyStreamCRC( bool verify )
+    {
+        m_verifyStreamCRC = verify;
+    }
+
     [[nodiscard]] ibz2_timings
     lastTimings()
     {
@@ -345,7 +364,18 @@ private:
         if ( next.is_eos == 0 ) {
             return;
         }
+        if ( m_verifyStreamCRC && ( next.expected_crc != m_calculatedStreamCRC ) && m_deferredStreamError.empty() ) {
+            std::stringstream msg;
+            msg << "[BZip2 block header] Stream CRC 0x" << std::hex << next.expected_crc
+                << " does not match calculated CRC 0x" << m_calculatedStreamCRC;
+            m_deferredStreamError = std::move( msg ).str();
+        }
+        m_calculatedStreamCRC = 0;
         m_index.append( next.enc_offset_bits, next.enc_size_bits, 0 );
+        if ( !m_deferredStreamError.empty() && !m_deferredStreamErrorArmed ) {
+            m_deferredStreamErrorArmed = true;
+            m_deferredStreamErrorAt = m_index.back().second;   /* where the stream's decoded bytes end */
+        }
         const auto nextStreamOffsetInBits = next.enc_offset_bits + next.enc_size_bits;
         if ( nextStreamOffsetInBits < m_source.fileSizeInBits() ) {
             uint64_t position = nextStreamOffsetInBits;
@@ -357,8 +387,25 @@ private:
         }
     }
 
+    /** thrown where BZ2Reader would throw: once the bytes in front of the end-of-stream block have been handed out */
+    void
+    throwDeferredStreamError()
+    {
+        if ( m_deferredStreamErrorArmed && ( m_currentPosition >= m_deferredStreamErrorAt ) ) {
+            const auto message = std::move( m_deferredStreamError );
+            m_deferredStreamError.clear();
+            m_deferredStreamErrorArmed = false;
+            throw std::runtime_error( message );
+        }
+    }
+
     BlockSource m_source;
     BlockIndex m_index;
+    bool m_verifyStreamCRC{ true };
+    uint32_t m_calculatedStreamCRC{ 0 };
+    std::string m_deferredStreamError;
+    bool m_deferredStreamErrorArmed{ false };
+    size_t m_deferredStreamErrorAt{ 0 };
 
     size_t m_currentPosition{ 0 };
     bool m_atEndOfFile{ false };

@@ -6,6 +6,7 @@
  */
 #include <cstdint>
 #include <cstring>
+#include <cstdlib>
 #include <memory>
 #include <new>
 #include <optional>
@@ -70,6 +71,17 @@ namespace
 {
 thread_local std::string g_openError;
 thread_local int g_openKind = IBZ2R_NONE;
+thread_local int g_openDevice = -1;   /* ibz2r_set_open_device; -1 = $IBZ2_DEVICE, else device 0 */
+
+int
+openDevice()
+{
+    if ( g_openDevice >= 0 ) {
+        return g_openDevice;
+    }
+    const char* const env = std::getenv( "IBZ2_DEVICE" );
+    return env != nullptr ? std::max( 0, std::atoi( env ) ) : 0;
+}
 
 template<typename Function>
 long long
@@ -116,9 +128,9 @@ wrap( UniqueFileReader fileReader, size_t parallelization )
     auto handle = std::make_unique<ibz2_reader>();
     /* parallelization == 1 selects the serial class, anything else the parallel one (indexed_bzip2.pyx:295-296) */
     if ( parallelization == 1 ) {
-        handle->reader = std::make_unique<BZ2Reader>( std::move( fileReader ) );
+        handle->reader = std::make_unique<BZ2Reader>( std::move( fileReader ), openDevice() );
     } else {
-        auto parallel = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), parallelization );
+        auto parallel = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), parallelization, openDevice() );
         handle->parallel = parallel.get();
         handle->reader = std::move( parallel );
     }
@@ -136,6 +148,13 @@ openWith( Function&& function )
 }  // namespace
 
 extern "C" {
+/* the CUDA device the readers opened next by this thread decode on (the C++ constructors take it as an argument) */
+void
+ibz2r_set_open_device( int device )
+{
+    g_openDevice = device;
+}
+
 ibz2_reader*
 ibz2r_open_path( const char* path, size_t parallelization )
 {
@@ -276,6 +295,16 @@ ibz2r_set_block_offsets( ibz2_reader* r, const uint64_t* pairs, size_t count )
         r->reader->setBlockOffsets( std::move( offsets ) );
         return 0LL;
     } ) );
+}
+
+/* ParallelBZ2Reader::setVerifyStreamCRC; the serial class always checks (BZ2Reader.hpp:406-416) */
+int
+ibz2r_set_verify_stream_crc( ibz2_reader* r, int verify )
+{
+    if ( r->parallel != nullptr ) {
+        r->parallel->setVerifyStreamCRC( verify != 0 );
+    }
+    return 0;
 }
 
 int

@@ -24,6 +24,8 @@
 #include <unistd.h>
 
 #include "../host/BZ2Reader.hpp"
+#include <cstdlib>
+
 #include "../host/ParallelBZ2Reader.hpp"
 
 using namespace ibz2host;
@@ -392,7 +394,12 @@ ibzip2CLI( int argc, char** argv )
         if ( decoderParallelism == 1 ) {
             reader = std::make_unique<BZ2Reader>( std::move( fileReader ) );
         } else {
-            reader = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), decoderParallelism );
+            auto parallelReader = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), decoderParallelism );
+            /* the reference's parallel reader never looks at the stream CRC; this one does unless told not to */
+            if ( const char* const env = std::getenv( "IBZ2_VERIFY_STREAM_CRC" ); ( env != nullptr ) && ( env[0] == '0' ) ) {
+                parallelReader->setVerifyStreamCRC( false );
+            }
+            reader = std::move( parallelReader );
         }
         reader->setShowProfileOnDestruction( verbose );
 

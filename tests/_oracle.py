@@ -254,9 +254,10 @@ def ref_decode_file(path: str, parallelization: int = 4, serial_class: bool = Fa
     return RefResult(rc, err, payload, offs, secs.value)
 
 
-def ref_find_magic(data, magic: int, parallelization: int = 1, buffer_bytes: int = 1 << 20) -> np.ndarray:
+def ref_find_magic(data, magic: int, parallelization: int = 1, buffer_bytes: int = 1 << 20,
+                   capacity: int | None = None) -> np.ndarray:
     a = _buf(data)
-    cap = a.size // 6 + 16
+    cap = capacity if capacity is not None else a.size // 6 + 16
     out = np.zeros(cap, dtype=np.uint64)
     count = C.c_uint64(0)
     rc = ref().ref_find_magics(_ptr(a), a.size, magic, parallelization, buffer_bytes, _ptr(out), cap, C.byref(count), None)

@@ -28,7 +28,9 @@ import numpy as np
 HERE = Path(__file__).resolve().parent
 ROOT = HERE.parent.parent
 sys.path.insert(0, str(ROOT / "tests"))
+sys.path.insert(0, str(HERE))
 import _oracle  # noqa: E402
+import craft  # noqa: E402  (tests/golden/craft.py: hand-written streams libbz2 never produces)
 
 REF_DATA = Path("/root/reference/src/tests/data")
 CASES = HERE / "cases"
@@ -100,6 +102,41 @@ def generated_cases() -> dict[str, bytes]:
     hdr = bytearray(ref["dolorem-ipsum.txt"])
     hdr[3] = ord("1")  # BZh1 header in front of a block produced at level 9 (Appendix C-1: level digit ignored)
     cases["level-digit-ignored"] = bytes(hdr)
+
+    # ---- round 2 (appended, so that the generator state of the cases above is unchanged) ----
+    rng2 = np.random.default_rng(20261105)
+    # 2, 3, 4, 5 and 6 Huffman groups: libbz2 picks the count from the number of MTF symbols (< 200, 600, 1200, 2400)
+    for groups, size in [(2, 150), (3, 450), (4, 900), (5, 1800), (6, 4000)]:
+        cases[f"groups-{groups}"] = bz2.compress(rng2.bytes(size), 9)
+    # codes of up to 20 bits (bzip2.hpp:97; libbz2's encoder stops at 17): three hand-made tables, two of them with
+    # lengths 1, 2, 3, ..., 19, 20, 20 in opposite symbol orders, so that the 18..20-bit codes really occur
+    vals = np.arange(19, dtype=np.uint8) + 65
+    prob = 0.5 ** np.arange(1, 20)
+    prob[-1] *= 2
+    skew = bytes(rng2.choice(vals, 6000, p=prob / prob.sum())) + bytes(vals) * 3
+    packed = craft.rle1(skew)
+    last, _ = craft.bwt(packed)
+    used = sorted(set(packed))
+    symbols = craft.mtf_rle2(last, used)
+    alphabet = len(used) + 2
+    by_freq = sorted(range(alphabet), key=lambda x: (-symbols.count(x), x))
+    tables = [craft.skewed_lengths(alphabet, by_freq), craft.skewed_lengths(alphabet, by_freq[::-1]),
+              craft.skewed_lengths(alphabet, by_freq, longest=12)]
+    cases["long-codes-20bit"] = craft.stream([dict(data=skew, tables=tables,
+                                                   selectors_of=lambda g: (0, 0, 2, 1, 0, 2)[g % 6])])
+    # an EMPTY symbol map: the alphabet is RUNA, RUNB and the end-of-block symbol would be 1 = RUNB, which
+    # bzip2.hpp:723 takes for a run symbol first, so the block never ends (selector out of range)
+    cases["err-empty-symbol-map-runb"] = craft.stream([dict(data=b"x", tables=[[1, 1], [1, 1]], raw_symbols=[1])])
+    cases["err-empty-symbol-map-runs"] = craft.stream([dict(data=b"x", tables=[[1, 1], [1, 1]],
+                                                            raw_symbols=[0] * 30 + [1])])
+    # wrong STREAM CRC (the 32 bits behind the end-of-stream magic) with every block CRC right: BZ2Reader.hpp:406-416
+    # throws, ParallelBZ2Reader does not look at it
+    bad = bytearray(cases["text-450k-l1"])
+    bad[-3] ^= 0x04
+    cases["err-stream-crc"] = bytes(bad)
+    second = bytearray(bz2.compress(text_like(rng2, 30_000), 1))
+    second[-3] ^= 0x40
+    cases["err-stream-crc-multistream"] = ref["base64-32KiB"] + bytes(second) + ref["1B"]
     return cases
 
 
@@ -139,6 +176,9 @@ def main() -> None:
                                "stdout_sha256": hashlib.sha256(out).hexdigest()}
         # independent cross-check (libbz2) where the file is valid
         try:
+            if name.startswith("err-stream-crc"):
+                # CPython's bz2.decompress silently drops an invalid stream that follows a valid one: no cross-check
+                raise ValueError("stream CRC damaged on purpose")
             raw = bz2.decompress(blob)
             entry["libbz2_sha256"] = hashlib.sha256(raw).hexdigest()
         except Exception as e:  # noqa: BLE001

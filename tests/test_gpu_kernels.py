@@ -30,6 +30,9 @@ def case(name):
 @pytest.fixture(scope="module")
 def ctx():
     c = _capi.Context(0)
+    # these tests compare block by block with the oracle's decode_block, which knows nothing about streams: the library's
+    # stream CRC verdict (IBZ2_ST_STREAM_CRC on the last block of a stream) is switched on where it is the subject
+    c.set_verify_stream_crc(False)
     yield c
     c.close()
 
@@ -301,6 +304,69 @@ def test_error_statuses_match_oracle(ctx):
         for off, r in zip(offs.tolist(), results):
             want = orc.decode_block(data, off, stages=False)
             assert r["status"] == want.info.status, f"{name}@{off}"
+
+
+def reference_stream_crcs(data: bytes):
+    """(bit offset of the stream's last data block, CRC field of its EOS block, fold of its block CRCs) per stream, from
+    the oracle's block headers: BZ2Reader.hpp:406-416 / :481-484 restated on the host"""
+    streams = []
+    crc = 0
+    last = None
+    eos = set(orc.find_magic(data, orc.MAGIC_EOS).tolist())
+    for offset in orc.find_magics(data).tolist():
+        if offset in eos:
+            header = _capi.read_block_header(data, offset)
+            if last is not None:
+                streams.append((last, header.expected_crc, crc))
+            crc, last = 0, None
+        else:
+            block = orc.decode_block(data, offset, stages=False)
+            crc = _capi.stream_crc_fold(crc, block.info.calc_crc)
+            last = offset
+    return streams
+
+
+@pytest.mark.parametrize("name", VALID)
+def test_stream_crc_fold(ctx, name):
+    """north_star step 6: the block CRCs are combined into the stream CRC and compared with the end-of-stream block.
+    Every stream of every golden file that the reference decodes gets checked; the two err-stream-crc files (every block
+    CRC right, the stream CRC wrong) get IBZ2_ST_STREAM_CRC on the last block of the damaged stream, and only there."""
+    data = case(name)
+    if name == "err-gap-then-valid":
+        pytest.skip("the finder lists a block behind a gap that belongs to no stream the readers reach")
+    want = reference_stream_crcs(data)
+    out = np.zeros(GOLDEN[name]["parallel"]["size"] + 64, dtype=np.uint8)
+    ctx.set_verify_stream_crc(True)   # the library's default
+    try:
+        results, total = ctx.decode_buffer(data, out, max_blocks=4096)
+    finally:
+        ctx.set_verify_stream_crc(False)
+    assert total == GOLDEN[name]["parallel"]["size"]
+    closing = results[(results["stream_flags"] & 2) != 0]
+    assert closing["enc_offset_bits"].tolist() == [w[0] for w in want]
+    assert closing["stream_crc_expected"].tolist() == [w[1] for w in want]
+    assert ((closing["stream_flags"] & 4) != 0).all()           # every stream starts inside the call: all checked
+    assert closing["stream_crc_calculated"].tolist() == [w[2] for w in want]
+    bad = [w[0] for w in want if w[1] != w[2]]
+    assert results["enc_offset_bits"][results["status"] == 17].tolist() == bad
+    assert (len(bad) > 0) == name.startswith("err-stream-crc")
+    assert ((results["status"] == 0) | (results["status"] == 17)).all()
+    # facts only, no verdict
+    quiet, _ = ctx.decode_buffer(data, out, max_blocks=4096)
+    assert (quiet["status"] == 0).all() and quiet["stream_crc_calculated"].tolist() == results["stream_crc_calculated"].tolist()
+    # a call that begins in the middle of a stream cannot vouch for that stream
+    if len(results) > 1 and (results["stream_flags"][1] & 1) == 0:
+        ctx.set_verify_stream_crc(True)
+        try:
+            tail, _ = ctx.decode_blocks(data, results["enc_offset_bits"][1:].copy(), out)
+        finally:
+            ctx.set_verify_stream_crc(False)
+        first_closing = tail[(tail["stream_flags"] & 2) != 0][0]
+        assert (first_closing["stream_flags"] & 4) == 0 and first_closing["status"] == 0
+    # the host-side fold over results laid end to end (what a multi-GPU caller does with its shares)
+    again = quiet.copy()
+    assert _capi.fold_stream_crcs(again, verify=True) == len(bad)
+    assert again["status"].tolist() == results["status"].tolist()
 
 
 def test_synthetic_corruptions_match_oracle(ctx):

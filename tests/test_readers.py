@@ -102,11 +102,16 @@ def test_cli_version_and_help_need_no_gpu():
 # on the B200
 # ---------------------------------------------------------------------------------------------------------------
 
+STREAM_CRC_CASES = [n for n in ALL if n.startswith("err-stream-crc")]
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ALL)
 def test_parallel_reader_matches_reference(name):
     want = GOLDEN[name]["parallel"]
-    f = ibz2.open(path(name), parallelization=4)
+    # the reference's ParallelBZ2Reader never looks at the stream CRC (only BZ2Reader does, BZ2Reader.hpp:406-416);
+    # ours does by default -- see test_parallel_reader_checks_the_stream_crc -- and is compared here with the check off
+    f = ibz2.open(path(name), parallelization=4, verify_stream_crc=name not in STREAM_CRC_CASES)
     if want["rc"] != 0:
         with pytest.raises(Exception) as info:
             f.read()
@@ -138,6 +143,31 @@ def test_serial_reader_matches_reference(name):
     data = f.read()
     assert len(data) == want["size"] and sha(data) == want["sha256"]
     assert [list(kv) for kv in sorted(f.block_offsets().items())] == want["offsets"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", STREAM_CRC_CASES)
+def test_parallel_reader_checks_the_stream_crc(name):
+    """Deliberate deviation: the parallel reader folds the block CRCs per stream while it builds the
+    block map and throws what the reference's SERIAL reader throws (BZ2Reader.hpp:406-416), after it has handed out
+    every byte in front of the end-of-stream block -- the same bytes the serial reference writes before it throws."""
+    want = GOLDEN[name]["serial"]
+    assert want["rc"] != 0 and "Stream CRC" in want["error"]
+    f = ibz2.open(path(name), parallelization=4)
+    got = bytearray()
+    with pytest.raises(RuntimeError) as info:
+        while True:
+            chunk = f.read(100_000)
+            if not chunk:
+                break
+            got += chunk
+    assert str(info.value) == want["error"]
+    cli = GOLDEN[name]["cli_serial"]
+    assert len(got) == cli["stdout_size"] and sha(bytes(got)) == cli["stdout_sha256"]
+    # the check happens once, while the map is built (BZ2Reader.hpp:409): afterwards the file reads like any other
+    rest = f.read()
+    everything = ibz2.open(path(name), parallelization=4, verify_stream_crc=False).read()
+    assert bytes(got) + rest == everything and sha(everything) == GOLDEN[name]["parallel"]["sha256"]
 
 
 @pytest.mark.gpu
@@ -217,7 +247,15 @@ def test_python_sources_fd_fileobject_bytesio():
 @pytest.mark.parametrize("flavour,parallelism", [("cli_parallel", "4"), ("cli_serial", "1")])
 def test_cli_decompress_matches_reference(name, flavour, parallelism):
     want = GOLDEN[name][flavour]
-    out = subprocess.run([str(CLI), "-d", "-c", "-P", parallelism, path(name)], capture_output=True)
+    env = dict(os.environ)
+    if name in STREAM_CRC_CASES and flavour == "cli_parallel":
+        # with its stream CRC check on (the default) the parallel reader behaves like the reference's serial one
+        out = subprocess.run([str(CLI), "-d", "-c", "-P", parallelism, path(name)], capture_output=True)
+        serial = GOLDEN[name]["cli_serial"]
+        assert out.returncode == serial["rc"] and out.stderr.decode().strip() == serial["stderr"]
+        assert len(out.stdout) == serial["stdout_size"] and sha(out.stdout) == serial["stdout_sha256"]
+        env["IBZ2_VERIFY_STREAM_CRC"] = "0"   # ... and like the reference's parallel one with the check off
+    out = subprocess.run([str(CLI), "-d", "-c", "-P", parallelism, path(name)], capture_output=True, env=env)
     assert out.returncode == want["rc"]
     assert out.stderr.decode().strip() == want["stderr"]
     if want["rc"] == 0 or flavour == "cli_parallel":
