@@ -39,6 +39,9 @@ constexpr int BITS_SLOTS = 32;          /* decoders per CTA */
 constexpr int BITS_CTAS_PER_SM = 2;
 constexpr int BITS_LANES_DEFAULT = 4;   /* active lanes per warp; BITS_SLOTS / lanes warps per CTA */
 /* experiment switches (the defaults are what the measurements in DESIGN.md chose) */
+#ifndef IBZ2_K2B_TOUCH
+#define IBZ2_K2B_TOUCH 1
+#endif
 #ifndef IBZ2_K2B_PREFETCH_WORDS
 #define IBZ2_K2B_PREFETCH_WORDS 40
 #endif
@@ -116,6 +119,17 @@ loadWordRaw( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t wordInd
         }
     }
     return w;
+}
+
+/* A load whose only purpose is to bring its sector into L1 (prefetch.global.L1 does not: with it 1 load in 8, the first
+ * of every sector, still missed).  The value is kept alive by the caller until long after it has arrived, so that the
+ * register is not handed to something that would then wait for the load. */
+__device__ __forceinline__ uint32_t
+touch( const uint32_t* p )
+{
+    uint32_t v;
+    asm volatile( "ld.global.nc.u32 %0, [%1];" : "=r"( v ) : "l"( p ) );
+    return v;
 }
 
 __device__ __forceinline__ uint32_t
@@ -230,6 +244,7 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
     uint32_t nsym = 0;
     uint32_t selIdx = 0;
     uint32_t selWord = 0;
+    uint32_t sink = 0;   /* keeps the touch() loads alive */
 
     while ( true ) {
         if ( !haveBlock ) {
@@ -327,6 +342,12 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 uint16_t* const groupOut = symOut + nsym;   /* nsym is a multiple of 50: 4-byte aligned */
                 const uint32_t packBias = lutAddr * 0x00010001U;
                 prefetchStream( wbase + IBZ2_K2B_PREFETCH_WORDS );   /* stays inside the file: see GROUP_MAX_WORDS */
+#if IBZ2_K2B_TOUCH
+                /* the sectors the groups after this one will read (a group takes 25 to 60 bytes): every first load of a
+                 * sector went to L2 or HBM otherwise, and the word queue hides one L1 hit, not that */
+                const uint32_t touched0 = touch( wbase + 24 );
+                const uint32_t touched1 = touch( wbase + 32 );
+#endif
                 uint32_t A = d.A;
                 uint32_t B = d.B;
                 uint32_t craw = d.craw;
@@ -445,6 +466,9 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
                 d.craw = craw;
                 d.pos = pos;
                 d.wordIdx += wofs;
+#if IBZ2_K2B_TOUCH
+                sink ^= touched0 ^ touched1;
+#endif
                 nsym += outcome == 0 ? GROUP_SIZE : groupDone;
             } else {
                 /* ---- the last groups before the end of the file: one symbol at a time with checked loads ---- */
@@ -472,6 +496,7 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
         if ( outcome != 0 ) {
             const uint64_t endBit = d.wordIdx * 32U + d.pos;
             BlockMeta& bm = meta[block];
+            bm.cycleLen = sink;   /* a diagnostic field that K4b overwrites: gives the touch() loads a use */
             if ( ( outcome == 1 ) && ( endBit <= nbits ) ) {
                 bm.nCoded = nsym;
                 bm.endBit = endBit;

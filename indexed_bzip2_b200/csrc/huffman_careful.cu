@@ -257,6 +257,7 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
     const uint64_t startBit = bm.bitOffset;
 
     uint32_t status = IBZ2_ST_OK;
+    uint32_t selectorsSeen = 0;   /* the selector count, for the message of a selector overrun */
     uint32_t headerCrc = 0;
     uint32_t origPtr = 0;
     uint32_t cnt = 0;       /* dbufCount */
@@ -352,6 +353,7 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
             break;
         }
         const uint32_t selectorsCount = br.get( 15 );
+        selectorsSeen = selectorsCount;
         if ( br.tell() > nbits ) {
             status = IBZ2_ST_EOF;
             break;
@@ -579,7 +581,8 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
         bm.status = status;
         bm.headerCrc = headerCrc;
         bm.origPtr = origPtr;
-        bm.n = ( status == IBZ2_ST_OK ) ? cnt : 0U;
+        /* a selector overrun reports the selector count, which the reference puts into its message (bzip2.hpp:714-718) */
+        bm.n = ( status == IBZ2_ST_OK ) ? cnt : ( status == IBZ2_ST_SELECTOR_OVERRUN ? selectorsSeen : 0U );
         bm.endBit = endBit;
         bm.isEos = isEos;
         bm.isEof = isEof;

@@ -42,27 +42,35 @@ k2Scratch( uint32_t* scratchAll, uint32_t block )
 }
 
 /* ---------------------------------------------------------------- K2c ---------------------------------------- */
-/* The list as 16 quads of 16 entries: quad 0 lives in registers, quads 1..15 in the lane's own shared-memory column
- * ([quad][thread], so the 32 lanes of a 16-byte access cover 512 contiguous bytes).  Shifting a whole quad per
- * iteration instead of a word takes half the instructions per byte moved, and a quarter-warp none of whose lanes still
- * has quads to shift costs no shared-memory wavefront -- with 32-bit accesses every iteration cost one as long as a
- * single lane of the warp was still shifting (measured: 15 of 32 lanes active, the LSU pipe 96 % busy). */
+/* A move-to-front step costs what it moves: with the list as one array that is the index itself, 128 bytes on average
+ * for incompressible data, and a warp waits for the lane with the largest index (the first version of this kernel
+ * shifted 16-byte quads through shared memory: 47 G warp instructions per 8 GB, 15 of 32 lanes active, LSU-bound).
+ * Here a step costs the same whatever the index is:
+ *   F   the entries moved to the front since the last merge, newest first, in registers (at most 15 of them);
+ *   M   the other entries in shared memory, 16 rows of 16, each row's live entries packed at its start.  Taking an entry
+ *       out of M closes the gap inside its row only and leaves the row one entry short (a "hole").
+ * The list is F followed by the live entries of the rows in order.  An index below |F| is served inside the registers;
+ * any other index j - |F| falls into row r0 = j' / 16 or the row after it, because there are at most 15 holes in
+ * total -- `before[k]`, the number of holes in front of row k, is kept as 16 nibbles, so that one funnel shift yields
+ * before[r0] and before[r0 + 1].  When some lane of the warp has collected 14 entries in F, every lane merges: F and
+ * the rows are streamed into full rows again (byte permutes with a carry word, word stores at a running address).
+ * Rows are stored as words, [word][thread]: a lane only ever touches its own bank, whatever row it is working on. */
+constexpr uint32_t MTF_MERGE_AT = 14;   /* F may grow by two entries between two looks at it: never more than 15 */
+
 __device__ __forceinline__ uint32_t
 quadWord( const uint4& q, uint32_t w )
 {
     return w == 0 ? q.x : ( w == 1 ? q.y : ( w == 2 ? q.z : q.w ) );
 }
 
-/* entries move up by one, `in` becomes entry 0; returns the entry pushed out */
-__device__ __forceinline__ uint32_t
+/* entries move up by one, `in` becomes entry 0 */
+__device__ __forceinline__ void
 shiftQuad( uint4& q, uint32_t in )
 {
-    const uint32_t out = q.w >> 24;
     q.w = __funnelshift_l( q.z, q.w, 8 );
     q.z = __funnelshift_l( q.y, q.z, 8 );
     q.y = __funnelshift_l( q.x, q.y, 8 );
     q.x = ( q.x << 8 ) | in;
-    return out;
 }
 
 /* entries 0 .. e - 1 of the quad move up by one (entry e is overwritten), `in` becomes entry 0; e = 4 w + sh / 8 */
@@ -85,7 +93,7 @@ shiftQuadBelow( uint4& q, uint32_t w, uint32_t sh, uint32_t in )
 __global__ void __launch_bounds__( MTFC_THREADS )
 mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scratchAll )
 {
-    __shared__ uint4 lists[16][MTFC_THREADS];   /* [quad][thread]; row 0 is not used (registers) */
+    __shared__ uint32_t rows[64][MTFC_THREADS];   /* word 4 r + k of a lane's list = entries 16 r + 4 k .. + 3 of M */
 
     const uint32_t block = blockIdx.y;
     const BlockMeta& bm = meta[block];
@@ -95,10 +103,12 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
     const uint32_t nCoded = bm.nCoded;
     const uint32_t chunk = blockIdx.x * MTFC_THREADS + threadIdx.x;
     const uint32_t begin = chunk << MTF_CHUNK_SHIFT;
-    if ( begin >= nCoded ) {
-        return;
+    if ( ( blockIdx.x * MTFC_THREADS ) << MTF_CHUNK_SHIFT >= nCoded ) {
+        return;   /* the whole CTA */
     }
-    const uint32_t count = min( MTF_CHUNK, nCoded - begin );
+    /* every lane of a warp stays until the warp's longest chunk is done: the merges are decided by votes */
+    const uint32_t count = begin < nCoded ? min( MTF_CHUNK, nCoded - begin ) : 0U;
+    const uint32_t warpCount = __reduce_max_sync( FULL, count );
     uint8_t* const scratch = k2Scratch( scratchAll, block );
     const uint16_t* const sym16 = reinterpret_cast<const uint16_t*>( scratch + K2_SYM16_OFFSET ) + begin;
     uint32_t* const sym8 = reinterpret_cast<uint32_t*>( scratch + K2_SYM8_OFFSET + begin );
@@ -107,74 +117,181 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
 
     /* digits of a RUNA/RUNB number directly in front of the chunk (bzip2.hpp:726-743: runPos = 1 << digits) */
     uint32_t runDigits = 0;
-    while ( ( runDigits <= MAX_RUN_DIGITS ) && ( runDigits < begin ) && ( sym16[-1 - static_cast<int>( runDigits )] <= 1U ) ) {
-        ++runDigits;
+    if ( count > 0 ) {
+        while ( ( runDigits <= MAX_RUN_DIGITS ) && ( runDigits < begin ) && ( sym16[-1 - static_cast<int>( runDigits )] <= 1U ) ) {
+            ++runDigits;
+        }
     }
     const uint32_t runShift = runDigits;
     bool longRun = runDigits > MAX_RUN_DIGITS;
     uint32_t produced = 0;   /* bytes of L the chunk's symbols stand for */
 
-    uint4* const my = &lists[0][threadIdx.x];
+    uint32_t* const my = &rows[0][threadIdx.x];
     constexpr uint32_t STRIDE = MTFC_THREADS;
 #pragma unroll
-    for ( uint32_t q = 1; q < 16U; ++q ) {
-        const uint32_t first = 0x03020100U + 0x10101010U * q;
-        my[q * STRIDE] = make_uint4( first, first + 0x04040404U, first + 0x08080808U, first + 0x0C0C0C0CU );
+    for ( uint32_t w = 0; w < 64U; ++w ) {
+        my[w * STRIDE] = 0x03020100U + 0x04040404U * w;   /* the identity list */
     }
-    uint4 head = make_uint4( 0x03020100U, 0x07060504U, 0x0B0A0908U, 0x0F0E0D0CU );   /* list entries 0..15 */
+    uint4 head = make_uint4( 0, 0, 0, 0 );   /* F */
+    uint32_t f = 0;
+    uint32_t beforeLo = 0;                   /* before[k] = holes in front of row k, one nibble each */
+    uint32_t beforeHi = 0;
+    uint32_t front = 0;                      /* entry 0 of the list */
 
-    for ( uint32_t base = 0; base < count; base += 8U ) {
+    /* F and the rows -> full rows.  Reads run one row ahead of the writes, which can reach that far. */
+    auto merge = [&] () {
+        uint32_t carry = 0;
+        uint32_t carryBytes = 0;
+        uint32_t* out = my;
+        const uint32_t* in = my;
+        uint32_t s0 = head.x;
+        uint32_t s1 = head.y;
+        uint32_t s2 = head.z;
+        uint32_t s3 = head.w;
+        uint32_t live = f;
+        uint32_t holesLo = beforeLo;
+        uint32_t holesHi = beforeHi;
+        uint32_t holesBefore = 0;
+#pragma unroll 1
+        for ( uint32_t r = 0; r <= 16U; ++r ) {
+            uint32_t n0 = 0;
+            uint32_t n1 = 0;
+            uint32_t n2 = 0;
+            uint32_t n3 = 0;
+            uint32_t nextLive = 0;
+            if ( r < 16U ) {
+                n0 = in[0];
+                n1 = in[STRIDE];
+                n2 = in[2U * STRIDE];
+                n3 = in[3U * STRIDE];
+                in += 4U * STRIDE;
+                holesLo = __funnelshift_r( holesLo, holesHi, 4 );
+                holesHi >>= 4;
+                const uint32_t holesBehind = r == 15U ? f : ( holesLo & 15U );   /* before[r + 1]; all of them behind the last row */
+                nextLive = 16U - ( holesBehind - holesBefore );
+                holesBefore = holesBehind;
+            }
+            /* the source's bytes go behind the carry's: word i of the result = bytes 4 i - carryBytes .. of the source */
+            const uint32_t selB = 0x7654U - 0x1111U * carryBytes;
+            const uint32_t lowNibbles = ( 1U << ( 4U * carryBytes ) ) - 1U;
+            const uint32_t selA = ( selB & ~lowNibbles ) | ( 0x3210U & lowNibbles );
+            const uint32_t y0 = __byte_perm( carry, s0, selA );
+            const uint32_t y1 = __byte_perm( s0, s1, selB );
+            const uint32_t y2 = __byte_perm( s1, s2, selB );
+            const uint32_t y3 = __byte_perm( s2, s3, selB );
+            const uint32_t y4 = __byte_perm( s3, 0U, selB );
+            const uint32_t total = carryBytes + live;   /* <= 3 + 16 */
+            const uint32_t full = total >> 2;
+            if ( full > 0U ) {
+                out[0] = y0;
+            }
+            if ( full > 1U ) {
+                out[STRIDE] = y1;
+            }
+            if ( full > 2U ) {
+                out[2U * STRIDE] = y2;
+            }
+            if ( full > 3U ) {
+                out[3U * STRIDE] = y3;
+            }
+            out += full * STRIDE;
+            carry = full == 0U ? y0 : ( full == 1U ? y1 : ( full == 2U ? y2 : ( full == 3U ? y3 : y4 ) ) );
+            carryBytes = total & 3U;
+            s0 = n0;
+            s1 = n1;
+            s2 = n2;
+            s3 = n3;
+            live = nextLive;
+        }
+        f = 0;
+        beforeLo = 0;
+        beforeHi = 0;
+    };
+
+    for ( uint32_t base = 0; base < warpCount; base += 8U ) {
         /* 8 symbols per 16-byte load; `begin` is a multiple of 1024 symbols, so the loads are aligned */
-        const uint4 v = *reinterpret_cast<const uint4*>( sym16 + base );
+        const uint4 v = base < count ? *reinterpret_cast<const uint4*>( sym16 + base ) : make_uint4( 0, 0, 0, 0 );
         const uint32_t packed[4] = { v.x, v.y, v.z, v.w };
         uint32_t out[2] = { 0, 0 };
 #pragma unroll
         for ( uint32_t k = 0; k < 8U; ++k ) {
             const uint32_t sym = ( packed[k >> 1] >> ( 16U * ( k & 1U ) ) ) & 0xFFFFU;
-            uint32_t o = head.x & 0xFFU;
-            if ( base + k < count ) {
+            const bool valid = base + k < count;
+            if ( valid ) {
                 const bool isRun = sym <= 1U;
                 produced += isRun ? ( ( sym + 1U ) << min( runDigits, MAX_RUN_DIGITS ) ) : 1U;
                 runDigits = isRun ? runDigits + 1U : 0U;
                 longRun = longRun || ( runDigits > MAX_RUN_DIGITS );
             }
-            if ( ( sym >= 2U ) && ( base + k < count ) ) {
+            if ( ( sym >= 2U ) && valid ) {
                 const uint32_t idx = sym - 1U;   /* 1..255 */
-                const uint32_t w = ( idx >> 2 ) & 3U;
-                const uint32_t sh = 8U * ( idx & 3U );
-                if ( idx < 4U ) {
-                    o = ( head.x >> sh ) & 0xFFU;
-                    const uint32_t keep = ( idx == 3U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );
-                    head.x = ( head.x & keep ) | ( ( ( head.x << 8 ) | o ) & ~keep );
-                } else if ( idx < 16U ) {
-                    o = ( quadWord( head, w ) >> sh ) & 0xFFU;
-                    shiftQuadBelow( head, w, sh, o );
-                } else {
-                    const uint32_t Q = idx >> 4;
-                    uint4 last = my[Q * STRIDE];
-                    o = ( quadWord( last, w ) >> sh ) & 0xFFU;
-                    uint32_t carry = shiftQuad( head, o );
-#pragma unroll 2
-                    for ( uint32_t q = 1; q < Q; ++q ) {
-                        uint4 x = my[q * STRIDE];
-                        carry = shiftQuad( x, carry );
-                        my[q * STRIDE] = x;
+                if ( idx < f ) {
+                    /* inside F */
+                    const uint32_t w = ( idx >> 2 ) & 3U;
+                    const uint32_t sh = 8U * ( idx & 3U );
+                    if ( idx < 4U ) {
+                        front = ( head.x >> sh ) & 0xFFU;
+                        const uint32_t keep = ( idx == 3U ) ? 0U : ( 0xFFFFFFFFU << ( sh + 8U ) );
+                        head.x = ( head.x & keep ) | ( ( ( head.x << 8 ) | front ) & ~keep );
+                    } else {
+                        front = ( quadWord( head, w ) >> sh ) & 0xFFU;
+                        shiftQuadBelow( head, w, sh, front );
                     }
-                    shiftQuadBelow( last, w, sh, carry );
-                    my[Q * STRIDE] = last;
+                } else {
+                    /* entry j of M: in row j / 16 or, when the holes in front of it add up, the row behind */
+                    const uint32_t j = idx - f;
+                    const uint32_t r0 = j >> 4;
+                    const bool low = r0 < 8U;
+                    const uint32_t window = __funnelshift_r( low ? beforeLo : beforeHi, low ? beforeHi : 0U, 4U * r0 );
+                    const uint32_t liveBeforeNext = 16U * ( r0 + 1U ) - ( ( window >> 4 ) & 15U );
+                    const bool next = j >= liveBeforeNext;
+                    const uint32_t row = r0 + ( next ? 1U : 0U );
+                    const uint32_t p = j - ( next ? liveBeforeNext : 16U * r0 - ( window & 15U ) );   /* 0..15 */
+                    uint32_t* const rowPtr = my + row * ( 4U * STRIDE );
+                    const uint32_t x0 = rowPtr[0];
+                    const uint32_t x1 = rowPtr[STRIDE];
+                    const uint32_t x2 = rowPtr[2U * STRIDE];
+                    const uint32_t x3 = rowPtr[3U * STRIDE];
+                    const uint32_t w = p >> 2;
+                    const uint32_t c = p & 3U;
+                    const uint32_t xw = w == 0 ? x0 : ( w == 1 ? x1 : ( w == 2 ? x2 : x3 ) );
+                    front = __byte_perm( xw, 0U, 0x4440U | c );
+                    /* the entries behind p move down by one: a word in front of p's stays, p's own drops byte c, the
+                     * words behind take one byte from their successor */
+                    const uint32_t selMixed = 0x4321U - ( 0x1111U & ( ( 1U << ( 4U * c ) ) - 1U ) );
+                    rowPtr[0] = __byte_perm( x0, x1, w == 0 ? selMixed : 0x3210U );
+                    rowPtr[STRIDE] = __byte_perm( x1, x2, w > 1U ? 0x3210U : ( w == 1U ? selMixed : 0x4321U ) );
+                    rowPtr[2U * STRIDE] = __byte_perm( x2, x3, w > 2U ? 0x3210U : ( w == 2U ? selMixed : 0x4321U ) );
+                    rowPtr[3U * STRIDE] = __byte_perm( x3, 0U, w == 3U ? selMixed : 0x4321U );
+                    /* one more hole in front of every row behind this one */
+                    const uint32_t s = 4U * ( row + 1U );   /* 4..64 */
+                    beforeLo += s < 32U ? ( 0x11111111U << ( s & 31U ) ) : 0U;
+                    beforeHi += s < 32U ? 0x11111111U : ( s < 64U ? ( 0x11111111U << ( s & 31U ) ) : 0U );
+                    shiftQuad( head, front );
+                    ++f;
                 }
             }
-            out[k >> 2] |= o << ( 8U * ( k & 3U ) );
+            out[k >> 2] |= front << ( 8U * ( k & 3U ) );
+            if ( ( k & 1U ) == 1U ) {
+                if ( __any_sync( FULL, f >= MTF_MERGE_AT ) ) {
+                    merge();
+                }
+            }
         }
-        sym8[( base >> 2 ) + 0U] = out[0];
-        sym8[( base >> 2 ) + 1U] = out[1];
+        if ( base < count ) {
+            sym8[( base >> 2 ) + 0U] = out[0];
+            sym8[( base >> 2 ) + 1U] = out[1];
+        }
     }
+    merge();
 
-    *ckpt = ChunkCheckpoint{ produced, runShift | ( longRun ? LONG_RUN_FLAG : 0U ) };
-    listOut[0] = head;
-#pragma unroll 5
-    for ( uint32_t q = 1; q < 16U; ++q ) {
-        listOut[q] = my[q * STRIDE];
+    if ( count > 0 ) {
+        *ckpt = ChunkCheckpoint{ produced, runShift | ( longRun ? LONG_RUN_FLAG : 0U ) };
+#pragma unroll 4
+        for ( uint32_t q = 0; q < 16U; ++q ) {
+            listOut[q] = make_uint4( my[( 4U * q ) * STRIDE], my[( 4U * q + 1U ) * STRIDE], my[( 4U * q + 2U ) * STRIDE],
+                                     my[( 4U * q + 3U ) * STRIDE] );
+        }
     }
 }
 

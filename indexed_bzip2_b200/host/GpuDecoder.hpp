@@ -59,7 +59,9 @@ throwForStatus( const ibz2_block_result& r )
     case IBZ2_ST_CODE_LENGTHS:
         throw std::domain_error( "Constructing a Huffman coding from the given code length sequence failed!" );
     case IBZ2_ST_SELECTOR_OVERRUN:
-        throw std::domain_error( "[BZip2 block data] selector out of maximum range" );
+        /* n_symbols carries the block's selector count for this status: the loop stops at selector == count */
+        msg << "[BZip2 block data] selector " << r.n_symbols << " out of maximum range " << r.n_symbols;
+        throw std::domain_error( msg.str() );
     case IBZ2_ST_DBUF_OVERFLOW:
         throw std::domain_error( "[BZip2 block data] dbufCount exceeds dbufSize" );
     case IBZ2_ST_INVALID_CODE:
