@@ -155,6 +155,10 @@ int ibz2_host_alloc_pinned( ibz2_ctx* ctx, uint64_t nbytes, void** hptr );
 int ibz2_host_free_pinned( ibz2_ctx* ctx, void* hptr );
 int ibz2_memcpy_h2d( ibz2_ctx* ctx, void* dptr, const void* hptr, uint64_t nbytes );
 int ibz2_memcpy_d2h( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbytes );
+/* the same as ibz2_memcpy_h2d for PAGEABLE host memory (a memory-mapped file): host threads copy into two pinned staging
+ * buffers that the copy engine empties in turn.  Stands where the reference reads the file through its SharedFileReader
+ * (core/filereader/Shared.hpp:267-300): the compressed file goes to the GPU once, when a reader opens it. */
+int ibz2_upload_pageable( ibz2_ctx* ctx, void* dptr, const void* hptr, uint64_t nbytes );
 int ibz2_synchronize( ibz2_ctx* ctx );
 
 /* ---- K1: magic finder ----
@@ -187,6 +191,36 @@ int ibz2_decode_buffer( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int da
                         void* out, uint64_t out_capacity, int out_mem,
                         ibz2_block_result* results, uint64_t results_capacity, uint64_t* nblocks,
                         uint64_t* total_out );
+
+/* ---- one file on several GPUs of one machine, in one process ----
+ * Stands in for the pool of decode threads inside ONE reference reader object (indexed_bzip2/ParallelBZ2Reader.hpp:50-69,
+ * core/BlockFetcher.hpp:176-190), with devices where the reference has threads: the compressed stream is cut into equal
+ * byte ranges, device i finds and decodes the blocks whose magic starts in range i (one host thread and one ibz2_ctx per
+ * device), the byte counts of the devices are scanned on the host and every device copies its bytes to its place in the
+ * caller's ONE output buffer.  No collective: blocks are independent.  Block results come back in file order with
+ * file-relative enc_offset_bits / out_offset, and the stream CRCs are folded over all of them (ibz2_fold_stream_crcs,
+ * verdict included).  `devices` may name one device several times (two contexts on one GPU: how the tests run it). */
+typedef struct ibz2_multi ibz2_multi;
+typedef struct ibz2_multi_timings {
+    float decode_ms;  /* wall clock: until the slowest device has decoded its share into its own memory */
+    float copy_ms;    /* wall clock: the device -> host copies to the caller's buffer, all devices at once */
+    float total_ms;   /* wall clock of the call */
+    float reserved;
+    uint64_t stream_crc_mismatches;
+} ibz2_multi_timings;
+int ibz2_multi_create( const int* devices, int ndevices, ibz2_multi** multi );
+void ibz2_multi_destroy( ibz2_multi* multi );
+const char* ibz2_multi_last_error( const ibz2_multi* multi );
+int ibz2_multi_device_count( const ibz2_multi* multi );
+/* pinned host memory that every device of the set can copy into (cudaHostAllocPortable) */
+int ibz2_multi_host_alloc_pinned( ibz2_multi* multi, uint64_t nbytes, void** hptr );
+int ibz2_multi_host_free_pinned( ibz2_multi* multi, void* hptr );
+/* data, out, results: HOST memory (pinned for full PCIe speed).  Otherwise like ibz2_decode_buffer( 0, UINT64_MAX ). */
+int ibz2_multi_decode_buffer( ibz2_multi* multi, const void* data, uint64_t nbytes, void* out, uint64_t out_capacity,
+                              ibz2_block_result* results, uint64_t results_capacity, uint64_t* nblocks,
+                              uint64_t* total_out );
+/* of the last call; per_device: `capacity` entries, one ibz2_timings per device in the order given to create */
+int ibz2_multi_get_timings( const ibz2_multi* multi, ibz2_multi_timings* timings, ibz2_timings* per_device, int capacity );
 
 /* CUDA-event stopwatch on the context's stream: brackets any number of calls (device time, not wall clock). */
 int ibz2_timer_start( ibz2_ctx* ctx );

@@ -60,6 +60,11 @@ class Timings(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class MultiTimings(C.Structure):
+    _fields_ = [("decode_ms", C.c_float), ("copy_ms", C.c_float), ("total_ms", C.c_float), ("reserved", C.c_float),
+                ("stream_crc_mismatches", C.c_uint64)]
+
+
 class Ibz2Error(RuntimeError):
     def __init__(self, rc: int, message: str):
         super().__init__(f"ibz2 error {RC_NAMES.get(rc, rc)}: {message}")
@@ -72,6 +77,8 @@ EXPORTS = [
     "ibz2_host_free_pinned", "ibz2_memcpy_h2d", "ibz2_memcpy_d2h", "ibz2_synchronize", "ibz2_find_magics",
     "ibz2_decode_blocks", "ibz2_decode_buffer", "ibz2_timer_start", "ibz2_timer_stop", "ibz2_debug_decode_block", "ibz2_read_stream_header", "ibz2_read_block_header",
     "ibz2_stream_crc_fold", "ibz2_set_verify_stream_crc", "ibz2_fold_stream_crcs",
+    "ibz2_upload_pageable", "ibz2_multi_create", "ibz2_multi_destroy", "ibz2_multi_last_error", "ibz2_multi_device_count",
+    "ibz2_multi_host_alloc_pinned", "ibz2_multi_host_free_pinned", "ibz2_multi_decode_buffer", "ibz2_multi_get_timings",
 ]
 
 _lib = None
@@ -136,6 +143,24 @@ def load_library() -> C.CDLL:
     L.ibz2_set_verify_stream_crc.argtypes = [vp, i32]
     L.ibz2_fold_stream_crcs.restype = u64
     L.ibz2_fold_stream_crcs.argtypes = [vp, u64, i32]
+    L.ibz2_upload_pageable.restype = i32
+    L.ibz2_upload_pageable.argtypes = [vp, vp, vp, u64]
+    L.ibz2_multi_create.restype = i32
+    L.ibz2_multi_create.argtypes = [C.POINTER(i32), i32, C.POINTER(vp)]
+    L.ibz2_multi_destroy.restype = None
+    L.ibz2_multi_destroy.argtypes = [vp]
+    L.ibz2_multi_last_error.restype = C.c_char_p
+    L.ibz2_multi_last_error.argtypes = [vp]
+    L.ibz2_multi_device_count.restype = i32
+    L.ibz2_multi_device_count.argtypes = [vp]
+    L.ibz2_multi_host_alloc_pinned.restype = i32
+    L.ibz2_multi_host_alloc_pinned.argtypes = [vp, u64, C.POINTER(vp)]
+    L.ibz2_multi_host_free_pinned.restype = i32
+    L.ibz2_multi_host_free_pinned.argtypes = [vp, vp]
+    L.ibz2_multi_decode_buffer.restype = i32
+    L.ibz2_multi_decode_buffer.argtypes = [vp, vp, u64, vp, u64, vp, u64, C.POINTER(u64), C.POINTER(u64)]
+    L.ibz2_multi_get_timings.restype = i32
+    L.ibz2_multi_get_timings.argtypes = [vp, C.POINTER(MultiTimings), C.POINTER(Timings), i32]
     if L.ibz2_abi_version() != 3:
         raise ImportError("libibz2_cuda.so has an unexpected ABI version")
     _lib = L
@@ -356,6 +381,69 @@ def read_block_header(data, bit_offset: int) -> BlockResult:
 
 def stream_crc_fold(stream_crc: int, block_crc: int) -> int:
     return int(load_library().ibz2_stream_crc_fold(stream_crc, block_crc))
+
+
+class MultiContext:
+    """ibz2_multi_*: one file decoded by several devices (or several contexts on one device) into ONE host buffer."""
+
+    def __init__(self, devices):
+        self.lib = load_library()
+        self.devices = [int(d) for d in devices]
+        handle = C.c_void_p()
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        rc = self.lib.ibz2_multi_create(arr, len(self.devices), C.byref(handle))
+        if rc != 0:
+            raise Ibz2Error(rc, (self.lib.ibz2_multi_last_error(None) or b"").decode())
+        self.handle = handle
+
+    def close(self):
+        if self.handle:
+            self.lib.ibz2_multi_destroy(self.handle)
+            self.handle = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise Ibz2Error(rc, (self.lib.ibz2_multi_last_error(self.handle) or b"").decode())
+
+    def pinned(self, nbytes: int) -> np.ndarray:
+        ptr = C.c_void_p()
+        self._check(self.lib.ibz2_multi_host_alloc_pinned(self.handle, nbytes, C.byref(ptr)))
+        self._pinned = getattr(self, "_pinned", []) + [ptr.value]
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(max(1, nbytes),))[:nbytes]
+
+    def free_pinned(self):
+        for ptr in getattr(self, "_pinned", []):
+            self.lib.ibz2_multi_host_free_pinned(self.handle, ptr)
+        self._pinned = []
+
+    def decode_buffer(self, data, out: np.ndarray | None, max_blocks: int | None = None):
+        a = as_u8(data)
+        capacity = max_blocks if max_blocks is not None else max(1024, a.size // 4096)
+        while True:
+            results = np.zeros(capacity, dtype=BLOCK_RESULT_DTYPE)
+            nblocks, total = C.c_uint64(), C.c_uint64()
+            rc = self.lib.ibz2_multi_decode_buffer(self.handle, a.ctypes.data, a.size,
+                                                   out.ctypes.data if out is not None else None,
+                                                   out.size if out is not None else 0, results.ctypes.data, capacity,
+                                                   C.byref(nblocks), C.byref(total))
+            if rc == 4 and nblocks.value > capacity:
+                capacity = int(nblocks.value)
+                continue
+            self._check(rc)
+            return results[:nblocks.value], int(total.value)
+
+    def timings(self) -> dict:
+        t = MultiTimings()
+        per = (Timings * len(self.devices))()
+        self._check(self.lib.ibz2_multi_get_timings(self.handle, C.byref(t), per, len(self.devices)))
+        return {"decode_ms": t.decode_ms, "copy_ms": t.copy_ms, "total_ms": t.total_ms,
+                "stream_crc_mismatches": int(t.stream_crc_mismatches), "devices": [p.as_dict() for p in per]}
 
 
 def fold_stream_crcs(results: np.ndarray, verify: bool = True) -> int:

@@ -22,7 +22,7 @@ HOST_LIB = PKG / "libibz2_host.so"     # C++ readers + flat C entry points for t
 CLI = PKG / "bin" / "ibzip2"           # command-line tool
 HOST_FLAGS = ["-std=c++17", "-O2", "-g", "-fPIC", "-Wall", "-Wextra", "-pthread", "-rdynamic"]
 
-CUDA_SOURCES = ["blockfinder.cu", "huffman_header.cu", "huffman_bits.cu", "huffman_careful.cu", "mtf.cu", "bwt_prepare.cu", "bwt_traverse.cu", "rle.cu", "crc.cu", "capi.cu"]
+CUDA_SOURCES = ["blockfinder.cu", "huffman_header.cu", "huffman_bits.cu", "huffman_careful.cu", "mtf.cu", "bwt_prepare.cu", "bwt_traverse.cu", "rle.cu", "crc.cu", "capi.cu", "multi.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

@@ -93,7 +93,9 @@ shiftQuadBelow( uint4& q, uint32_t w, uint32_t sh, uint32_t in )
 __global__ void __launch_bounds__( MTFC_THREADS )
 mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scratchAll )
 {
-    __shared__ uint32_t rows[64][MTFC_THREADS];   /* word 4 r + k of a lane's list = entries 16 r + 4 k .. + 3 of M */
+    /* word 4 r + k of a lane's list = entries 16 r + 4 k .. + 3 of M; eight more words because a step reads the four words
+     * from the one that holds its entry on, and a merge writes whole groups of four at its output position */
+    __shared__ uint32_t rows[72][MTFC_THREADS];
 
     const uint32_t block = blockIdx.y;
     const BlockMeta& bm = meta[block];
@@ -123,7 +125,7 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
         }
     }
     const uint32_t runShift = runDigits;
-    bool longRun = runDigits > MAX_RUN_DIGITS;
+    uint32_t mostDigits = runDigits;
     uint32_t produced = 0;   /* bytes of L the chunk's symbols stand for */
 
     uint32_t* const my = &rows[0][threadIdx.x];
@@ -182,20 +184,14 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
             const uint32_t y4 = __byte_perm( s3, 0U, selB );
             const uint32_t total = carryBytes + live;   /* <= 3 + 16 */
             const uint32_t full = total >> 2;
-            if ( full > 0U ) {
-                out[0] = y0;
-            }
-            if ( full > 1U ) {
-                out[STRIDE] = y1;
-            }
-            if ( full > 2U ) {
-                out[2U * STRIDE] = y2;
-            }
-            if ( full > 3U ) {
-                out[3U * STRIDE] = y3;
-            }
+            /* all four words go out; the ones behind the `full` complete ones are overwritten by the next source, and the
+             * first of them is this source's carry (the reads are a row ahead, the writes stay inside that row) */
+            out[0] = y0;
+            out[STRIDE] = y1;
+            out[2U * STRIDE] = y2;
+            out[3U * STRIDE] = y3;
             out += full * STRIDE;
-            carry = full == 0U ? y0 : ( full == 1U ? y1 : ( full == 2U ? y2 : ( full == 3U ? y3 : y4 ) ) );
+            carry = full == 4U ? y4 : out[0];
             carryBytes = total & 3U;
             s0 = n0;
             s1 = n1;
@@ -218,10 +214,12 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
             const uint32_t sym = ( packed[k >> 1] >> ( 16U * ( k & 1U ) ) ) & 0xFFFFU;
             const bool valid = base + k < count;
             if ( valid ) {
+                /* a number of more than 20 digits sends the block to the exact decoder whatever `produced` says, so the
+                 * shift may simply run out (clamped funnel shift: 0 from 32 digits on) */
                 const bool isRun = sym <= 1U;
-                produced += isRun ? ( ( sym + 1U ) << min( runDigits, MAX_RUN_DIGITS ) ) : 1U;
+                produced += isRun ? __funnelshift_lc( 0U, sym + 1U, runDigits ) : 1U;
                 runDigits = isRun ? runDigits + 1U : 0U;
-                longRun = longRun || ( runDigits > MAX_RUN_DIGITS );
+                mostDigits = max( mostDigits, runDigits );
             }
             if ( ( sym >= 2U ) && valid ) {
                 const uint32_t idx = sym - 1U;   /* 1..255 */
@@ -247,22 +245,27 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
                     const bool next = j >= liveBeforeNext;
                     const uint32_t row = r0 + ( next ? 1U : 0U );
                     const uint32_t p = j - ( next ? liveBeforeNext : 16U * r0 - ( window & 15U ) );   /* 0..15 */
-                    uint32_t* const rowPtr = my + row * ( 4U * STRIDE );
-                    const uint32_t x0 = rowPtr[0];
-                    const uint32_t x1 = rowPtr[STRIDE];
-                    const uint32_t x2 = rowPtr[2U * STRIDE];
-                    const uint32_t x3 = rowPtr[3U * STRIDE];
+                    /* the four words from the one that holds entry p on (they may reach into the next row: read, never
+                     * written back).  Entry p leaves; what is behind it in the row moves down by one. */
                     const uint32_t w = p >> 2;
                     const uint32_t c = p & 3U;
-                    const uint32_t xw = w == 0 ? x0 : ( w == 1 ? x1 : ( w == 2 ? x2 : x3 ) );
-                    front = __byte_perm( xw, 0U, 0x4440U | c );
-                    /* the entries behind p move down by one: a word in front of p's stays, p's own drops byte c, the
-                     * words behind take one byte from their successor */
-                    const uint32_t selMixed = 0x4321U - ( 0x1111U & ( ( 1U << ( 4U * c ) ) - 1U ) );
-                    rowPtr[0] = __byte_perm( x0, x1, w == 0 ? selMixed : 0x3210U );
-                    rowPtr[STRIDE] = __byte_perm( x1, x2, w > 1U ? 0x3210U : ( w == 1U ? selMixed : 0x4321U ) );
-                    rowPtr[2U * STRIDE] = __byte_perm( x2, x3, w > 2U ? 0x3210U : ( w == 2U ? selMixed : 0x4321U ) );
-                    rowPtr[3U * STRIDE] = __byte_perm( x3, 0U, w == 3U ? selMixed : 0x4321U );
+                    uint32_t* const wordPtr = my + ( row * 4U + w ) * STRIDE;
+                    const uint32_t x0 = wordPtr[0];
+                    const uint32_t x1 = wordPtr[STRIDE];
+                    const uint32_t x2 = wordPtr[2U * STRIDE];
+                    const uint32_t x3 = wordPtr[3U * STRIDE];
+                    front = __byte_perm( x0, 0U, 0x4440U | c );
+                    const uint32_t selMixed = 0x4321U - ( 0x1111U & ( ( 1U << ( 4U * c ) ) - 1U ) );   /* drops byte c */
+                    wordPtr[0] = __byte_perm( x0, x1, selMixed );
+                    if ( w < 3U ) {
+                        wordPtr[STRIDE] = __byte_perm( x1, x2, 0x4321U );
+                    }
+                    if ( w < 2U ) {
+                        wordPtr[2U * STRIDE] = __byte_perm( x2, x3, 0x4321U );
+                    }
+                    if ( w < 1U ) {
+                        wordPtr[3U * STRIDE] = x3 >> 8;
+                    }
                     /* one more hole in front of every row behind this one */
                     const uint32_t s = 4U * ( row + 1U );   /* 4..64 */
                     beforeLo += s < 32U ? ( 0x11111111U << ( s & 31U ) ) : 0U;
@@ -286,7 +289,7 @@ mtfChunkKernel( const BlockMeta* __restrict__ meta, uint32_t* __restrict__ scrat
     merge();
 
     if ( count > 0 ) {
-        *ckpt = ChunkCheckpoint{ produced, runShift | ( longRun ? LONG_RUN_FLAG : 0U ) };
+        *ckpt = ChunkCheckpoint{ produced, runShift | ( mostDigits > MAX_RUN_DIGITS ? LONG_RUN_FLAG : 0U ) };
 #pragma unroll 4
         for ( uint32_t q = 0; q < 16U; ++q ) {
             listOut[q] = make_uint4( my[( 4U * q ) * STRIDE], my[( 4U * q + 1U ) * STRIDE], my[( 4U * q + 2U ) * STRIDE],

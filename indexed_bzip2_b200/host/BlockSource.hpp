@@ -1,19 +1,34 @@
 /*
  * BlockSource -- "give me the decoded block that starts at this bit offset" for both readers: the compressed file
- * (host copy for header probes, device copy for decoding), the finder's list of data-block offsets and the batch of
- * blocks decoded last.  It replaces the reference's BlockFetcher + cache + prefetcher
- * (core/BlockFetcher.hpp:244-317, core/Cache.hpp, core/Prefetcher.hpp) with the policy a GPU wants:
- * a miss decodes the wanted block AND the blocks behind it in one call; consecutive misses in file order double the
- * batch up to MAX_BATCH_BLOCKS, any other access pattern starts again from MIN_BATCH_BLOCKS.
+ * (memory-mapped on the host for the header probes, in HBM for decoding), the finder's list of data-block offsets and
+ * a cache of decoded batches.  It stands where the reference has BlockFetcher + Cache + Prefetcher
+ * (core/BlockFetcher.hpp:244-317 and :446-559, core/Cache.hpp:122-297, core/Prefetcher.hpp:82-223), with the policy a
+ * GPU wants:
+ *   - the unit of work is a BATCH of consecutive blocks decoded by one ibz2_decode_blocks call (the GPU needs thousands
+ *     of blocks in flight; one block alone costs as long as its sequential Huffman chain);
+ *   - prefetching = batch size.  Like FetchNextAdaptive (Prefetcher.hpp:159-176) nothing is prefetched on random
+ *     access and more and more on consecutive access: every miss that continues where the last batch ended decodes
+ *     eight times as many blocks as the one before, up to MAX_BATCH_BLOCKS; any other access starts small again.  A
+ *     caller that knows how far its read reaches (block map complete) says so, and the blocks of ONE read are decoded
+ *     by ONE call;
+ *   - decoded batches stay in a least-recently-used cache (the reference keeps max(16, P) blocks + 2 P prefetched
+ *     ones, BlockFetcher.hpp:180-182; here up to MAX_CACHED_BATCHES batches inside a byte budget), each in its own
+ *     pinned host buffer; the buffers of evicted batches are reused.
+ * The file is not read into a private copy: paths and descriptors are memory-mapped, and the mapping goes to the GPU
+ * through pinned staging buffers (ibz2_upload_pageable).  It must fit in HBM next to the decode scratch.
  */
 #pragma once
 
 #include <algorithm>
+#include <cstdlib>
 #include <limits>
+#include <list>
 #include <memory>
 #include <optional>
 #include <unordered_map>
 #include <vector>
+
+#include <sys/mman.h>
 
 #include "FileReader.hpp"
 #include "GpuDecoder.hpp"
@@ -24,7 +39,10 @@ class BlockSource
 {
 public:
     static constexpr size_t MIN_BATCH_BLOCKS = 4;
-    static constexpr size_t MAX_BATCH_BLOCKS = 2048;
+    static constexpr size_t MAX_BATCH_BLOCKS = 4096;      /* 3.7 GB of decoded bytes at 900 kB blocks */
+    static constexpr size_t BATCH_GROWTH_SHIFT = 3;       /* consecutive misses: 4, 32, 256, 2048, 4096 blocks */
+    static constexpr size_t MAX_CACHED_BATCHES = 16;
+    static constexpr size_t DEFAULT_CACHE_BYTES = 6ULL << 30;
 
     BlockSource( UniqueFileReader fileReader, size_t parallelization, int device ) :
         m_parallelization( parallelization ),
@@ -33,35 +51,70 @@ public:
         if ( !fileReader ) {
             throw std::invalid_argument( "A file reader is required!" );
         }
+        if ( const char* const env = std::getenv( "IBZ2_CACHE_BYTES" ); env != nullptr ) {
+            m_cacheBudget = std::max<size_t>( 1, std::strtoull( env, nullptr, 10 ) );
+        }
         if ( auto* memory = dynamic_cast<MemoryFileReader*>( fileReader.get() ); memory != nullptr ) {
-            m_file = std::move( memory->bytes() );
+            m_owned = std::move( memory->bytes() );
+            m_data = m_owned.data();
+            m_size = m_owned.size();
             return;
         }
+        if ( auto* standard = dynamic_cast<StandardFileReader*>( fileReader.get() );
+             ( standard != nullptr ) && standard->seekable() ) {
+            /* a regular file: mapped, not copied (the reference shares one descriptor between its threads instead,
+             * core/filereader/Shared.hpp:267-300) */
+            m_size = standard->size().value_or( 0 );
+            if ( m_size == 0 ) {
+                return;
+            }
+            void* const mapping = ::mmap( nullptr, m_size, PROT_READ, MAP_SHARED, standard->fileno(), 0 );
+            if ( mapping != MAP_FAILED ) {
+                m_mapping = mapping;
+                m_data = static_cast<const uint8_t*>( mapping );
+                ::madvise( mapping, m_size, MADV_SEQUENTIAL );
+                return;
+            }
+            m_size = 0;   /* fall through: read it */
+        }
         if ( fileReader->seekable() ) {
-            m_file.resize( fileReader->size().value_or( 0 ) );
+            m_owned.resize( fileReader->size().value_or( 0 ) );
             fileReader->seek( 0 );
         }
-        /* non-seekable input (stdin) is read to its end in growing steps */
+        /* anything else (a pipe) is read to its end in growing steps */
         size_t done = 0;
         while ( true ) {
-            if ( done == m_file.size() ) {
+            if ( done == m_owned.size() ) {
                 if ( fileReader->seekable() ) {
                     break;
                 }
-                m_file.resize( std::max<size_t>( 1U << 20, m_file.size() * 2 ) );
+                m_owned.resize( std::max<size_t>( 1U << 20, m_owned.size() * 2 ) );
             }
-            const size_t n = fileReader->read( reinterpret_cast<char*>( m_file.data() ) + done, m_file.size() - done );
+            const size_t n = fileReader->read( reinterpret_cast<char*>( m_owned.data() ) + done, m_owned.size() - done );
             if ( n == 0 ) {
                 break;
             }
             done += n;
         }
-        m_file.resize( done );
+        m_owned.resize( done );
+        m_data = m_owned.data();
+        m_size = m_owned.size();
     }
 
-    [[nodiscard]] const uint8_t* fileData() const { return m_file.data(); }
-    [[nodiscard]] size_t fileSize() const { return m_file.size(); }
-    [[nodiscard]] size_t fileSizeInBits() const { return m_file.size() * 8U; }
+    ~BlockSource()
+    {
+        close();
+        if ( m_mapping != nullptr ) {
+            ::munmap( m_mapping, m_size );
+        }
+    }
+
+    BlockSource( const BlockSource& ) = delete;
+    BlockSource& operator=( const BlockSource& ) = delete;
+
+    [[nodiscard]] const uint8_t* fileData() const { return m_data; }
+    [[nodiscard]] size_t fileSize() const { return m_size; }
+    [[nodiscard]] size_t fileSizeInBits() const { return m_size * 8U; }
 
     /** rapidgzip::BlockFinder: every data-block magic of the file, ascending, found once by K1. */
     const std::vector<uint64_t>&
@@ -97,18 +150,26 @@ public:
         dropBatch();
     }
 
+    /** Forgets every decoded block (their pinned buffers stay for reuse). */
     void
     dropBatch()
     {
-        m_results.clear();
-        m_byOffset.clear();
-        m_data = nullptr;
+        while ( !m_batches.empty() ) {
+            evictOldest();
+        }
     }
 
     void
     noteSeek()
     {
         m_sequentialFetches = 0;
+    }
+
+    /** The caller's next fetches will ask for this many consecutive data blocks (0: unknown). */
+    void
+    expectBlocks( size_t count )
+    {
+        m_expected = count;
     }
 
     struct Block
@@ -121,13 +182,18 @@ public:
      * The decoded block at @p encodedOffset; throws what the reference's decoder would have thrown for it.
      * @p finderIndex is the block's index in the finder list when the caller knows it.  An offset the finder does
      * not list (possible for the serial reader on odd files) is decoded on its own.
+     * The returned pointers stay valid until the next fetch.
      */
     Block
     fetch( uint64_t encodedOffset, std::optional<size_t> finderIndex = std::nullopt )
     {
         if ( const auto cached = m_byOffset.find( encodedOffset ); cached != m_byOffset.end() ) {
-            return checked( cached->second );
+            /* Cache::get moves a hit to the young end (core/Cache.hpp:160-178) */
+            m_batches.splice( m_batches.begin(), m_batches, cached->second.first );
+            ++m_hits;
+            return checked( *cached->second.first, cached->second.second );
         }
+        ++m_misses;
 
         const auto& offsets = finderOffsets();
         std::vector<uint64_t> single;
@@ -144,32 +210,47 @@ public:
             const bool sequential = first == m_nextSequentialBlock;
             m_sequentialFetches = sequential ? m_sequentialFetches + 1 : 0;
             const size_t floor = std::max<size_t>( MIN_BATCH_BLOCKS, std::min<size_t>( m_parallelization, 64 ) );
-            const size_t wanted = std::min<size_t>( MAX_BATCH_BLOCKS, floor << std::min<size_t>( m_sequentialFetches, 12 ) );
+            const size_t grown = floor << std::min<size_t>( BATCH_GROWTH_SHIFT * m_sequentialFetches, 20 );
+            /* a read whose extent is known decodes what it needs in one call, and no more than that on random access */
+            const size_t wanted = ( m_expected > 0 ) && !sequential ? m_expected : std::max( grown, m_expected );
             const size_t limit = finderCount();
-            count = std::min( wanted, limit > first ? limit - first : 1 );
+            count = std::min( std::min<size_t>( wanted, MAX_BATCH_BLOCKS ), limit > first ? limit - first : 1 );
+            /* stop in front of a block that is cached already */
+            for ( size_t i = 1; i < count; ++i ) {
+                if ( m_byOffset.count( offsets[first + i] ) != 0 ) {
+                    count = i;
+                    break;
+                }
+            }
             m_nextSequentialBlock = first + count;
             batchOffsets = offsets.data() + first;
         } else {
             single.push_back( encodedOffset );
             batchOffsets = single.data();
         }
+        m_expected = 0;
 
-        dropBatch();
-        uint8_t* data = nullptr;
-        size_t dataSize = 0;
-        gpu().decode( batchOffsets, count, m_results, data, dataSize );
-        m_data = data;
-        for ( size_t i = 0; i < m_results.size(); ++i ) {
-            m_byOffset.emplace( m_results[i].enc_offset_bits, i );
+        Batch batch;
+        batch.buffer = takeBuffer( count * 1000000ULL + 65536ULL );
+        gpu().decode( batchOffsets, count, batch.results, batch.buffer );
+        batch.bytes = batch.buffer.capacity;
+        m_batches.push_front( std::move( batch ) );
+        const auto inserted = m_batches.begin();
+        for ( size_t i = 0; i < inserted->results.size(); ++i ) {
+            m_byOffset[inserted->results[i].enc_offset_bits] = { inserted, i };
         }
-        return checked( m_byOffset.at( encodedOffset ) );
+        m_cachedBytes += inserted->bytes;
+        while ( ( m_batches.size() > 1 ) && ( ( m_batches.size() > MAX_CACHED_BATCHES ) || ( m_cachedBytes > m_cacheBudget ) ) ) {
+            evictOldest();
+        }
+        return checked( *inserted, m_byOffset.at( encodedOffset ).second );
     }
 
     /** BZ2BlockFetcher::readBlockHeader (BZ2BlockFetcher.hpp:64-82): magic, CRC and EOS padding only. */
     [[nodiscard]] ibz2_block_result
     probeHeader( uint64_t bitOffset ) const
     {
-        return GpuDecoder::probeHeader( m_file.data(), m_file.size(), bitOffset );
+        return GpuDecoder::probeHeader( m_data, m_size, bitOffset );
     }
 
     GpuDecoder&
@@ -177,7 +258,7 @@ public:
     {
         if ( !m_gpu ) {
             m_gpu = std::make_unique<GpuDecoder>( m_device );
-            m_gpu->upload( m_file.data(), m_file.size() );
+            m_gpu->upload( m_data, m_size );
         }
         return *m_gpu;
     }
@@ -186,15 +267,36 @@ public:
     close()
     {
         dropBatch();
+        if ( m_gpu ) {
+            for ( auto& buffer : m_freeBuffers ) {
+                m_gpu->freePinned( buffer );
+            }
+        }
+        m_freeBuffers.clear();
         m_gpu.reset();
     }
 
-private:
-    /** A block that failed to decode throws where the reference's worker exception would surface: on access. */
-    Block
-    checked( size_t i ) const
+    /** cache statistics like BlockFetcher::statistics() (core/BlockFetcher.hpp:62-126): hits, misses */
+    [[nodiscard]] std::pair<size_t, size_t>
+    cacheStatistics() const
     {
-        const auto& r = m_results[i];
+        return { m_hits, m_misses };
+    }
+
+private:
+    struct Batch
+    {
+        std::vector<ibz2_block_result> results;
+        GpuDecoder::PinnedBuffer buffer;
+        size_t bytes{ 0 };
+    };
+    using BatchList = std::list<Batch>;
+
+    /** A block that failed to decode throws where the reference's worker exception would surface: on access. */
+    static Block
+    checked( const Batch& batch, size_t i )
+    {
+        const auto& r = batch.results[i];
         if ( ( r.status == IBZ2_ST_OK ) && ( r.is_eos == 0 ) && ( r.calculated_crc != r.expected_crc ) ) {
             ibz2_block_result failed = r;
             failed.status = IBZ2_ST_CRC;
@@ -203,10 +305,57 @@ private:
         if ( r.status != IBZ2_ST_OK ) {
             throwForStatus( r );
         }
-        return Block{ &r, m_data + r.out_offset };
+        return Block{ &r, static_cast<const uint8_t*>( batch.buffer.data ) + r.out_offset };
     }
 
-    std::vector<uint8_t> m_file;
+    void
+    evictOldest()
+    {
+        auto& oldest = m_batches.back();
+        for ( const auto& r : oldest.results ) {
+            const auto entry = m_byOffset.find( r.enc_offset_bits );
+            if ( ( entry != m_byOffset.end() ) && ( &*entry->second.first == &oldest ) ) {
+                m_byOffset.erase( entry );
+            }
+        }
+        m_cachedBytes -= std::min( m_cachedBytes, oldest.bytes );
+        if ( oldest.buffer.data != nullptr ) {
+            m_freeBuffers.push_back( oldest.buffer );
+        }
+        m_batches.pop_back();
+        /* a few spare buffers are worth keeping (pinning memory is slow), the largest ones first */
+        if ( m_freeBuffers.size() > 4 ) {
+            const auto smallest = std::min_element( m_freeBuffers.begin(), m_freeBuffers.end(),
+                                                    [] ( const auto& a, const auto& b ) { return a.capacity < b.capacity; } );
+            gpu().freePinned( *smallest );
+            m_freeBuffers.erase( smallest );
+        }
+    }
+
+    /** The smallest spare buffer that is large enough, else a new one. */
+    GpuDecoder::PinnedBuffer
+    takeBuffer( size_t capacity )
+    {
+        auto best = m_freeBuffers.end();
+        for ( auto it = m_freeBuffers.begin(); it != m_freeBuffers.end(); ++it ) {
+            if ( ( it->capacity >= capacity ) && ( ( best == m_freeBuffers.end() ) || ( it->capacity < best->capacity ) ) ) {
+                best = it;
+            }
+        }
+        if ( best != m_freeBuffers.end() ) {
+            const auto buffer = *best;
+            m_freeBuffers.erase( best );
+            return buffer;
+        }
+        return gpu().allocPinned( capacity );
+    }
+
+    /* the compressed file on the host: a mapping, or bytes this object owns */
+    const uint8_t* m_data{ nullptr };
+    size_t m_size{ 0 };
+    void* m_mapping{ nullptr };
+    std::vector<uint8_t> m_owned;
+
     const size_t m_parallelization;
     const int m_device;
     std::unique_ptr<GpuDecoder> m_gpu;
@@ -215,10 +364,15 @@ private:
     bool m_finderReady{ false };
     size_t m_finderLimit{ std::numeric_limits<size_t>::max() };
 
-    std::vector<ibz2_block_result> m_results;
-    std::unordered_map<uint64_t, size_t> m_byOffset;
-    const uint8_t* m_data{ nullptr };
+    BatchList m_batches;   /* youngest first */
+    std::unordered_map<uint64_t, std::pair<BatchList::iterator, size_t>> m_byOffset;
+    std::vector<GpuDecoder::PinnedBuffer> m_freeBuffers;
+    size_t m_cachedBytes{ 0 };
+    size_t m_cacheBudget{ DEFAULT_CACHE_BYTES };
     size_t m_nextSequentialBlock{ 0 };
     size_t m_sequentialFetches{ 0 };
+    size_t m_expected{ 0 };
+    size_t m_hits{ 0 };
+    size_t m_misses{ 0 };
 };
 }  // namespace ibz2host

@@ -419,3 +419,52 @@ def test_decode_buffer_host(ctx, monkeypatch, name, split):
     assert out[:total].tobytes() == want_out[:total].tobytes()
     if name in VALID and (results["status"] == 0).all() and total == GOLDEN[name]["parallel"]["size"] and total > 0:
         assert hashlib.sha256(out[:total].tobytes()).hexdigest() == GOLDEN[name]["parallel"]["sha256"]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# ibz2_multi_*: one file, several contexts (here: on the one device the test box has), ONE output buffer
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("contexts", [2, 3])
+def test_multi_device_decode_matches_single(ctx, contexts):
+    """The multi-device call cuts the stream into byte ranges, decodes every range through its own context and places
+    the bytes of all of them in one caller buffer: bytes, block list and stream CRC verdicts must be those of the
+    single-context call (which earlier tests pin to the oracle and the reference)."""
+    with _capi.MultiContext([0] * contexts) as multi:
+        for name in ["text-450k-l1", "mixed-384k-l2", "multistream-b64-1B-empty-b64", "pbzip2-style-5-streams",
+                     "longruns-3M-l1", "ref-1B", "ref-empty", "err-stream-crc", "err-stream-crc-multistream", "err-bitflip"]:
+            data = case(name)
+            size = GOLDEN[name]["parallel"]["size"] if GOLDEN[name]["parallel"]["rc"] == 0 else 1 << 20
+            out_one = np.zeros(size + 64, dtype=np.uint8)
+            ctx.set_verify_stream_crc(True)
+            try:
+                want, total_one = ctx.decode_buffer(data, out_one, max_blocks=4096)
+            finally:
+                ctx.set_verify_stream_crc(False)
+            out = multi.pinned(size + 64)
+            out[:] = 0xEE
+            got, total = multi.decode_buffer(data, out, max_blocks=4096)
+            label = f"{name} x{contexts}"
+            assert total == total_one, label
+            for field in ("enc_offset_bits", "enc_size_bits", "out_offset", "out_size", "expected_crc", "calculated_crc",
+                          "status", "n_symbols", "stream_flags", "stream_crc_expected", "stream_crc_calculated"):
+                assert got[field].tolist() == want[field].tolist(), f"{label}: {field}"
+            ok = want["status"] == 0
+            if ok.all():
+                assert np.array_equal(out[:total], out_one[:total]), label
+                if GOLDEN[name]["parallel"]["rc"] == 0 and not name.startswith("err-"):
+                    assert hashlib.sha256(out[:total].tobytes()).hexdigest() == GOLDEN[name]["parallel"]["sha256"], label
+            t = multi.timings()
+            assert t["stream_crc_mismatches"] == int((want["status"] == 17).sum()), label
+            assert len(t["devices"]) == contexts
+            multi.free_pinned()
+        # the caller's buffer is too small: the blocks that do not fit say so, the ones in front of them are delivered
+        data = case("text-450k-l1")
+        small = multi.pinned(200_000)
+        got, total = multi.decode_buffer(data, small, max_blocks=64)
+        assert total == GOLDEN["text-450k-l1"]["parallel"]["size"]
+        fits = got["out_offset"] + got["out_size"] <= 200_000
+        assert (got["status"][fits] == 0).all() and (got["status"][~fits] == 15).all() and (~fits).any()
+        full = orc.parallel_reader(data).data
+        edge = int((got["out_offset"] + got["out_size"])[fits].max())
+        assert small[:edge].tobytes() == full[:edge]
