@@ -9,9 +9,12 @@
  *   i.e. the first two bytes of the 32-bit word m, at pattern offset d = 32m - p in 0..31.  So a word can only be
  *   the anchor of a match if its leading halfword is one of the 2 x 32 values magic[d : d + 16].  Each thread streams
  *   16-byte vectors (coalesced 128-bit loads), tests the four leading halfwords against a 64 Kibit bitmap in shared
- *   memory, and only on a hit (p ~ 2^-10 per word on random data) verifies the 32 candidate positions p in
- *   (32m - 32, 32m] exactly with funnel shifts.  Every p has exactly one anchor word, so no match is reported twice.
- *   Matches are appended through one global atomic counter (they are rare) and sorted by the caller.
+ *   memory, and only on a hit (p ~ 2^-10 per word on random data) are the 32 candidate positions p in
+ *   (32m - 32, 32m] verified exactly with funnel shifts.  Every p has exactly one anchor word, so no match is reported
+ *   twice.  Matches are appended through one global atomic counter (they are rare) and sorted by the caller.
+ *   A hit is rare per word but not per warp (one warp iteration in eight has one when both magics are wanted), and a lane
+ *   that loops over 32 positions on its own holds 31 others up for ~500 instructions: that was half of the kernel's
+ *   time.  So the WARP verifies an anchor: the lane that found it broadcasts where it is, and lane s tests position s.
  */
 #include "common.cuh"
 
@@ -45,8 +48,9 @@ loadWordBEChecked( const uint8_t* __restrict__ data, uint64_t nbytes, int64_t by
     return w;
 }
 
-/* Exact test of the 32 bit positions whose anchor word starts at byte wordByte. */
-__device__ __noinline__ void
+/* Exact test of the 32 bit positions whose anchor word starts at byte wordByte, one position per lane of the calling
+ * warp (all 32 lanes call it with the same arguments). */
+__device__ __forceinline__ void
 verifyAnchor( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t wordByte, uint32_t which,
               uint64_t* __restrict__ found, uint32_t* __restrict__ foundCount, uint32_t capacity )
 {
@@ -55,28 +59,47 @@ verifyAnchor( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t wordBy
     const uint32_t b = loadWordBEChecked( data, nbytes, base + 4 );
     const uint32_t c = loadWordBEChecked( data, nbytes, base + 8 );
     const uint64_t nbits = nbytes * 8U;
-    for ( uint32_t s = 1; s <= 32U; ++s ) {
-        const int64_t p = base * 8 + s;
-        if ( ( p < 0 ) || ( static_cast<uint64_t>( p ) + 48U > nbits ) ) {
-            continue;
+    const uint32_t s = ( threadIdx.x & 31U ) + 1U;   /* 1..32 */
+    const int64_t p = base * 8 + s;
+    if ( ( p < 0 ) || ( static_cast<uint64_t>( p ) + 48U > nbits ) ) {
+        return;
+    }
+    const uint32_t hi = ( s == 32U ) ? b : __funnelshift_l( b, a, s );
+    const uint32_t mid = ( s == 32U ) ? c : __funnelshift_l( c, b, s );
+    const uint64_t v = ( static_cast<uint64_t>( hi ) << 16 ) | ( mid >> 16 );
+    uint64_t report = 0;
+    bool hit = false;
+    if ( ( ( which & IBZ2_FIND_BLOCK ) != 0 ) && ( v == MAGIC_BLOCK ) ) {
+        report = static_cast<uint64_t>( p );
+        hit = true;
+    } else if ( ( ( which & IBZ2_FIND_EOS ) != 0 ) && ( v == MAGIC_EOS ) ) {
+        report = static_cast<uint64_t>( p ) | IBZ2_OFFSET_EOS_FLAG;
+        hit = true;
+    }
+    if ( hit ) {
+        const uint32_t idx = atomicAdd( foundCount, 1U );
+        if ( idx < capacity ) {
+            found[idx] = report;
         }
-        const uint32_t hi = ( s == 32U ) ? b : __funnelshift_l( b, a, s );
-        const uint32_t mid = ( s == 32U ) ? c : __funnelshift_l( c, b, s );
-        const uint64_t v = ( static_cast<uint64_t>( hi ) << 16 ) | ( mid >> 16 );
-        uint64_t report = 0;
-        bool hit = false;
-        if ( ( ( which & IBZ2_FIND_BLOCK ) != 0 ) && ( v == MAGIC_BLOCK ) ) {
-            report = static_cast<uint64_t>( p );
-            hit = true;
-        } else if ( ( ( which & IBZ2_FIND_EOS ) != 0 ) && ( v == MAGIC_EOS ) ) {
-            report = static_cast<uint64_t>( p ) | IBZ2_OFFSET_EOS_FLAG;
-            hit = true;
-        }
-        if ( hit ) {
-            const uint32_t idx = atomicAdd( foundCount, 1U );
-            if ( idx < capacity ) {
-                found[idx] = report;
-            }
+    }
+}
+
+/* The anchors that the lanes of a warp have found in one 16-byte vector each (bit k of `hits`: word k), verified by the
+ * whole warp one after the other. */
+__device__ __forceinline__ void
+verifyWarp( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t vector, uint32_t hits, uint32_t which,
+            uint64_t* __restrict__ found, uint32_t* __restrict__ foundCount, uint32_t capacity )
+{
+    uint32_t pending = __ballot_sync( 0xFFFFFFFFU, hits != 0 );
+    while ( pending != 0 ) {
+        const int source = __ffs( static_cast<int>( pending ) ) - 1;
+        pending &= pending - 1U;
+        const uint64_t v = __shfl_sync( 0xFFFFFFFFU, vector, source );
+        uint32_t h = __shfl_sync( 0xFFFFFFFFU, hits, source );
+        while ( h != 0 ) {
+            const uint32_t k = static_cast<uint32_t>( __ffs( static_cast<int>( h ) ) ) - 1U;
+            h &= h - 1U;
+            verifyAnchor( data, nbytes, v * 16U + 4U * k, which, found, foundCount, capacity );
         }
     }
 }
@@ -105,7 +128,9 @@ findMagicsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, uint32_t wh
     const uint64_t stride = static_cast<uint64_t>( gridDim.x ) * FINDER_THREADS;
     const uint64_t tid = static_cast<uint64_t>( blockIdx.x ) * FINDER_THREADS + threadIdx.x;
 
-    for ( uint64_t v0 = tid; v0 < nVectors; v0 += stride * FINDER_UNROLL ) {
+    /* the trip count is the warp's (its first lane's): the verification is a warp affair */
+    const uint64_t warpFirst = tid - ( threadIdx.x & 31U );
+    for ( uint64_t v0 = tid, w0 = warpFirst; w0 < nVectors; v0 += stride * FINDER_UNROLL, w0 += stride * FINDER_UNROLL ) {
         uint4 q[FINDER_UNROLL];
 #pragma unroll
         for ( int u = 0; u < FINDER_UNROLL; ++u ) {
@@ -122,18 +147,15 @@ findMagicsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, uint32_t wh
                 const uint32_t key = words[k] & 0xFFFFU;
                 hits |= ( ( bitmap[key >> 5] >> ( key & 31U ) ) & 1U ) << k;
             }
-            if ( ( hits != 0 ) && ( v < nVectors ) ) {
-                for ( int k = 0; k < 4; ++k ) {
-                    if ( ( hits >> k ) & 1U ) {
-                        verifyAnchor( data, nbytes, v * 16U + 4U * k, which, found, foundCount, capacity );
-                    }
-                }
+            hits = v < nVectors ? hits : 0U;
+            if ( __any_sync( 0xFFFFFFFFU, hits != 0 ) ) {
+                verifyWarp( data, nbytes, v, hits, which, found, foundCount, capacity );
             }
         }
     }
 
-    /* ragged tail: the up to 4 words (last one possibly partial) behind the last full 16-byte vector */
-    if ( tid == 0 ) {
+    /* ragged tail: the up to 4 words (last one possibly partial) behind the last full 16-byte vector, by the first warp */
+    if ( tid < 32U ) {
         for ( uint64_t byte = nVectors * 16U; byte < nbytes; byte += 4U ) {
             uint32_t key = data[byte];
             if ( byte + 1U < nbytes ) {

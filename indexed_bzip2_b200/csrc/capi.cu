@@ -788,7 +788,12 @@ decodeOnDevice( ibz2_ctx* ctx, const uint8_t* dData, uint64_t nbytes, const uint
 
         /* K4..K6 in sub-waves: with host output a finished sub-wave travels while the next one is computed, and the part
          * of the copy that nothing hides shrinks to one sub-wave */
-        const uint32_t sub = std::min<uint32_t>( count, subWaveBlocks( ctx, pipelined ) );
+        /* with host output at least eight sub-waves whatever the wave holds (the copy of a sub-wave hides behind the
+         * next one's kernels: a rank of an 8-GPU job has 1133 blocks, fewer than one fixed sub-wave), but not so small
+         * that the SMs idle between launches */
+        const uint32_t sub = pipelined ? std::min<uint32_t>( subWaveBlocks( ctx, true ),
+                                                             std::max<uint32_t>( ( count + 7U ) / 8U, static_cast<uint32_t>( ctx->sms ) ) )
+                                       : std::min<uint32_t>( count, subWaveBlocks( ctx, false ) );
         cudaEvent_t previousDone = nullptr;
         uint32_t previousSlot = 0;
         uint32_t k = 0;

@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <cstddef>
 #include <cstdint>
+#include <limits>
 #include <map>
 #include <stdexcept>
 #include <utility>
@@ -106,6 +107,33 @@ public:
     dataBlockCount() const
     {
         return m_entries.size() - m_eosCount;
+    }
+
+    /** Data blocks that hold decoded bytes [offset, offset + size); gives up (and says so with 0) beyond 4096 entries. */
+    [[nodiscard]] size_t
+    dataBlocksIn( size_t decodedOffset, size_t size ) const
+    {
+        if ( ( size == 0 ) || m_entries.empty() ) {
+            return 0;
+        }
+        const auto end = ( size > std::numeric_limits<size_t>::max() - decodedOffset ) ? std::numeric_limits<size_t>::max()
+                                                                                         : decodedOffset + size;
+        auto it = std::upper_bound( m_entries.begin(), m_entries.end(), decodedOffset,
+                                    [] ( size_t offset, const Entry& e ) { return offset < e.second; } );
+        if ( it != m_entries.begin() ) {
+            --it;
+        }
+        size_t count = 0;
+        for ( size_t seen = 0; ( it != m_entries.end() ) && ( it->second < end ); ++it, ++seen ) {
+            if ( seen > 4096 ) {
+                return 0;
+            }
+            const auto next = std::next( it );
+            if ( ( next != m_entries.end() ) && ( next->second > it->second ) ) {
+                ++count;   /* an entry with bytes of its own: a data block */
+            }
+        }
+        return count;
     }
 
     void

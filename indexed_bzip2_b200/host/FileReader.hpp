@@ -132,6 +132,16 @@ public:
         return m_seekable ? std::optional<size_t>( m_size ) : std::nullopt;
     }
 
+    /** The descriptor itself, for callers that map the file instead of reading it (filereader/Standard.hpp:88-95). */
+    [[nodiscard]] int
+    fileno() const
+    {
+        if ( m_fd < 0 ) {
+            throw std::invalid_argument( "Trying to get fileno of an invalid file!" );
+        }
+        return m_fd;
+    }
+
 private:
     void
     init()

@@ -11,7 +11,10 @@
 #pragma once
 
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <optional>
 #include <sstream>
@@ -80,12 +83,39 @@ throwForStatus( const ibz2_block_result& r )
     }
 }
 
+/** IBZ2_DEBUG_TIMING=1: wall-clock time of every call the readers make into the C ABI, on stderr */
+class DebugTimer
+{
+public:
+    explicit
+    DebugTimer( const char* what, size_t amount = 0 ) :
+        m_what( what ),
+        m_amount( amount ),
+        m_start( std::chrono::steady_clock::now() )
+    {}
+
+    ~DebugTimer()
+    {
+        static const bool enabled = std::getenv( "IBZ2_DEBUG_TIMING" ) != nullptr;
+        if ( enabled ) {
+            const double ms = std::chrono::duration<double, std::milli>( std::chrono::steady_clock::now() - m_start ).count();
+            std::fprintf( stderr, "[ibz2 host] %-22s %10.3f ms  (%zu)\n", m_what, ms, m_amount );
+        }
+    }
+
+private:
+    const char* m_what;
+    size_t m_amount;
+    std::chrono::steady_clock::time_point m_start;
+};
+
 class GpuDecoder
 {
 public:
     explicit
     GpuDecoder( int device = 0 )
     {
+        const DebugTimer timer( "create context" );
         const int rc = ibz2_create( device, &m_ctx );
         if ( rc != IBZ2_OK ) {
             throw std::runtime_error( std::string( "Cannot open the CUDA bzip2 decoder (there is no CPU fallback): " )
@@ -101,24 +131,48 @@ public:
             if ( m_deviceData != nullptr ) {
                 ibz2_device_free( m_ctx, m_deviceData );
             }
-            if ( m_pinned != nullptr ) {
-                ibz2_host_free_pinned( m_ctx, m_pinned );
-            }
             ibz2_destroy( m_ctx );
         }
+    }
+
+    /** Page-locked host memory that a batch of decoded blocks lands in; owned by whoever asked for it. */
+    struct PinnedBuffer
+    {
+        void* data{ nullptr };
+        size_t capacity{ 0 };
+    };
+
+    [[nodiscard]] PinnedBuffer
+    allocPinned( size_t capacity )
+    {
+        const DebugTimer timer( "alloc pinned bytes", capacity );
+        PinnedBuffer buffer;
+        check( ibz2_host_alloc_pinned( m_ctx, capacity, &buffer.data ), "ibz2_host_alloc_pinned" );
+        buffer.capacity = capacity;
+        return buffer;
+    }
+
+    void
+    freePinned( PinnedBuffer& buffer )
+    {
+        if ( buffer.data != nullptr ) {
+            ibz2_host_free_pinned( m_ctx, buffer.data );
+        }
+        buffer = PinnedBuffer{};
     }
 
     GpuDecoder( const GpuDecoder& ) = delete;
     GpuDecoder& operator=( const GpuDecoder& ) = delete;
 
-    /** Copies the compressed file to the device; @p data may be released afterwards. */
+    /** Copies the compressed file (pageable memory: a mapping or a vector) to the device through pinned staging. */
     void
     upload( const uint8_t* data, size_t size )
     {
+        const DebugTimer timer( "upload bytes", size );
         m_size = size;
         check( ibz2_device_alloc( m_ctx, size + 16, &m_deviceData ), "ibz2_device_alloc" );
         if ( size > 0 ) {
-            check( ibz2_memcpy_h2d( m_ctx, m_deviceData, data, size ), "ibz2_memcpy_h2d" );
+            check( ibz2_upload_pageable( m_ctx, m_deviceData, data, size ), "ibz2_upload_pageable" );
         }
     }
 
@@ -132,6 +186,7 @@ public:
     [[nodiscard]] std::vector<uint64_t>
     findBlocks() const
     {
+        const DebugTimer timer( "find blocks in bytes", m_size );
         std::vector<uint64_t> offsets( 1024 );
         while ( true ) {
             uint64_t count = 0;
@@ -148,35 +203,32 @@ public:
     }
 
     /**
-     * Decodes the blocks at @p offsets (bit offsets of their magics) into @p out, back to back.
+     * Decodes the blocks at @p offsets (bit offsets of their magics) into @p buffer, back to back; the buffer is
+     * replaced by a larger one when the blocks turn out to need it.
      * @p results gets one entry per block; failing blocks keep their status and do not fail the call.
      */
     void
-    decode( const uint64_t* offsets, size_t count, std::vector<ibz2_block_result>& results, uint8_t*& out,
-            size_t& outSize )
+    decode( const uint64_t* offsets, size_t count, std::vector<ibz2_block_result>& results, PinnedBuffer& buffer )
     {
+        const DebugTimer timer( "decode blocks", count );
         results.assign( count, ibz2_block_result{} );
-        outSize = 0;
-        out = nullptr;
         if ( count == 0 ) {
             return;
         }
-        size_t capacity = count * 1000000ULL + 65536ULL;
         for ( int attempt = 0; attempt < 2; ++attempt ) {
-            ensurePinned( capacity );
             uint64_t total = 0;
-            check( ibz2_decode_blocks( m_ctx, m_deviceData, m_size, IBZ2_MEM_DEVICE, offsets, count, m_pinned,
-                                       m_pinnedCapacity, IBZ2_MEM_HOST, results.data(), &total ),
+            check( ibz2_decode_blocks( m_ctx, m_deviceData, m_size, IBZ2_MEM_DEVICE, offsets, count, buffer.data,
+                                       buffer.capacity, IBZ2_MEM_HOST, results.data(), &total ),
                    "ibz2_decode_blocks" );
             const bool overflow = std::any_of( results.begin(), results.end(), [] ( const ibz2_block_result& r ) {
                 return r.status == IBZ2_ST_OUTPUT_CAPACITY;
             } );
             if ( !overflow ) {
-                outSize = total;
-                out = static_cast<uint8_t*>( m_pinned );
                 return;
             }
-            capacity = total + 65536ULL;   /* RLE1 can expand a block 51-fold: now the sizes are known */
+            /* RLE1 can expand a block 51-fold: now the sizes are known */
+            freePinned( buffer );
+            buffer = allocPinned( total + 65536ULL );
         }
         throw std::runtime_error( "Decoded block sizes changed between two decodes of the same blocks" );
     }
@@ -207,25 +259,8 @@ private:
         }
     }
 
-    void
-    ensurePinned( size_t capacity )
-    {
-        if ( capacity <= m_pinnedCapacity ) {
-            return;
-        }
-        if ( m_pinned != nullptr ) {
-            ibz2_host_free_pinned( m_ctx, m_pinned );
-            m_pinned = nullptr;
-            m_pinnedCapacity = 0;
-        }
-        check( ibz2_host_alloc_pinned( m_ctx, capacity, &m_pinned ), "ibz2_host_alloc_pinned" );
-        m_pinnedCapacity = capacity;
-    }
-
     ibz2_ctx* m_ctx{ nullptr };
     void* m_deviceData{ nullptr };
     size_t m_size{ 0 };
-    void* m_pinned{ nullptr };
-    size_t m_pinnedCapacity{ 0 };
 };
 }  // namespace ibz2host

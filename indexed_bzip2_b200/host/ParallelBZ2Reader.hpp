@@ -117,6 +117,11 @@ public:
             return 0;
         }
 
+        /* with the block map complete the blocks this read touches are known: they are decoded by one call */
+        if ( m_index.finished() && ( nBytesToRead != std::numeric_limits<size_t>::max() ) ) {
+            m_source.expectBlocks( m_index.dataBlocksIn( m_currentPosition, nBytesToRead ) );
+        }
+
         size_t nBytesDecoded = 0;
         while ( ( nBytesDecoded < nBytesToRead ) && !eof() ) {
             throwDeferredStreamError();

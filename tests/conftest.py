@@ -13,10 +13,8 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "ref: needs the compiled reference under oracle/_ref (skipped when absent)")
 
 
-def pytest_collection_modifyitems(config, items):
-    # GPU tests must fail loudly (not skip) when selected with -m gpu on a box whose GPU/extension is missing;
-    # without -m gpu they are deselected by the marker expression the driver passes.
-    pass
+# GPU tests fail loudly (they do not skip) when selected with -m gpu on a box whose GPU or extension is missing; without
+# -m gpu they are deselected by the marker expression the driver passes.
 
 
 @pytest.fixture(scope="session")

@@ -89,6 +89,16 @@ def test_host_library_exports_the_reader_entry_points():
         ibz2.open(path("ref-1B"), parallelization="4")
 
 
+def test_reference_module_name_is_importable():
+    """python/indexed_bzip2/pyproject.toml:14,51-57: the module is `indexed_bzip2`, the console script `ibzip2` -> cli"""
+    import indexed_bzip2
+
+    assert indexed_bzip2.open is ibz2.open and indexed_bzip2.IndexedBzip2File is ibz2.IndexedBzip2File
+    assert indexed_bzip2.cli is ibz2.cli and indexed_bzip2.__version__ == "1.7.0"
+    text = (ROOT / "pyproject.toml").read_text()
+    assert 'ibzip2 = "indexed_bzip2_b200:cli"' in text
+
+
 def test_cli_version_and_help_need_no_gpu():
     out = subprocess.run([str(CLI), "--version"], capture_output=True, text=True)
     assert out.returncode == 0
