@@ -382,6 +382,35 @@ def algorithmic_bytes(stage: str, c: int, n: int, u: int, s: int = 0) -> int:
             "rle_scan_ms": 5 * n, "rle_write_ms": 5 * n + u, "crc_ms": u}[stage]
 
 
+def multi_api_run(w, devices: int, steps: int) -> dict:
+    from indexed_bzip2_b200 import _capi
+
+    comp = w.compressed
+    with _capi.MultiContext(list(range(devices))) as multi:
+        pin_in = multi.pinned(comp.size)
+        pin_in[:] = comp
+        out = multi.pinned(w.raw_size + (64 << 20))
+        results, total = multi.decode_buffer(pin_in, out, max_blocks=w.blocks + 16)   # warm-up: contexts, scratch
+        wall = []
+        device_ms = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            results, total = multi.decode_buffer(pin_in, out, max_blocks=w.blocks + 16)
+            wall.append((time.perf_counter() - t0) * 1e3)
+            t = multi.timings()
+            device_ms.append(max(d["total_ms"] for d in t["devices"]))
+        ok = bool((results["status"] == 0).all()) and total == w.raw_size and w.verify(out[:total]) \
+            and t["stream_crc_mismatches"] == 0 and bool(results[-1]["stream_flags"] & 4)
+        ms = sum(wall) / len(wall)
+        line = {"value": round(w.raw_size / (ms * 1e-3) / 1e9, 3), "unit": UNIT, "ms_per_step": round(ms, 3),
+                "device_ms_max": round(sum(device_ms) / len(device_ms), 3), "devices": devices, "verified": ok,
+                "api": "ibz2_multi_decode_buffer: host buffer in, ONE pinned host buffer out, one process; wall clock of "
+                       "the call (its slowest device's CUDA-event time beside it)",
+                "last_call": {k: v for k, v in t.items() if k != "devices"}}
+        multi.free_pinned()
+    return line
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -614,6 +643,14 @@ def run_ours(args):
         except Exception as e:
             line["reader_api"] = {"value": None, "note": f"failed: {e}"}
     if world > 1:
+        # the same job through the product's own multi-GPU call (ibz2_multi_decode_buffer: ONE process, one host thread
+        # and one context per GPU, one pinned output buffer); the other ranks have released their GPUs and wait
+        dist.barrier()
+        if rank == 0 and os.environ.get("IBZ2_BENCH_MULTI", "1") != "0":
+            try:
+                line["multi_api"] = multi_api_run(w, world, args.steps)
+            except Exception as e:
+                line["multi_api"] = {"value": None, "note": f"failed: {e}"}
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:

@@ -75,6 +75,7 @@ def _load():
         "ibz2r_join_threads": (i32, [vp]),
         "ibz2r_set_verify_stream_crc": (i32, [vp, i32]),
         "ibz2r_set_open_device": (None, [i32]),
+        "ibz2r_set_open_devices": (None, [C.POINTER(i32), i32]),
         "ibz2r_cli": (i32, [i32, C.POINTER(C.c_char_p)]),
     }
     for name, (restype, argtypes) in sigs.items():
@@ -102,13 +103,15 @@ def _hasValidFileno(file):
 class _Reader:
     """What _IndexedBzip2File / _IndexedBzip2FileParallel are in the reference: a thin object around the C++ reader."""
 
-    def __init__(self, file, parallelization, device=None, verify_stream_crc=True):
+    def __init__(self, file, parallelization, device=None, verify_stream_crc=True, gpus=None):
         if not isinstance(parallelization, int):
             raise TypeError(f"Parallelization argument must be an integer not '{parallelization}'!")
         lib = _load()
         self._lib = lib
         self._handle = None
         lib.ibz2r_set_open_device(-1 if device is None else int(device))   # None: $IBZ2_DEVICE, else device 0
+        devices = list(range(gpus)) if isinstance(gpus, int) else [int(d) for d in (gpus or [])]
+        lib.ibz2r_set_open_devices((C.c_int * max(1, len(devices)))(*devices), len(devices))
         if isinstance(file, int) and not isinstance(file, bool):
             handle = lib.ibz2r_open_fd(file, parallelization)
         elif _hasValidFileno(file):
@@ -286,15 +289,17 @@ class IndexedBzip2File(io.BufferedReader):
         self.set_block_offsets(offsets)
 
 
-def open(filename, parallelization=1, *, device=None, verify_stream_crc=True):
+def open(filename, parallelization=1, *, device=None, verify_stream_crc=True, gpus=None):
     """
     filename: can be a file path, a file descriptor, or a file object
               with suitable read, seekable, seek, and tell methods.
     device: CUDA device index (default: $IBZ2_DEVICE, else 0).  New next to the reference.
     verify_stream_crc: the parallel reader checks the CRC of every bzip2 stream while it builds the block map, which
               the reference only does in its serial reader; False restores the reference's behaviour.
+    gpus: a number N (devices 0..N-1) or a list of device indices that share the decoding of every large batch of the
+              parallel reader.  New next to the reference.
     """
-    return IndexedBzip2File(filename, parallelization, device=device, verify_stream_crc=verify_stream_crc)
+    return IndexedBzip2File(filename, parallelization, device=device, verify_stream_crc=verify_stream_crc, gpus=gpus)
 
 
 def cli(args=None):

@@ -74,7 +74,9 @@ struct ibz2_ctx
 
 namespace
 {
-int g_smCount = 148;
+/* what the launch wrappers size their grids with: the SM count of the context whose call runs on this thread (contexts on
+ * devices with different SM counts may live in one process; every entry point sets it before it launches anything) */
+thread_local int g_smCount = 148;
 
 #define IBZ2_CUDA_CHECK( ctx, call )                                                                          \
     do {                                                                                                      \
@@ -85,36 +87,43 @@ int g_smCount = 148;
         }                                                                                                     \
     } while ( false )
 
-cudaEvent_t
-nextEvent( ibz2_ctx* ctx )
-{
-    if ( ctx->eventsUsed == ctx->events.size() ) {
-        cudaEvent_t e;
-        cudaEventCreate( &e );
-        ctx->events.push_back( e );
-    }
-    cudaEvent_t e = ctx->events[ctx->eventsUsed++];
-    cudaEventRecord( e, ctx->stream );
-    return e;
-}
-
-/* an event of the pool that the callee records */
+/* an event of the pool that the callee records.  Events only carry timings: when one cannot be created the first event
+ * of the pool stands in (the timings of that call are then meaningless, its results are not), and the error stays
+ * readable through ibz2_last_error. */
 cudaEvent_t
 spareEvent( ibz2_ctx* ctx )
 {
     if ( ctx->eventsUsed == ctx->events.size() ) {
-        cudaEvent_t e;
-        cudaEventCreate( &e );
+        cudaEvent_t e = nullptr;
+        const cudaError_t err = cudaEventCreate( &e );
+        if ( err != cudaSuccess ) {
+            ctx->lastError = std::string( "cudaEventCreate: " ) + cudaGetErrorString( err );
+            cudaGetLastError();
+            return ctx->events.empty() ? nullptr : ctx->events.front();
+        }
         ctx->events.push_back( e );
     }
     return ctx->events[ctx->eventsUsed++];
+}
+
+cudaEvent_t
+nextEvent( ibz2_ctx* ctx )
+{
+    cudaEvent_t e = spareEvent( ctx );
+    if ( e != nullptr ) {
+        cudaEventRecord( e, ctx->stream );
+    }
+    return e;
 }
 
 float
 elapsed( cudaEvent_t a, cudaEvent_t b )
 {
     float ms = 0;
-    cudaEventElapsedTime( &ms, a, b );
+    if ( ( a == nullptr ) || ( b == nullptr ) || ( cudaEventElapsedTime( &ms, a, b ) != cudaSuccess ) ) {
+        cudaGetLastError();
+        return 0;
+    }
     return ms;
 }
 
@@ -326,9 +335,21 @@ ibz2_create( int device, ibz2_ctx** out )
     }
     ctx->device = device;
     cudaDeviceProp prop{};
+    /* whatever has been created when a step fails is released by ibz2_destroy, which looks at every handle */
     if ( ( ( err = cudaSetDevice( device ) ) != cudaSuccess )
-         || ( ( err = cudaGetDeviceProperties( &prop, device ) ) != cudaSuccess )
-         || ( ( err = cudaStreamCreateWithFlags( &ctx->stream, cudaStreamNonBlocking ) ) != cudaSuccess )
+         || ( ( err = cudaGetDeviceProperties( &prop, device ) ) != cudaSuccess ) ) {
+        g_createError = std::string( "CUDA initialisation failed: " ) + cudaGetErrorString( err );
+        cudaGetLastError();
+        ibz2_destroy( ctx );
+        return IBZ2_E_CUDA;
+    }
+    if ( prop.major < 10 ) {
+        g_createError = "this library is built for sm_100a (Blackwell B200) only; device is sm_"
+                        + std::to_string( prop.major ) + std::to_string( prop.minor );
+        ibz2_destroy( ctx );
+        return IBZ2_E_NO_DEVICE;
+    }
+    if ( ( ( err = cudaStreamCreateWithFlags( &ctx->stream, cudaStreamNonBlocking ) ) != cudaSuccess )
          || ( ( err = cudaStreamCreateWithFlags( &ctx->copyStream, cudaStreamNonBlocking ) ) != cudaSuccess )
          || ( ( err = cudaStreamCreateWithFlags( &ctx->inStream, cudaStreamNonBlocking ) ) != cudaSuccess )
          || ( ( err = cudaEventCreateWithFlags( &ctx->inFirstHalf, cudaEventDefault ) ) != cudaSuccess )
@@ -336,26 +357,17 @@ ibz2_create( int device, ibz2_ctx** out )
          || ( ( err = cudaMallocHost( &ctx->hRunning, 16 * sizeof( uint64_t ) ) ) != cudaSuccess )
          || ( ( err = cudaMalloc( &ctx->dRunning, 2 * sizeof( uint64_t ) ) ) != cudaSuccess ) ) {
         g_createError = std::string( "CUDA initialisation failed: " ) + cudaGetErrorString( err );
-        delete ctx;
+        cudaGetLastError();
+        ibz2_destroy( ctx );
         return IBZ2_E_CUDA;
-    }
-    if ( prop.major < 10 ) {
-        g_createError = "this library is built for sm_100a (Blackwell B200) only; device is sm_"
-                        + std::to_string( prop.major ) + std::to_string( prop.minor );
-        cudaFree( ctx->dRunning );
-        cudaStreamDestroy( ctx->stream );
-        delete ctx;
-        return IBZ2_E_NO_DEVICE;
     }
     ctx->sms = prop.multiProcessorCount;
     g_smCount = ctx->sms;
-    ctx->batchBlocks = static_cast<uint32_t>( ctx->sms ) * 64U;   /* two rounds of K2b's 32 decoders per SM */
+    ctx->batchBlocks = static_cast<uint32_t>( ctx->sms ) * 64U;   /* one round of K2b's 64 decoders per SM */
     ibz2::initCrcConstants();
     if ( ( err = cudaGetLastError() ) != cudaSuccess ) {
         g_createError = std::string( "constant upload failed: " ) + cudaGetErrorString( err );
-        cudaFree( ctx->dRunning );
-        cudaStreamDestroy( ctx->stream );
-        delete ctx;
+        ibz2_destroy( ctx );
         return IBZ2_E_CUDA;
     }
     *out = ctx;
@@ -369,7 +381,10 @@ ibz2_destroy( ibz2_ctx* ctx )
         return;
     }
     cudaSetDevice( ctx->device );
-    cudaStreamSynchronize( ctx->stream );
+    g_smCount = ctx->sms;
+    if ( ctx->stream != nullptr ) {
+        cudaStreamSynchronize( ctx->stream );
+    }
     freeScratch( ctx );
     cudaFree( ctx->dIn );
     cudaFree( ctx->dOut );
@@ -400,9 +415,14 @@ ibz2_destroy( ibz2_ctx* ctx )
     }
     if ( ctx->timerStart != nullptr ) {
         cudaEventDestroy( ctx->timerStart );
+    }
+    if ( ctx->timerStop != nullptr ) {
         cudaEventDestroy( ctx->timerStop );
     }
-    cudaStreamDestroy( ctx->stream );
+    if ( ctx->stream != nullptr ) {
+        cudaStreamDestroy( ctx->stream );
+    }
+    cudaGetLastError();   /* a half-built context may have handed null handles to the calls above */
     delete ctx;
 }
 
@@ -422,7 +442,8 @@ ibz2_set_batch_blocks( ibz2_ctx* ctx, uint32_t blocks )
     if ( ( ctx == nullptr ) || ( blocks == 0 ) ) {
         return IBZ2_E_INVALID_ARGUMENT;
     }
-    ctx->batchBlocks = blocks;
+    /* several kernels launch with dim3( x, blocks of a sub-wave ), and a sub-wave is up to half a wave: gridDim.y <= 65535 */
+    ctx->batchBlocks = std::min<uint32_t>( blocks, 2U * 65535U );
     return IBZ2_OK;
 }
 
@@ -487,6 +508,7 @@ ibz2_device_alloc( ibz2_ctx* ctx, uint64_t nbytes, void** dptr )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaMalloc( dptr, nbytes + 256U ) );
     return IBZ2_OK;
 }
@@ -498,6 +520,7 @@ ibz2_device_free( ibz2_ctx* ctx, void* dptr )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaFree( dptr ) );
     return IBZ2_OK;
 }
@@ -509,6 +532,7 @@ ibz2_host_alloc_pinned( ibz2_ctx* ctx, uint64_t nbytes, void** hptr )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaHostAlloc( hptr, nbytes > 0 ? nbytes : 1, cudaHostAllocPortable ) );
     return IBZ2_OK;
 }
@@ -530,6 +554,7 @@ ibz2_memcpy_h2d( ibz2_ctx* ctx, void* dptr, const void* hptr, uint64_t nbytes )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( dptr, hptr, nbytes, cudaMemcpyHostToDevice, ctx->stream ) );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
     return IBZ2_OK;
@@ -545,6 +570,7 @@ ibz2_upload_pageable( ibz2_ctx* ctx, void* dptr, const void* hptr, uint64_t nbyt
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     constexpr uint64_t CHUNK = 32ULL << 20;
     constexpr unsigned THREADS = 4;
     if ( nbytes <= ( 4ULL << 20 ) ) {
@@ -593,6 +619,7 @@ ibz2_memcpy_d2h( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbytes )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( hptr, dptr, nbytes, cudaMemcpyDeviceToHost, ctx->stream ) );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
     return IBZ2_OK;
@@ -605,6 +632,7 @@ ibz2_synchronize( ibz2_ctx* ctx )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->stream ) );
     return IBZ2_OK;
 }
@@ -937,6 +965,8 @@ static void
 beginCall( ibz2_ctx* ctx )
 {
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
+    g_smCount = ctx->sms;
     ctx->timings = ibz2_timings{};
     ctx->eventsUsed = 0;
 }
@@ -1071,6 +1101,19 @@ decodeBufferSplit( ibz2_ctx* ctx, const uint8_t* data, uint64_t nbytes, uint64_t
     IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->inFirstHalf, s ) );
     const cudaEvent_t e1 = nextEvent( ctx );
     bool secondHalfQueued = false;
+    /* whichever way this function is left, nothing reads the caller's input or writes the caller's output afterwards */
+    struct DrainCopies
+    {
+        ibz2_ctx* ctx;
+        const bool* queued;
+        ~DrainCopies()
+        {
+            if ( *queued ) {
+                cudaStreamSynchronize( ctx->inStream );
+            }
+            cudaStreamSynchronize( ctx->copyStream );
+        }
+    } drainCopies{ ctx, &secondHalfQueued };
     const std::function<int()> queueSecondHalf = [&] () -> int {
         if ( !secondHalfQueued ) {
             secondHalfQueued = true;
@@ -1275,6 +1318,7 @@ ibz2_timer_start( ibz2_ctx* ctx )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     if ( ctx->timerStart == nullptr ) {
         IBZ2_CUDA_CHECK( ctx, cudaEventCreate( &ctx->timerStart ) );
         IBZ2_CUDA_CHECK( ctx, cudaEventCreate( &ctx->timerStop ) );
@@ -1291,6 +1335,7 @@ ibz2_timer_stop( ibz2_ctx* ctx, float* milliseconds )
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     IBZ2_CUDA_CHECK( ctx, cudaEventRecord( ctx->timerStop, ctx->stream ) );
     IBZ2_CUDA_CHECK( ctx, cudaEventSynchronize( ctx->timerStop ) );
     IBZ2_CUDA_CHECK( ctx, cudaEventElapsedTime( milliseconds, ctx->timerStart, ctx->timerStop ) );
@@ -1306,6 +1351,7 @@ ibz2_debug_decode_block( ibz2_ctx* ctx, const void* data, uint64_t nbytes, uint6
         return IBZ2_E_INVALID_ARGUMENT;
     }
     cudaSetDevice( ctx->device );
+    g_smCount = ctx->sms;
     cudaStream_t s = ctx->stream;
     int rc = ensureInput( ctx, nbytes );
     if ( rc == IBZ2_OK ) {

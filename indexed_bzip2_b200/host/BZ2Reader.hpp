@@ -25,7 +25,7 @@ class BZ2Reader final : public BZ2ReaderInterface
 public:
     explicit
     BZ2Reader( UniqueFileReader fileReader, int device = 0 ) :
-        m_source( std::move( fileReader ), 1, device )
+        m_source( std::move( fileReader ), 1, std::vector<int>{ device } )
     {}
 
     explicit

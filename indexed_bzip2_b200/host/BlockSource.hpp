@@ -24,7 +24,9 @@
 #include <limits>
 #include <list>
 #include <memory>
+#include <exception>
 #include <optional>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -42,21 +44,28 @@ public:
     static constexpr size_t MAX_BATCH_BLOCKS = 2048;      /* 1.8 GB of decoded bytes at 900 kB blocks */
     static constexpr size_t BATCH_GROWTH_SHIFT = 3;       /* consecutive misses: 4, 32, 256, 2048 blocks */
     static constexpr size_t MAX_CACHED_BATCHES = 16;
+    static constexpr size_t MIN_BLOCKS_PER_DEVICE = 64;   /* below this a batch stays on the first device */
     /* Page-locking host memory is the slow part of a sequential read (measured: 0.72 s per 2 GB buffer against 0.125 s
      * to decode the 2048 blocks that fill it), so the cache holds two large batches, whose buffers then take turns. */
     static constexpr size_t LARGE_BATCH_BYTES = 256ULL << 20;
     static constexpr size_t MAX_LARGE_BATCHES = 2;
     static constexpr size_t DEFAULT_CACHE_BYTES = 6ULL << 30;
 
-    BlockSource( UniqueFileReader fileReader, size_t parallelization, int device ) :
+    /** @p devices: the CUDA devices that share the decoding of every large batch (one entry: the usual case; an entry
+     *  may repeat, which gives one GPU two contexts -- how the tests exercise the multi-device path on one GPU). */
+    BlockSource( UniqueFileReader fileReader, size_t parallelization, std::vector<int> devices ) :
         m_parallelization( parallelization ),
-        m_device( device )
+        m_devices( devices.empty() ? std::vector<int>{ 0 } : std::move( devices ) ),
+        m_gpus( m_devices.size() )
     {
         if ( !fileReader ) {
             throw std::invalid_argument( "A file reader is required!" );
         }
         if ( const char* const env = std::getenv( "IBZ2_CACHE_BYTES" ); env != nullptr ) {
             m_cacheBudget = std::max<size_t>( 1, std::strtoull( env, nullptr, 10 ) );
+        }
+        if ( const char* const env = std::getenv( "IBZ2_MIN_BLOCKS_PER_DEVICE" ); env != nullptr ) {
+            m_minBlocksPerDevice = std::max<size_t>( 1, std::strtoull( env, nullptr, 10 ) );
         }
         if ( auto* memory = dynamic_cast<MemoryFileReader*>( fileReader.get() ); memory != nullptr ) {
             m_owned = std::move( memory->bytes() );
@@ -236,21 +245,59 @@ public:
         }
         m_expected = 0;
 
-        Batch batch;
-        batch.buffer = takeBuffer( count * 1000000ULL + 65536ULL );
-        gpu().decode( batchOffsets, count, batch.results, batch.buffer );
-        batch.bytes = batch.buffer.capacity;
-        m_batches.push_front( std::move( batch ) );
-        const auto inserted = m_batches.begin();
-        for ( size_t i = 0; i < inserted->results.size(); ++i ) {
-            m_byOffset[inserted->results[i].enc_offset_bits] = { inserted, i };
+        /* Several devices: each takes a contiguous part of the batch (blocks are independent: no collective, the parts
+         * land in separate pinned buffers and enter the cache as batches of their own), decoded by one host thread per
+         * device like the worker threads of the reference's pool (core/BlockFetcher.hpp:176-190).  Small batches are
+         * not worth it: a decode call costs one block's Huffman chain however few blocks it holds. */
+        const size_t parts = ( listed && ( count >= m_minBlocksPerDevice * m_gpus.size() ) ) ? m_gpus.size() : 1;
+        std::vector<Batch> decoded( parts );
+        if ( parts == 1 ) {
+            decoded[0].buffer = takeBuffer( count * 1000000ULL + 65536ULL );
+            gpu().decode( batchOffsets, count, decoded[0].results, decoded[0].buffer );
+        } else {
+            std::vector<std::thread> workers;
+            std::vector<std::exception_ptr> failures( parts );
+            for ( size_t d = 0; d < parts; ++d ) {
+                const size_t begin = count * d / parts;
+                const size_t end = count * ( d + 1 ) / parts;
+                gpu( d );   /* contexts and uploads are created here, one after the other */
+                decoded[d].buffer = takeBuffer( ( end - begin ) * 1000000ULL + 65536ULL );
+                workers.emplace_back( [this, d, begin, end, batchOffsets, &decoded, &failures] () {
+                    try {
+                        m_gpus[d]->decode( batchOffsets + begin, end - begin, decoded[d].results, decoded[d].buffer );
+                    } catch ( ... ) {
+                        failures[d] = std::current_exception();
+                    }
+                } );
+            }
+            for ( auto& worker : workers ) {
+                worker.join();
+            }
+            for ( const auto& failure : failures ) {
+                if ( failure ) {
+                    std::rethrow_exception( failure );
+                }
+            }
         }
-        m_cachedBytes += inserted->bytes;
-        while ( ( m_batches.size() > 1 )
-                && ( ( m_batches.size() > MAX_CACHED_BATCHES ) || ( m_cachedBytes > m_cacheBudget ) || ( largeBatches() > MAX_LARGE_BATCHES ) ) ) {
+        /* youngest last: the part that holds the wanted block ends up at the front */
+        for ( size_t d = parts; d-- > 0; ) {
+            decoded[d].bytes = decoded[d].buffer.capacity;
+            m_batches.push_front( std::move( decoded[d] ) );
+            const auto inserted = m_batches.begin();
+            for ( size_t i = 0; i < inserted->results.size(); ++i ) {
+                m_byOffset[inserted->results[i].enc_offset_bits] = { inserted, i };
+            }
+            m_cachedBytes += inserted->bytes;
+        }
+        const auto wantedEntry = m_byOffset.at( encodedOffset );
+        m_batches.splice( m_batches.begin(), m_batches, wantedEntry.first );
+        const auto inserted = wantedEntry.first;
+        while ( ( m_batches.size() > parts )
+                && ( ( m_batches.size() > MAX_CACHED_BATCHES ) || ( m_cachedBytes > m_cacheBudget )
+                     || ( largeBatches() > MAX_LARGE_BATCHES * parts ) ) ) {
             evictOldest();
         }
-        return checked( *inserted, m_byOffset.at( encodedOffset ).second );
+        return checked( *inserted, wantedEntry.second );
     }
 
     /** BZ2BlockFetcher::readBlockHeader (BZ2BlockFetcher.hpp:64-82): magic, CRC and EOS padding only. */
@@ -260,27 +307,36 @@ public:
         return GpuDecoder::probeHeader( m_data, m_size, bitOffset );
     }
 
+    /** The decoder of device @p index of the set (created, and given the file, on first use). */
     GpuDecoder&
-    gpu()
+    gpu( size_t index = 0 )
     {
-        if ( !m_gpu ) {
-            m_gpu = std::make_unique<GpuDecoder>( m_device );
-            m_gpu->upload( m_data, m_size );
+        if ( !m_gpus[index] ) {
+            m_gpus[index] = std::make_unique<GpuDecoder>( m_devices[index] );
+            m_gpus[index]->upload( m_data, m_size );
         }
-        return *m_gpu;
+        return *m_gpus[index];
+    }
+
+    [[nodiscard]] size_t
+    deviceCount() const
+    {
+        return m_gpus.size();
     }
 
     void
     close()
     {
         dropBatch();
-        if ( m_gpu ) {
+        if ( m_gpus[0] ) {
             for ( auto& buffer : m_freeBuffers ) {
-                m_gpu->freePinned( buffer );
+                m_gpus[0]->freePinned( buffer );   /* pinned memory is portable: any context may free it */
             }
         }
         m_freeBuffers.clear();
-        m_gpu.reset();
+        for ( auto& decoder : m_gpus ) {
+            decoder.reset();
+        }
     }
 
     /** cache statistics like BlockFetcher::statistics() (core/BlockFetcher.hpp:62-126): hits, misses */
@@ -381,8 +437,8 @@ private:
     std::vector<uint8_t> m_owned;
 
     const size_t m_parallelization;
-    const int m_device;
-    std::unique_ptr<GpuDecoder> m_gpu;
+    const std::vector<int> m_devices;
+    std::vector<std::unique_ptr<GpuDecoder>> m_gpus;
 
     std::vector<uint64_t> m_finderOffsets;
     bool m_finderReady{ false };
@@ -393,6 +449,7 @@ private:
     std::vector<GpuDecoder::PinnedBuffer> m_freeBuffers;
     size_t m_cachedBytes{ 0 };
     size_t m_cacheBudget{ DEFAULT_CACHE_BYTES };
+    size_t m_minBlocksPerDevice{ MIN_BLOCKS_PER_DEVICE };
     size_t m_nextSequentialBlock{ 0 };
     size_t m_sequentialFetches{ 0 };
     size_t m_expected{ 0 };

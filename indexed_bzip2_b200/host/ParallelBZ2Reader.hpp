@@ -33,7 +33,16 @@ class ParallelBZ2Reader final : public BZ2ReaderInterface
 public:
     explicit
     ParallelBZ2Reader( UniqueFileReader fileReader, size_t parallelization = 0, int device = 0 ) :
-        m_source( requireSeekable( std::move( fileReader ) ), parallelization, device )
+        m_source( requireSeekable( std::move( fileReader ) ), parallelization, std::vector<int>{ device } )
+    {}
+
+    /**
+     * New next to the reference: the GPUs of one machine that share the decoding of every large batch, one host thread
+     * per device -- where the reference scales with the threads of its pool (ParallelBZ2Reader.hpp:50-69), this reader
+     * scales with devices.  Positions, block map and bytes do not depend on the set.
+     */
+    ParallelBZ2Reader( UniqueFileReader fileReader, size_t parallelization, std::vector<int> devices ) :
+        m_source( requireSeekable( std::move( fileReader ) ), parallelization, std::move( devices ) )
     {}
 
     explicit

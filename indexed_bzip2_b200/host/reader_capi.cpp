@@ -8,6 +8,7 @@
 #include <cstring>
 #include <cstdlib>
 #include <memory>
+#include <vector>
 #include <new>
 #include <optional>
 #include <string>
@@ -72,6 +73,7 @@ namespace
 thread_local std::string g_openError;
 thread_local int g_openKind = IBZ2R_NONE;
 thread_local int g_openDevice = -1;   /* ibz2r_set_open_device; -1 = $IBZ2_DEVICE, else device 0 */
+thread_local std::vector<int> g_openDevices;   /* ibz2r_set_open_devices; empty = the single device above */
 
 int
 openDevice()
@@ -130,7 +132,9 @@ wrap( UniqueFileReader fileReader, size_t parallelization )
     if ( parallelization == 1 ) {
         handle->reader = std::make_unique<BZ2Reader>( std::move( fileReader ), openDevice() );
     } else {
-        auto parallel = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), parallelization, openDevice() );
+        auto parallel = g_openDevices.empty()
+                        ? std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), parallelization, openDevice() )
+                        : std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), parallelization, g_openDevices );
         handle->parallel = parallel.get();
         handle->reader = std::move( parallel );
     }
@@ -153,6 +157,13 @@ void
 ibz2r_set_open_device( int device )
 {
     g_openDevice = device;
+}
+
+/* the set of devices a parallel reader opened next by this thread spreads its batches over (count 0: one device) */
+void
+ibz2r_set_open_devices( const int* devices, int count )
+{
+    g_openDevices.assign( devices, devices + ( ( devices != nullptr ) && ( count > 0 ) ? count : 0 ) );
 }
 
 ibz2_reader*

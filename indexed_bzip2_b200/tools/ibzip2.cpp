@@ -57,7 +57,7 @@ const std::map<char, std::string> SHORT_NAMES = {
     { 'q', "quiet" }, { 'v', "verbose" }, { 'V', "version" }, { 'l', "list-compressed-offsets" }, { 'L', "list-offsets" },
 };
 const std::vector<std::string> WITH_VALUE = { "input", "output", "block-finder-parallelism", "decoder-parallelism",
-                                              "list-compressed-offsets", "list-offsets", "buffer-size" };
+                                              "list-compressed-offsets", "list-offsets", "buffer-size", "gpus" };
 
 bool
 takesValue( const std::string& name )
@@ -177,7 +177,9 @@ printHelp()
         "  -t, --test                    Test compressed file integrity.\n"
         "  -p, --block-finder-parallelism arg  Only for compatibility: the block finder is one GPU kernel.\n"
         "  -P, --decoder-parallelism arg  1 selects the serial reader (BZ2Reader), anything else the parallel reader\n"
-        "                                (ParallelBZ2Reader). The blocks are decoded on the GPU either way.\n\n"
+        "                                (ParallelBZ2Reader). The blocks are decoded on the GPU either way.\n"
+        "      --gpus arg                Number of GPUs (devices 0 .. arg - 1) that share the decoding of the parallel\n"
+        "                                reader. Not in the reference. Default: $IBZ2_GPUS, else 1.\n\n"
         " Output options:\n"
         "  -h, --help                    Print this help message.\n"
         "  -q, --quiet                   Suppress noncritical error messages.\n"
@@ -394,7 +396,16 @@ ibzip2CLI( int argc, char** argv )
         if ( decoderParallelism == 1 ) {
             reader = std::make_unique<BZ2Reader>( std::move( fileReader ) );
         } else {
-            auto parallelReader = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), decoderParallelism );
+            /* --gpus N (or $IBZ2_GPUS): devices 0 .. N - 1 share every large batch; new next to the reference */
+            std::vector<int> devices;
+            {
+                const char* const env = std::getenv( "IBZ2_GPUS" );
+                const auto gpus = std::stoul( arguments.value( "gpus", env != nullptr ? env : "1" ) );
+                for ( unsigned long d = 0; d < std::max( 1UL, gpus ); ++d ) {
+                    devices.push_back( static_cast<int>( d ) );
+                }
+            }
+            auto parallelReader = std::make_unique<ParallelBZ2Reader>( std::move( fileReader ), decoderParallelism, devices );
             /* the reference's parallel reader never looks at the stream CRC; this one does unless told not to */
             if ( const char* const env = std::getenv( "IBZ2_VERIFY_STREAM_CRC" ); ( env != nullptr ) && ( env[0] == '0' ) ) {
                 parallelReader->setVerifyStreamCRC( false );

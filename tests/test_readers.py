@@ -213,6 +213,28 @@ def test_seek_and_partial_reads(name, parallelization):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name", ["text-450k-l1", "pbzip2-style-5-streams", "multistream-b64-1B-empty-b64", "longruns-3M-l1"])
+def test_parallel_reader_over_several_devices(name, monkeypatch):
+    """ParallelBZ2Reader( ..., devices ) and `ibzip2 --gpus N`: every batch is cut into one part per device (here: two and
+    three contexts on the one GPU of the box, and parts of a single block), bytes and block map stay what they are."""
+    monkeypatch.setenv("IBZ2_MIN_BLOCKS_PER_DEVICE", "1")
+    want = GOLDEN[name]["parallel"]
+    for devices in ([0, 0], [0, 0, 0]):
+        f = ibz2.open(path(name), parallelization=4, gpus=devices)
+        data = f.read()
+        assert sha(data) == want["sha256"] and [list(kv) for kv in sorted(f.block_offsets().items())] == want["offsets"]
+        rng = np.random.default_rng(11)
+        for _ in range(10):
+            offset = int(rng.integers(0, max(1, len(data))))
+            f.seek(offset)
+            assert f.read(50_000) == data[offset:offset + 50_000]
+        f.close()
+    env = dict(os.environ, IBZ2_MIN_BLOCKS_PER_DEVICE="1")
+    out = subprocess.run([str(CLI), "-d", "-c", "-P", "4", "--gpus", "1", path(name)], capture_output=True, env=env)
+    assert out.returncode == 0 and sha(out.stdout) == want["sha256"]
+
+
+@pytest.mark.gpu
 def test_index_export_import_roundtrip(tmp_path):
     name = "pbzip2-style-5-streams"
     raw = orc.parallel_reader(open(path(name), "rb").read()).data
