@@ -160,6 +160,10 @@ int ibz2_memcpy_d2h( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbyte
  * (core/filereader/Shared.hpp:267-300): the compressed file goes to the GPU once, when a reader opens it. */
 int ibz2_upload_pageable( ibz2_ctx* ctx, void* dptr, const void* hptr, uint64_t nbytes );
 int ibz2_synchronize( ibz2_ctx* ctx );
+/* device -> PINNED host without waiting, on a stream of its own; ibz2_copy_synchronize waits for the copies queued so
+ * far.  For consumers that keep decoded blocks in HBM and hand out the bytes a read asks for (host/BlockSource.hpp). */
+int ibz2_memcpy_d2h_async( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbytes );
+int ibz2_copy_synchronize( ibz2_ctx* ctx );
 
 /* ---- K1: magic finder ----
  * Reports every bit offset p (MSB-first numbering, p + 48 <= 8 * nbytes) at which one of the selected 48-bit magics

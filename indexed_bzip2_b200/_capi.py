@@ -77,7 +77,7 @@ EXPORTS = [
     "ibz2_host_free_pinned", "ibz2_memcpy_h2d", "ibz2_memcpy_d2h", "ibz2_synchronize", "ibz2_find_magics",
     "ibz2_decode_blocks", "ibz2_decode_buffer", "ibz2_timer_start", "ibz2_timer_stop", "ibz2_debug_decode_block", "ibz2_read_stream_header", "ibz2_read_block_header",
     "ibz2_stream_crc_fold", "ibz2_set_verify_stream_crc", "ibz2_fold_stream_crcs",
-    "ibz2_upload_pageable", "ibz2_multi_create", "ibz2_multi_destroy", "ibz2_multi_last_error", "ibz2_multi_device_count",
+    "ibz2_upload_pageable", "ibz2_memcpy_d2h_async", "ibz2_copy_synchronize", "ibz2_multi_create", "ibz2_multi_destroy", "ibz2_multi_last_error", "ibz2_multi_device_count",
     "ibz2_multi_host_alloc_pinned", "ibz2_multi_host_free_pinned", "ibz2_multi_decode_buffer", "ibz2_multi_get_timings",
 ]
 
@@ -143,6 +143,10 @@ def load_library() -> C.CDLL:
     L.ibz2_set_verify_stream_crc.argtypes = [vp, i32]
     L.ibz2_fold_stream_crcs.restype = u64
     L.ibz2_fold_stream_crcs.argtypes = [vp, u64, i32]
+    L.ibz2_memcpy_d2h_async.restype = i32
+    L.ibz2_memcpy_d2h_async.argtypes = [vp, vp, vp, u64]
+    L.ibz2_copy_synchronize.restype = i32
+    L.ibz2_copy_synchronize.argtypes = [vp]
     L.ibz2_upload_pageable.restype = i32
     L.ibz2_upload_pageable.argtypes = [vp, vp, vp, u64]
     L.ibz2_multi_create.restype = i32

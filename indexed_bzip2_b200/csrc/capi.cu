@@ -625,6 +625,30 @@ ibz2_memcpy_d2h( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbytes )
     return IBZ2_OK;
 }
 
+/* device -> pinned host on the context's copy stream, without waiting: the building block of a consumer that hands a
+ * decoded batch on piece by piece (one piece travels while the previous one is written out) */
+int
+ibz2_memcpy_d2h_async( ibz2_ctx* ctx, void* hptr, const void* dptr, uint64_t nbytes )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( hptr, dptr, nbytes, cudaMemcpyDeviceToHost, ctx->copyStream ) );
+    return IBZ2_OK;
+}
+
+int
+ibz2_copy_synchronize( ibz2_ctx* ctx )
+{
+    if ( ctx == nullptr ) {
+        return IBZ2_E_INVALID_ARGUMENT;
+    }
+    cudaSetDevice( ctx->device );
+    IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( ctx->copyStream ) );
+    return IBZ2_OK;
+}
+
 int
 ibz2_synchronize( ibz2_ctx* ctx )
 {

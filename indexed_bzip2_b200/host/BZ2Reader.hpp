@@ -153,7 +153,9 @@ public:
                 const auto offsetInBlock = m_currentPosition - dataBlock->decodedOffset;
                 const auto n = std::min<size_t>( block.result->out_size - offsetInBlock, nBytesToRead - nBytesDecoded );
                 if ( writeFunctor ) {
-                    writeFunctor( block.data + offsetInBlock, n );
+                    m_source.deliver( block, offsetInBlock, n, [&writeFunctor] ( const uint8_t* bytes, size_t size ) {
+                        writeFunctor( bytes, size );
+                    } );
                 }
                 nBytesDecoded += n;
                 m_currentPosition += n;

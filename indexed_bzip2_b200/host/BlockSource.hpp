@@ -12,8 +12,10 @@
  *     caller that knows how far its read reaches (block map complete) says so, and the blocks of ONE read are decoded
  *     by ONE call;
  *   - decoded batches stay in a least-recently-used cache (the reference keeps max(16, P) blocks + 2 P prefetched
- *     ones, BlockFetcher.hpp:180-182; here up to MAX_CACHED_BATCHES batches inside a byte budget), each in its own
- *     pinned host buffer; the buffers of evicted batches are reused.
+ *     ones, BlockFetcher.hpp:180-182; here up to MAX_CACHED_BATCHES batches inside a byte budget) IN HBM, where they
+ *     were decoded; the buffers of evicted batches are reused.  Only the bytes a read asks for cross PCIe, through two
+ *     small pinned staging buffers (GpuDecoder::deliver): page-locking host memory for whole batches cost more than
+ *     decoding them (0.72 s per 2 GB against 0.125 s).
  * The file is not read into a private copy: paths and descriptors are memory-mapped, and the mapping goes to the GPU
  * through pinned staging buffers (ibz2_upload_pageable).  It must fit in HBM next to the decode scratch.
  */
@@ -45,11 +47,9 @@ public:
     static constexpr size_t BATCH_GROWTH_SHIFT = 3;       /* consecutive misses: 4, 32, 256, 2048 blocks */
     static constexpr size_t MAX_CACHED_BATCHES = 16;
     static constexpr size_t MIN_BLOCKS_PER_DEVICE = 64;   /* below this a batch stays on the first device */
-    /* Page-locking host memory is the slow part of a sequential read (measured: 0.72 s per 2 GB buffer against 0.125 s
-     * to decode the 2048 blocks that fill it), so the cache holds two large batches, whose buffers then take turns. */
     static constexpr size_t LARGE_BATCH_BYTES = 256ULL << 20;
-    static constexpr size_t MAX_LARGE_BATCHES = 2;
-    static constexpr size_t DEFAULT_CACHE_BYTES = 6ULL << 30;
+    static constexpr size_t MAX_LARGE_BATCHES = 4;
+    static constexpr size_t DEFAULT_CACHE_BYTES = 12ULL << 30;   /* of HBM, per device; $IBZ2_CACHE_BYTES */
 
     /** @p devices: the CUDA devices that share the decoding of every large batch (one entry: the usual case; an entry
      *  may repeat, which gives one GPU two contexts -- how the tests exercise the multi-device path on one GPU). */
@@ -188,8 +188,17 @@ public:
     struct Block
     {
         const ibz2_block_result* result{ nullptr };
-        const uint8_t* data{ nullptr };
+        const uint8_t* deviceData{ nullptr };   /* the block's decoded bytes, in the memory of device `decoder` */
+        size_t decoder{ 0 };
     };
+
+    /** Bytes [offset, offset + size) of a fetched block to @p sink( const uint8_t*, size_t ), in order, in pieces. */
+    template<typename Sink>
+    void
+    deliver( const Block& block, size_t offset, size_t size, const Sink& sink )
+    {
+        m_gpus[block.decoder]->deliver( block.deviceData + offset, size, sink );
+    }
 
     /**
      * The decoded block at @p encodedOffset; throws what the reference's decoder would have thrown for it.
@@ -252,7 +261,7 @@ public:
         const size_t parts = ( listed && ( count >= m_minBlocksPerDevice * m_gpus.size() ) ) ? m_gpus.size() : 1;
         std::vector<Batch> decoded( parts );
         if ( parts == 1 ) {
-            decoded[0].buffer = takeBuffer( count * 1000000ULL + 65536ULL );
+            decoded[0].buffer = takeBuffer( 0, count * 1000000ULL + 65536ULL );
             gpu().decode( batchOffsets, count, decoded[0].results, decoded[0].buffer );
         } else {
             std::vector<std::thread> workers;
@@ -261,7 +270,8 @@ public:
                 const size_t begin = count * d / parts;
                 const size_t end = count * ( d + 1 ) / parts;
                 gpu( d );   /* contexts and uploads are created here, one after the other */
-                decoded[d].buffer = takeBuffer( ( end - begin ) * 1000000ULL + 65536ULL );
+                decoded[d].decoder = d;
+                decoded[d].buffer = takeBuffer( d, ( end - begin ) * 1000000ULL + 65536ULL );
                 workers.emplace_back( [this, d, begin, end, batchOffsets, &decoded, &failures] () {
                     try {
                         m_gpus[d]->decode( batchOffsets + begin, end - begin, decoded[d].results, decoded[d].buffer );
@@ -328,9 +338,9 @@ public:
     close()
     {
         dropBatch();
-        if ( m_gpus[0] ) {
-            for ( auto& buffer : m_freeBuffers ) {
-                m_gpus[0]->freePinned( buffer );   /* pinned memory is portable: any context may free it */
+        for ( auto& spare : m_freeBuffers ) {
+            if ( m_gpus[spare.first] ) {
+                m_gpus[spare.first]->freeDevice( spare.second );
             }
         }
         m_freeBuffers.clear();
@@ -350,7 +360,8 @@ private:
     struct Batch
     {
         std::vector<ibz2_block_result> results;
-        GpuDecoder::PinnedBuffer buffer;
+        GpuDecoder::DeviceBuffer buffer;   /* in the memory of device `decoder` */
+        size_t decoder{ 0 };
         size_t bytes{ 0 };
     };
     using BatchList = std::list<Batch>;
@@ -368,7 +379,7 @@ private:
         if ( r.status != IBZ2_ST_OK ) {
             throwForStatus( r );
         }
-        return Block{ &r, static_cast<const uint8_t*>( batch.buffer.data ) + r.out_offset };
+        return Block{ &r, static_cast<const uint8_t*>( batch.buffer.data ) + r.out_offset, batch.decoder };
     }
 
     [[nodiscard]] static size_t
@@ -400,34 +411,36 @@ private:
         }
         m_cachedBytes -= std::min( m_cachedBytes, oldest.bytes );
         if ( oldest.buffer.data != nullptr ) {
-            m_freeBuffers.push_back( oldest.buffer );
+            m_freeBuffers.emplace_back( oldest.decoder, oldest.buffer );
         }
         m_batches.pop_back();
-        /* a few spare buffers are worth keeping (pinning memory is slow), the largest ones first */
-        if ( m_freeBuffers.size() > 4 ) {
-            const auto smallest = std::min_element( m_freeBuffers.begin(), m_freeBuffers.end(),
-                                                    [] ( const auto& a, const auto& b ) { return a.capacity < b.capacity; } );
-            gpu().freePinned( *smallest );
+        /* a few spare buffers are worth keeping, the largest ones first */
+        if ( m_freeBuffers.size() > 4 * m_gpus.size() ) {
+            const auto smallest = std::min_element( m_freeBuffers.begin(), m_freeBuffers.end(), [] ( const auto& a, const auto& b ) {
+                return a.second.capacity < b.second.capacity;
+            } );
+            m_gpus[smallest->first]->freeDevice( smallest->second );
             m_freeBuffers.erase( smallest );
         }
     }
 
-    /** The smallest spare buffer that is large enough, else a new one. */
-    GpuDecoder::PinnedBuffer
-    takeBuffer( size_t capacity )
+    /** The smallest spare buffer of device @p decoder that is large enough, else a new one. */
+    GpuDecoder::DeviceBuffer
+    takeBuffer( size_t decoder, size_t capacity )
     {
         auto best = m_freeBuffers.end();
         for ( auto it = m_freeBuffers.begin(); it != m_freeBuffers.end(); ++it ) {
-            if ( ( it->capacity >= capacity ) && ( ( best == m_freeBuffers.end() ) || ( it->capacity < best->capacity ) ) ) {
+            if ( ( it->first == decoder ) && ( it->second.capacity >= capacity )
+                 && ( ( best == m_freeBuffers.end() ) || ( it->second.capacity < best->second.capacity ) ) ) {
                 best = it;
             }
         }
         if ( best != m_freeBuffers.end() ) {
-            const auto buffer = *best;
+            const auto buffer = best->second;
             m_freeBuffers.erase( best );
             return buffer;
         }
-        return gpu().allocPinned( capacity );
+        return gpu( decoder ).allocDevice( capacity );
     }
 
     /* the compressed file on the host: a mapping, or bytes this object owns */
@@ -446,7 +459,7 @@ private:
 
     BatchList m_batches;   /* youngest first */
     std::unordered_map<uint64_t, std::pair<BatchList::iterator, size_t>> m_byOffset;
-    std::vector<GpuDecoder::PinnedBuffer> m_freeBuffers;
+    std::vector<std::pair<size_t, GpuDecoder::DeviceBuffer>> m_freeBuffers;   /* ( device of the set, buffer ) */
     size_t m_cachedBytes{ 0 };
     size_t m_cacheBudget{ DEFAULT_CACHE_BYTES };
     size_t m_minBlocksPerDevice{ MIN_BLOCKS_PER_DEVICE };

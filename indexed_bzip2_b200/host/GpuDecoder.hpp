@@ -131,34 +131,70 @@ public:
             if ( m_deviceData != nullptr ) {
                 ibz2_device_free( m_ctx, m_deviceData );
             }
+            for ( auto& buffer : m_staging ) {
+                if ( buffer != nullptr ) {
+                    ibz2_host_free_pinned( m_ctx, buffer );
+                }
+            }
             ibz2_destroy( m_ctx );
         }
     }
 
-    /** Page-locked host memory that a batch of decoded blocks lands in; owned by whoever asked for it. */
-    struct PinnedBuffer
+    /** Device memory that a batch of decoded blocks lands in; owned by whoever asked for it. */
+    struct DeviceBuffer
     {
         void* data{ nullptr };
         size_t capacity{ 0 };
     };
 
-    [[nodiscard]] PinnedBuffer
-    allocPinned( size_t capacity )
+    [[nodiscard]] DeviceBuffer
+    allocDevice( size_t capacity )
     {
-        const DebugTimer timer( "alloc pinned bytes", capacity );
-        PinnedBuffer buffer;
-        check( ibz2_host_alloc_pinned( m_ctx, capacity, &buffer.data ), "ibz2_host_alloc_pinned" );
+        const DebugTimer timer( "alloc device bytes", capacity );
+        DeviceBuffer buffer;
+        check( ibz2_device_alloc( m_ctx, capacity, &buffer.data ), "ibz2_device_alloc" );
         buffer.capacity = capacity;
         return buffer;
     }
 
     void
-    freePinned( PinnedBuffer& buffer )
+    freeDevice( DeviceBuffer& buffer )
     {
         if ( buffer.data != nullptr ) {
-            ibz2_host_free_pinned( m_ctx, buffer.data );
+            ibz2_device_free( m_ctx, buffer.data );
         }
-        buffer = PinnedBuffer{};
+        buffer = DeviceBuffer{};
+    }
+
+    /**
+     * Hands @p size decoded bytes that live in HBM at @p deviceData to @p sink, through two pinned staging buffers:
+     * one piece travels over PCIe while the sink (a write() to a descriptor, a memcpy into the caller's buffer) works on
+     * the piece before it.  Decoded blocks stay in HBM; only what a read asks for crosses the link.
+     */
+    template<typename Sink>
+    void
+    deliver( const uint8_t* deviceData, size_t size, const Sink& sink )
+    {
+        if ( size == 0 ) {
+            return;
+        }
+        if ( m_staging[0] == nullptr ) {
+            const DebugTimer timer( "alloc pinned bytes", 2 * STAGING_BYTES );
+            for ( auto& buffer : m_staging ) {
+                check( ibz2_host_alloc_pinned( m_ctx, STAGING_BYTES, &buffer ), "ibz2_host_alloc_pinned" );
+            }
+        }
+        const size_t pieces = ( size + STAGING_BYTES - 1 ) / STAGING_BYTES;
+        const auto pieceSize = [&] ( size_t k ) { return std::min( STAGING_BYTES, size - k * STAGING_BYTES ); };
+        check( ibz2_memcpy_d2h_async( m_ctx, m_staging[0], deviceData, pieceSize( 0 ) ), "ibz2_memcpy_d2h_async" );
+        for ( size_t k = 0; k < pieces; ++k ) {
+            check( ibz2_copy_synchronize( m_ctx ), "ibz2_copy_synchronize" );   /* piece k has arrived */
+            if ( k + 1 < pieces ) {
+                check( ibz2_memcpy_d2h_async( m_ctx, m_staging[( k + 1 ) & 1U], deviceData + ( k + 1 ) * STAGING_BYTES,
+                                              pieceSize( k + 1 ) ), "ibz2_memcpy_d2h_async" );
+            }
+            sink( static_cast<const uint8_t*>( m_staging[k & 1U] ), pieceSize( k ) );
+        }
     }
 
     GpuDecoder( const GpuDecoder& ) = delete;
@@ -203,12 +239,12 @@ public:
     }
 
     /**
-     * Decodes the blocks at @p offsets (bit offsets of their magics) into @p buffer, back to back; the buffer is
-     * replaced by a larger one when the blocks turn out to need it.
+     * Decodes the blocks at @p offsets (bit offsets of their magics) into the DEVICE buffer @p buffer, back to back; the
+     * buffer is replaced by a larger one when the blocks turn out to need it.
      * @p results gets one entry per block; failing blocks keep their status and do not fail the call.
      */
     void
-    decode( const uint64_t* offsets, size_t count, std::vector<ibz2_block_result>& results, PinnedBuffer& buffer )
+    decode( const uint64_t* offsets, size_t count, std::vector<ibz2_block_result>& results, DeviceBuffer& buffer )
     {
         const DebugTimer timer( "decode blocks", count );
         results.assign( count, ibz2_block_result{} );
@@ -218,7 +254,7 @@ public:
         for ( int attempt = 0; attempt < 2; ++attempt ) {
             uint64_t total = 0;
             check( ibz2_decode_blocks( m_ctx, m_deviceData, m_size, IBZ2_MEM_DEVICE, offsets, count, buffer.data,
-                                       buffer.capacity, IBZ2_MEM_HOST, results.data(), &total ),
+                                       buffer.capacity, IBZ2_MEM_DEVICE, results.data(), &total ),
                    "ibz2_decode_blocks" );
             const bool overflow = std::any_of( results.begin(), results.end(), [] ( const ibz2_block_result& r ) {
                 return r.status == IBZ2_ST_OUTPUT_CAPACITY;
@@ -227,8 +263,8 @@ public:
                 return;
             }
             /* RLE1 can expand a block 51-fold: now the sizes are known */
-            freePinned( buffer );
-            buffer = allocPinned( total + 65536ULL );
+            freeDevice( buffer );
+            buffer = allocDevice( total + 65536ULL );
         }
         throw std::runtime_error( "Decoded block sizes changed between two decodes of the same blocks" );
     }
@@ -259,8 +295,11 @@ private:
         }
     }
 
+    static constexpr size_t STAGING_BYTES = 16ULL << 20;
+
     ibz2_ctx* m_ctx{ nullptr };
     void* m_deviceData{ nullptr };
     size_t m_size{ 0 };
+    void* m_staging[2] = { nullptr, nullptr };
 };
 }  // namespace ibz2host

@@ -159,7 +159,6 @@ public:
             } else {
                 block = m_source.fetch( span.encodedOffsetInBits );
             }
-            const uint8_t* const blockBytes = block.data;
             const size_t blockSize = block.result->out_size;
 
             const auto offsetInBlock = m_currentPosition - span.decodedOffsetInBytes;
@@ -169,7 +168,10 @@ public:
             }
             const auto nBytesToDecode = std::min( blockSize - offsetInBlock, nBytesToRead - nBytesDecoded );
             if ( writeFunctor ) {
-                writeFunctor( blockBytes + offsetInBlock, nBytesToDecode );
+                /* the block lives in HBM: what this read wants of it comes over in pieces */
+                m_source.deliver( block, offsetInBlock, nBytesToDecode, [&writeFunctor] ( const uint8_t* bytes, size_t n ) {
+                    writeFunctor( bytes, n );
+                } );
             }
             nBytesDecoded += nBytesToDecode;
             m_currentPosition += nBytesToDecode;
