@@ -22,6 +22,7 @@ import ctypes as C
 import io
 import os
 import sys
+import tempfile
 from pathlib import Path
 
 __version__ = "1.7.0"
@@ -74,6 +75,8 @@ def _load():
         "ibz2r_set_block_offsets": (i32, [vp, C.POINTER(C.c_uint64), sz]),
         "ibz2r_join_threads": (i32, [vp]),
         "ibz2r_set_verify_stream_crc": (i32, [vp, i32]),
+        "ibz2r_export_index": (i32, [vp, C.c_char_p, i32]),
+        "ibz2r_import_index": (i32, [vp, C.c_char_p]),
         "ibz2r_set_open_device": (None, [i32]),
         "ibz2r_set_open_devices": (None, [C.POINTER(i32), i32]),
         "ibz2r_cli": (i32, [i32, C.POINTER(C.c_char_p)]),
@@ -269,24 +272,32 @@ class IndexedBzip2File(io.BufferedReader):
         # by BufferedReader or more specifically _BufferedIOMixin
         super().__init__(fobj, buffer_size=1024**2)
 
-    def export_index(self, file):
-        """The block map as the CLI's -L writes it: one "<encoded bits>,<decoded bytes>" line per entry."""
-        text = "".join(f"{bits},{nbytes}\n" for bits, nbytes in sorted(self.block_offsets().items()))
-        if hasattr(file, "write"):
-            file.write(text if isinstance(file, io.TextIOBase) else text.encode())
-        else:
-            Path(file).write_text(text)
+    def export_index(self, file, format="csv"):
+        """The block map as the CLI's -L writes it ("csv": one "<encoded bits>,<decoded bytes>" line per entry) or as a
+        GZIDX file ("gzidx": the indexed_gzip format rapidgzip reads and writes for bzip2 as well)."""
+        if format not in ("csv", "gzidx"):
+            raise ValueError("format must be 'csv' or 'gzidx'")
+        reader = self.bz2reader
+        if not hasattr(file, "write"):
+            reader._checked(reader._lib.ibz2r_export_index(reader._require(), os.fsencode(str(file)), int(format == "gzidx")))
+            return
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, "index")
+            reader._checked(reader._lib.ibz2r_export_index(reader._require(), os.fsencode(path), int(format == "gzidx")))
+            data = Path(path).read_bytes()
+        file.write(data.decode() if isinstance(file, io.TextIOBase) else data)
 
     def import_index(self, file):
-        text = file.read() if hasattr(file, "read") else Path(file).read_text()
-        if isinstance(text, bytes):
-            text = text.decode()
-        offsets = {}
-        for line in text.splitlines():
-            if line.strip():
-                bits, nbytes = line.split(",")
-                offsets[int(bits)] = int(nbytes)
-        self.set_block_offsets(offsets)
+        """Either format (told apart by the GZIDX magic); a GZIDX file must list every block, as export_index's do."""
+        reader = self.bz2reader
+        if not hasattr(file, "read"):
+            reader._checked(reader._lib.ibz2r_import_index(reader._require(), os.fsencode(str(file))))
+            return
+        data = file.read()
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, "index")
+            Path(path).write_bytes(data.encode() if isinstance(data, str) else bytes(data))
+            reader._checked(reader._lib.ibz2r_import_index(reader._require(), os.fsencode(path)))
 
 
 def open(filename, parallelization=1, *, device=None, verify_stream_crc=True, gpus=None):

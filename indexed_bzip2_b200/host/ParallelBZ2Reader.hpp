@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "BlockIndex.hpp"
+#include "IndexFileFormat.hpp"
 #include "BZ2ReaderInterface.hpp"
 #include "BlockSource.hpp"
 
@@ -291,29 +292,53 @@ public:
         m_source.dropBatch();
     }
 
-    /** New next to the reference: the index as the text the CLI's -L writes, one "bits,bytes" pair per line. */
+    /**
+     * New next to the reference's bzip2 readers (its gzip reader has them, ParallelGzipReader.hpp:993-1029): the block
+     * map as the text `ibzip2 -L` writes, one "bits,bytes" pair per line, or as a GZIDX file (IndexFileFormat.hpp).
+     */
     void
-    exportIndex( std::ostream& out )
+    exportIndex( std::ostream& out, IndexFormat format = IndexFormat::OFFSET_LINES )
     {
-        for ( const auto& [bits, bytes] : blockOffsets() ) {
+        const auto offsets = blockOffsets();
+        if ( format == IndexFormat::GZIDX ) {
+            writeGzidx( out, offsets, m_source.fileSize() );
+            return;
+        }
+        for ( const auto& [bits, bytes] : offsets ) {
             out << bits << "," << bytes << "\n";
         }
     }
 
+    /** Either format, told apart by the GZIDX magic. */
     void
     importIndex( std::istream& in )
     {
         std::map<size_t, size_t> offsets;
-        std::string line;
-        while ( std::getline( in, line ) ) {
-            if ( line.empty() ) {
-                continue;
+        if ( in.peek() == 'G' ) {
+            offsets = readGzidx( in );
+            /* rapidgzip's checkpoints for bzip2 are chunk starts: some block boundaries, not all.  This reader decodes
+             * block by block, so every data block needs its entry (as in the files exportIndex writes). */
+            const auto& found = m_source.finderOffsets();
+            size_t listed = 0;
+            for ( const auto offset : found ) {
+                listed += offsets.count( offset );
             }
-            const auto comma = line.find( ',' );
-            if ( comma == std::string::npos ) {
-                throw std::invalid_argument( "Index lines must look like <bits>,<bytes>" );
+            if ( listed != found.size() ) {
+                throw std::invalid_argument( "The index does not list every bzip2 block of the file (a chunk-level index "
+                                             "as rapidgzip writes it?); only block-level indexes can be imported." );
             }
-            offsets.emplace( std::stoull( line.substr( 0, comma ) ), std::stoull( line.substr( comma + 1 ) ) );
+        } else {
+            std::string line;
+            while ( std::getline( in, line ) ) {
+                if ( line.empty() ) {
+                    continue;
+                }
+                const auto comma = line.find( ',' );
+                if ( comma == std::string::npos ) {
+                    throw std::invalid_argument( "Index lines must look like <bits>,<bytes>" );
+                }
+                offsets.emplace( std::stoull( line.substr( 0, comma ) ), std::stoull( line.substr( comma + 1 ) ) );
+            }
         }
         setBlockOffsets( std::move( offsets ) );
     }

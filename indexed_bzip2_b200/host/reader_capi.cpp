@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstring>
 #include <cstdlib>
+#include <fstream>
 #include <memory>
 #include <vector>
 #include <new>
@@ -302,6 +303,99 @@ ibz2r_set_block_offsets( ibz2_reader* r, const uint64_t* pairs, size_t count )
         std::map<size_t, size_t> offsets;
         for ( size_t i = 0; i < count; ++i ) {
             offsets.emplace( pairs[2 * i], pairs[2 * i + 1] );
+        }
+        r->reader->setBlockOffsets( std::move( offsets ) );
+        return 0LL;
+    } ) );
+}
+
+/* ---- test hooks (no GPU): the GZIDX writer and reader on plain offset pairs ---- */
+int
+ibz2r_gzidx_write( const uint64_t* pairs, size_t count, uint64_t compressedSizeInBytes, const char* path )
+{
+    try {
+        std::map<size_t, size_t> offsets;
+        for ( size_t i = 0; i < count; ++i ) {
+            offsets.emplace( pairs[2 * i], pairs[2 * i + 1] );
+        }
+        std::ofstream out( path, std::ios::binary );
+        writeGzidx( out, offsets, compressedSizeInBytes );
+        return 0;
+    } catch ( const std::exception& e ) {
+        g_openError = e.what();
+        return -1;
+    }
+}
+
+long long
+ibz2r_gzidx_read( const char* path, uint64_t* pairs, size_t capacity )
+{
+    try {
+        std::ifstream in( path, std::ios::binary );
+        const auto offsets = readGzidx( in );
+        size_t i = 0;
+        for ( const auto& [bits, bytes] : offsets ) {
+            if ( i < capacity ) {
+                pairs[2 * i] = bits;
+                pairs[2 * i + 1] = bytes;
+            }
+            ++i;
+        }
+        return static_cast<long long>( offsets.size() );
+    } catch ( const std::exception& e ) {
+        g_openError = e.what();
+        return -1;
+    }
+}
+
+/* The block map to / from an index file: format 0 = the "<bits>,<bytes>" lines of `ibzip2 -L`, 1 = GZIDX (IndexFileFormat.hpp).
+ * The import tells the formats apart by the magic bytes. */
+int
+ibz2r_export_index( ibz2_reader* r, const char* path, int format )
+{
+    return static_cast<int>( guarded( r->lastError, r->lastKind, [&] () {
+        std::ofstream out( path, std::ios::binary );
+        if ( !out ) {
+            throw std::invalid_argument( std::string( "Cannot open index file for writing: " ) + path );
+        }
+        if ( r->parallel != nullptr ) {
+            r->parallel->exportIndex( out, format == 1 ? IndexFormat::GZIDX : IndexFormat::OFFSET_LINES );
+        } else if ( format == 1 ) {
+            const auto offsets = r->reader->blockOffsets();
+            /* the serial reader's map has no end-of-stream entries and ends at the last block's end: the same checkpoints */
+            writeGzidx( out, offsets, offsets.empty() ? 0 : ( offsets.rbegin()->first + 7U ) / 8U );
+        } else {
+            for ( const auto& [bits, bytes] : r->reader->blockOffsets() ) {
+                out << bits << "," << bytes << "\n";
+            }
+        }
+        return 0LL;
+    } ) );
+}
+
+int
+ibz2r_import_index( ibz2_reader* r, const char* path )
+{
+    return static_cast<int>( guarded( r->lastError, r->lastKind, [&] () {
+        std::ifstream in( path, std::ios::binary );
+        if ( !in ) {
+            throw std::invalid_argument( std::string( "Cannot open index file: " ) + path );
+        }
+        if ( r->parallel != nullptr ) {
+            r->parallel->importIndex( in );
+            return 0LL;
+        }
+        std::map<size_t, size_t> offsets;
+        if ( in.peek() == 'G' ) {
+            offsets = readGzidx( in );
+        } else {
+            std::string line;
+            while ( std::getline( in, line ) ) {
+                const auto comma = line.find( ',' );
+                if ( comma != std::string::npos ) {
+                    offsets.emplace( std::stoull( line.substr( 0, comma ) ), std::stoull( line.substr( comma + 1 ) ) );
+                }
+            }
         }
         r->reader->setBlockOffsets( std::move( offsets ) );
         return 0LL;

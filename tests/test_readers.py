@@ -335,3 +335,113 @@ def test_cli_output_file_rules(tmp_path):
     assert subprocess.run([str(CLI), "-d", "-f", str(source)], capture_output=True).returncode == 0
     piped = subprocess.run([str(CLI), "-d", "-c"], input=source.read_bytes(), capture_output=True)
     assert piped.returncode == 0 and piped.stdout == raw               # standard input -> standard output
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GZIDX (rapidgzip/IndexFileFormat.hpp:37-64): written here, read by the compiled reference, and back
+# ---------------------------------------------------------------------------------------------------------------
+
+REF_GZIDX = ROOT / "oracle" / "_ref" / "libref_gzidx.so"
+
+
+def ref_gzidx():
+    lib = C.CDLL(str(REF_GZIDX))
+    lib.refgz_last_error.restype = C.c_char_p
+    lib.refgz_reads_with_index.restype = C.c_int
+    lib.refgz_reads_with_index.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p,
+                                           C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.refgz_export_index.restype = C.c_int
+    lib.refgz_export_index.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    return lib
+
+
+def gzidx_write(offsets, compressed_size, target):
+    lib = ibz2._load()
+    lib.ibz2r_gzidx_write.restype = C.c_int
+    lib.ibz2r_gzidx_write.argtypes = [C.POINTER(C.c_uint64), C.c_size_t, C.c_uint64, C.c_char_p]
+    flat = (C.c_uint64 * (2 * len(offsets)))(*[x for pair in offsets for x in pair])
+    assert lib.ibz2r_gzidx_write(flat, len(offsets), compressed_size, os.fsencode(str(target))) == 0
+
+
+def gzidx_read(source):
+    lib = ibz2._load()
+    lib.ibz2r_gzidx_read.restype = C.c_longlong
+    lib.ibz2r_gzidx_read.argtypes = [C.c_char_p, C.POINTER(C.c_uint64), C.c_size_t]
+    pairs = (C.c_uint64 * 8192)()
+    count = lib.ibz2r_gzidx_read(os.fsencode(str(source)), pairs, 4096)
+    assert count >= 0
+    return [[pairs[2 * i], pairs[2 * i + 1]] for i in range(count)]
+
+
+@pytest.mark.parametrize("name", [n for n in VALID if GOLDEN[n]["parallel"]["size"] > 0 and not n.startswith("err-")])
+def test_gzidx_written_here_is_read_by_the_reference(name, tmp_path):
+    """The block map of the reference's ParallelBZ2Reader (golden), written as GZIDX by our writer: one checkpoint per
+    data block and the end of the file, layout byte for byte as IndexFileFormat.hpp:37-64 describes it; the reference's
+    gzip-architecture reader imports it and returns the right bytes at random offsets (needs oracle/_ref/libref_gzidx.so)."""
+    want = GOLDEN[name]["parallel"]
+    offsets = want["offsets"]
+    compressed_size = GOLDEN[name]["compressed_size"]
+    index = tmp_path / "index.gzidx"
+    gzidx_write(offsets, compressed_size, index)
+    blob = index.read_bytes()
+    data_blocks = [o for i, o in enumerate(offsets) if i + 1 == len(offsets) or offsets[i + 1][1] != o[1]]
+    assert blob[:7] == b"GZIDX\x01\x00" and len(blob) == 35 + 18 * len(data_blocks)
+    assert int.from_bytes(blob[7:15], "little") == compressed_size
+    assert int.from_bytes(blob[15:23], "little") == want["size"]
+    assert int.from_bytes(blob[27:31], "little") == 32768 and int.from_bytes(blob[31:35], "little") == len(data_blocks)
+    for i, (bits, nbytes) in enumerate(data_blocks):
+        entry = blob[35 + 18 * i:35 + 18 * (i + 1)]
+        assert int.from_bytes(entry[:8], "little") * 8 - entry[16] == bits and entry[16] < 8 and entry[17] == 0
+        assert int.from_bytes(entry[8:16], "little") == nbytes
+    assert gzidx_read(index) == data_blocks
+    if not REF_GZIDX.exists():
+        pytest.skip("oracle/_ref/libref_gzidx.so not built (needs zlib)")
+    raw = orc.parallel_reader(open(path(name), "rb").read()).data
+    rng = np.random.default_rng(3)
+    size = min(4096, len(raw))
+    positions = np.sort(rng.integers(0, len(raw) - size + 1, 6)).astype(np.uint64)
+    out = np.zeros(size, dtype=np.uint8)
+    checksum, decoded = C.c_uint64(0), C.c_uint64(0)
+    lib = ref_gzidx()
+    rc = lib.refgz_reads_with_index(os.fsencode(path(name)), os.fsencode(str(index)), 2, positions.ctypes.data, len(positions),
+                                    size, out.ctypes.data, C.byref(checksum), C.byref(decoded))
+    assert rc == 0, lib.refgz_last_error()
+    assert decoded.value == len(raw)
+    assert out.tobytes() == raw[int(positions[0]):int(positions[0]) + size]
+    assert checksum.value == sum(sum(raw[int(p):int(p) + size]) for p in positions)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["text-450k-l1", "pbzip2-style-5-streams", "multistream-b64-1B-empty-b64", "ref-1B"])
+def test_gzidx_export_import_through_the_readers(name, tmp_path):
+    raw = orc.parallel_reader(open(path(name), "rb").read()).data
+    first = ibz2.open(path(name), parallelization=4)
+    index = tmp_path / "index.gzidx"
+    first.export_index(index, format="gzidx")
+    want = GOLDEN[name]["parallel"]["offsets"]
+    assert gzidx_read(index) == [o for i, o in enumerate(want) if i + 1 == len(want) or want[i + 1][1] != o[1]]
+    for parallelization in (4, 1):
+        second = ibz2.open(path(name), parallelization=parallelization)
+        second.import_index(index)
+        assert second.block_offsets_complete() and second.size() == len(raw)
+        rng = np.random.default_rng(9)
+        for _ in range(8):
+            offset = int(rng.integers(0, len(raw)))
+            second.seek(offset)
+            assert second.read(3000) == raw[offset:offset + 3000]
+    buffer = io.BytesIO()
+    first.export_index(buffer, format="gzidx")
+    assert buffer.getvalue() == index.read_bytes()
+    if REF_GZIDX.exists():
+        # the reference's own index of the same file: chunk starts only.  One block per chunk: importable; else refused.
+        theirs = tmp_path / "theirs.gzidx"
+        assert ref_gzidx().refgz_export_index(os.fsencode(path(name)), os.fsencode(str(theirs)), 2) == 0
+        third = ibz2.open(path(name), parallelization=4)
+        blocks = sum(1 for i, o in enumerate(want[:-1]) if want[i + 1][1] != o[1])
+        if len(gzidx_read(theirs)) == blocks + 1:
+            third.import_index(theirs)
+            third.seek(len(raw) // 3)
+            assert third.read(1000) == raw[len(raw) // 3:len(raw) // 3 + 1000]
+        else:
+            with pytest.raises(ValueError, match="does not list every bzip2 block"):
+                third.import_index(theirs)
