@@ -15,6 +15,7 @@
 #include <string>
 
 #include "BZ2Reader.hpp"
+#include "Bzip2Chunk.hpp"
 #include "ParallelBZ2Reader.hpp"
 
 using namespace ibz2host;
@@ -305,6 +306,54 @@ ibz2r_set_block_offsets( ibz2_reader* r, const uint64_t* pairs, size_t count )
             offsets.emplace( pairs[2 * i], pairs[2 * i + 1] );
         }
         r->reader->setBlockOffsets( std::move( offsets ) );
+        return 0LL;
+    } ) );
+}
+
+/* ---- Bzip2Chunk::decodeChunk for FFI callers and the tests: one chunk of a file on disk ----
+ * info[0..3] = encodedOffsetInBits, encodedSizeInBits, decodedSizeInBytes, stoppedPreemptively;
+ * boundaries / footers: ( encoded offset, decoded offset ) pairs; counts[0..1] = how many there are of each.
+ * Returns 0, or -1 with ibz2r_last_error( NULL ) / ibz2r_last_error_kind( NULL ) set. */
+int
+ibz2r_decode_chunk( const char* path, uint64_t chunkOffset, uint64_t untilOffset, uint64_t maxDecompressedChunkSize,
+                    uint64_t* info, uint64_t* boundaries, size_t boundariesCapacity, uint64_t* footers, size_t footersCapacity,
+                    uint64_t* counts, uint8_t* out, uint64_t outCapacity )
+{
+    return static_cast<int>( guarded( g_openError, g_openKind, [&] () {
+        std::ifstream in( path, std::ios::binary );
+        if ( !in ) {
+            throw std::invalid_argument( std::string( "Cannot open " ) + path );
+        }
+        const std::vector<char> file( ( std::istreambuf_iterator<char>( in ) ), std::istreambuf_iterator<char>() );
+        const auto* const bytes = reinterpret_cast<const uint8_t*>( file.data() );
+        GpuDecoder decoder( openDevice() );
+        decoder.upload( bytes, file.size() );
+        const auto blocks = decoder.findBlocks();
+        auto chunk = Bzip2Chunk::decodeChunk( decoder, bytes, file.size(), blocks, chunkOffset, untilOffset,
+                                              maxDecompressedChunkSize );
+        info[0] = chunk.encodedOffsetInBits;
+        info[1] = chunk.encodedSizeInBits;
+        info[2] = chunk.decodedSizeInBytes;
+        info[3] = chunk.stoppedPreemptively ? 1 : 0;
+        counts[0] = chunk.blockBoundaries.size();
+        counts[1] = chunk.footers.size();
+        for ( size_t i = 0; i < std::min( boundariesCapacity, chunk.blockBoundaries.size() ); ++i ) {
+            boundaries[2 * i] = chunk.blockBoundaries[i].encodedOffset;
+            boundaries[2 * i + 1] = chunk.blockBoundaries[i].decodedOffset;
+        }
+        for ( size_t i = 0; i < std::min( footersCapacity, chunk.footers.size() ); ++i ) {
+            footers[2 * i] = chunk.footers[i].encodedOffset;
+            footers[2 * i + 1] = chunk.footers[i].decodedOffset;
+        }
+        if ( out != nullptr ) {
+            uint64_t written = 0;
+            decoder.deliver( static_cast<const uint8_t*>( chunk.data.data ), std::min<uint64_t>( chunk.decodedSizeInBytes, outCapacity ),
+                             [&] ( const uint8_t* piece, size_t n ) {
+                std::memcpy( out + written, piece, n );
+                written += n;
+            } );
+        }
+        decoder.freeDevice( chunk.data );
         return 0LL;
     } ) );
 }

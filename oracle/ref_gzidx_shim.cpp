@@ -67,6 +67,35 @@ refgz_reads_with_index( const char* path, const char* indexPath, int paralleliza
     }
 }
 
+/* The chunk map of the reference's gzip-architecture reader for a bzip2 file read with chunks of `chunkSizeInBytes`
+ * compressed bytes: ( encoded bit offset, decoded byte offset ) pairs incl. the end of the file.  Every entry is where
+ * Bzip2Chunk::decodeChunk (rapidgzip/chunkdecoding/Bzip2Chunk.hpp:200-268) started a chunk. */
+int
+refgz_chunk_offsets( const char* path, int parallelization, uint64_t chunkSizeInBytes, uint64_t* pairs, uint64_t capacity,
+                     uint64_t* count )
+{
+    try {
+        using namespace rapidgzip;
+        ParallelGzipReader<ChunkData> reader( std::make_unique<StandardFileReader>( std::string( path ) ),
+                                              static_cast<size_t>( parallelization ), chunkSizeInBytes );
+        reader.read( -1, nullptr, std::numeric_limits<size_t>::max() );
+        const auto offsets = reader.blockOffsets();
+        uint64_t i = 0;
+        for ( const auto& [encoded, decoded] : offsets ) {
+            if ( i < capacity ) {
+                pairs[2 * i] = encoded;
+                pairs[2 * i + 1] = decoded;
+            }
+            ++i;
+        }
+        *count = i;
+        return 0;
+    } catch ( const std::exception& e ) {
+        g_lastError = e.what();
+        return 1;
+    }
+}
+
 /* The reference's own GZIDX export for a bzip2 file (chunk-level checkpoints). */
 int
 refgz_export_index( const char* path, const char* indexPath, int parallelization )

@@ -445,3 +445,65 @@ def test_gzidx_export_import_through_the_readers(name, tmp_path):
         else:
             with pytest.raises(ValueError, match="does not list every bzip2 block"):
                 third.import_index(theirs)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Bzip2Chunk::decodeChunk (rapidgzip/chunkdecoding/Bzip2Chunk.hpp:200-268) on the GPU, against the chunk map of the
+# compiled reference's gzip-architecture reader
+# ---------------------------------------------------------------------------------------------------------------
+
+def decode_chunk(name, chunk_offset, until_offset, max_size=(1 << 64) - 1, out_capacity=1 << 22):
+    lib = ibz2._load()
+    lib.ibz2r_decode_chunk.restype = C.c_int
+    lib.ibz2r_decode_chunk.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64),
+                                       C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(C.c_uint64), C.c_size_t,
+                                       C.POINTER(C.c_uint64), C.c_void_p, C.c_uint64]
+    info, counts = (C.c_uint64 * 4)(), (C.c_uint64 * 2)()
+    boundaries, footers = (C.c_uint64 * 2048)(), (C.c_uint64 * 2048)()
+    out = np.zeros(out_capacity, dtype=np.uint8)
+    rc = lib.ibz2r_decode_chunk(os.fsencode(path(name)), chunk_offset, until_offset, max_size, info, boundaries, 1024, footers,
+                                1024, counts, out.ctypes.data, out_capacity)
+    if rc != 0:
+        raise RuntimeError((lib.ibz2r_last_error(None) or b"").decode())
+    return {"encoded_offset": info[0], "encoded_size": info[1], "decoded_size": info[2], "stopped": bool(info[3]),
+            "boundaries": [(boundaries[2 * i], boundaries[2 * i + 1]) for i in range(counts[0])],
+            "footers": [(footers[2 * i], footers[2 * i + 1]) for i in range(counts[1])],
+            "data": out[:min(info[2], out_capacity)].tobytes()}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["text-450k-l1", "pbzip2-style-5-streams", "multistream-b64-1B-empty-b64", "mixed-384k-l2"])
+def test_bzip2_chunk_adapter_matches_the_reference_chunk_map(name):
+    if not REF_GZIDX.exists():
+        pytest.skip("oracle/_ref/libref_gzidx.so not built (needs zlib)")
+    lib = ref_gzidx()
+    lib.refgz_chunk_offsets.restype = C.c_int
+    lib.refgz_chunk_offsets.argtypes = [C.c_char_p, C.c_int, C.c_uint64, C.POINTER(C.c_uint64), C.c_uint64, C.POINTER(C.c_uint64)]
+    pairs, count = (C.c_uint64 * 4096)(), C.c_uint64(0)
+    # 8 KiB chunks: the reference cuts these small files into several chunks (a chunk holds at least one block)
+    assert lib.refgz_chunk_offsets(os.fsencode(path(name)), 2, 8192, pairs, 2048, C.byref(count)) == 0, lib.refgz_last_error()
+    chunks = [(pairs[2 * i], pairs[2 * i + 1]) for i in range(count.value)]
+    raw = orc.parallel_reader(open(path(name), "rb").read()).data
+    assert chunks[-1][1] == len(raw) and len(chunks) >= 2
+    want_map = GOLDEN[name]["parallel"]["offsets"]
+    for (start, decoded_start), (end, decoded_end) in zip(chunks, chunks[1:]):
+        got = decode_chunk(name, start, end)
+        assert got["encoded_offset"] == start and got["encoded_offset"] + got["encoded_size"] == end
+        if decoded_start == decoded_end:
+            # a chunk that starts at an end-of-stream block and holds nothing else (the reference's map has such entries)
+            assert got["decoded_size"] == 0 and got["boundaries"] == [] and len(got["footers"]) >= 1
+            continue
+        assert got["decoded_size"] == decoded_end - decoded_start and got["data"] == raw[decoded_start:decoded_end]
+        assert not got["stopped"]
+        # every block boundary inside the chunk is one of the reference's ParallelBZ2Reader block-map entries
+        inside = [(b, d - decoded_start) for b, d in want_map if start < b < end and (b, d) != (end, decoded_end)]
+        data_blocks = [(b, d) for (b, d), nxt in zip(want_map, want_map[1:]) if nxt[1] != d and start < b < end]
+        assert got["boundaries"] == [(b, d - decoded_start) for b, d in data_blocks]
+        assert all(f[1] <= got["decoded_size"] for f in got["footers"]) and len(inside) >= len(got["boundaries"])
+    # the whole file as one chunk, cut short by the size limit; and a range without any block
+    whole = decode_chunk(name, chunks[0][0], chunks[-1][0])
+    assert whole["decoded_size"] == len(raw) and whole["data"] == raw[:1 << 22]
+    limited = decode_chunk(name, chunks[0][0], chunks[-1][0], max_size=1)
+    assert limited["stopped"] and 0 < limited["decoded_size"] < len(raw) and limited["data"] == raw[:limited["decoded_size"]]
+    with pytest.raises(RuntimeError, match="Failed to find any valid bzip2 block"):
+        decode_chunk(name, chunks[-1][0], chunks[-1][0] + 1000)
