@@ -10,7 +10,8 @@
  *     access and more and more on consecutive access: every miss that continues where the last batch ended decodes
  *     eight times as many blocks as the one before, up to MAX_BATCH_BLOCKS; any other access starts small again.  A
  *     caller that knows how far its read reaches (block map complete) says so, and the blocks of ONE read are decoded
- *     by ONE call;
+ *     by ONE call.  Once the batches are large, the next one is decoded by a second host thread while the caller
+ *     consumes the current one;
  *   - decoded batches stay in a least-recently-used cache (the reference keeps max(16, P) blocks + 2 P prefetched
  *     ones, BlockFetcher.hpp:180-182; here up to MAX_CACHED_BATCHES batches inside a byte budget) IN HBM, where they
  *     were decoded; the buffers of evicted batches are reused.  Only the bytes a read asks for cross PCIe, through two
@@ -63,6 +64,9 @@ public:
         }
         if ( const char* const env = std::getenv( "IBZ2_CACHE_BYTES" ); env != nullptr ) {
             m_cacheBudget = std::max<size_t>( 1, std::strtoull( env, nullptr, 10 ) );
+        }
+        if ( const char* const env = std::getenv( "IBZ2_PREFETCH_MIN_BLOCKS" ); env != nullptr ) {
+            m_prefetchMinBlocks = std::strtoull( env, nullptr, 10 );
         }
         if ( const char* const env = std::getenv( "IBZ2_MIN_BLOCKS_PER_DEVICE" ); env != nullptr ) {
             m_minBlocksPerDevice = std::max<size_t>( 1, std::strtoull( env, nullptr, 10 ) );
@@ -157,6 +161,7 @@ public:
     void
     setFinderOffsets( std::vector<uint64_t> offsets )
     {
+        joinPrefetch( false );   /* it reads the list that is about to be replaced */
         m_finderOffsets = std::move( offsets );
         m_finderReady = true;
         m_finderLimit = std::numeric_limits<size_t>::max();
@@ -167,6 +172,7 @@ public:
     void
     dropBatch()
     {
+        joinPrefetch( false );
         while ( !m_batches.empty() ) {
             evictOldest();
         }
@@ -215,6 +221,16 @@ public:
             ++m_hits;
             return checked( *cached->second.first, cached->second.second );
         }
+        /* the batch a second thread has been decoding while the caller worked on the last one (Prefetcher.hpp: the
+         * prefetch cache is looked at before anything is decoded on demand, BlockFetcher.hpp:262-280) */
+        if ( joinPrefetch( true ) ) {
+            if ( const auto cached = m_byOffset.find( encodedOffset ); cached != m_byOffset.end() ) {
+                m_batches.splice( m_batches.begin(), m_batches, cached->second.first );
+                ++m_prefetchHits;
+                startPrefetch();
+                return checked( *cached->second.first, cached->second.second );
+            }
+        }
         ++m_misses;
 
         const auto& offsets = finderOffsets();
@@ -259,6 +275,7 @@ public:
          * device like the worker threads of the reference's pool (core/BlockFetcher.hpp:176-190).  Small batches are
          * not worth it: a decode call costs one block's Huffman chain however few blocks it holds. */
         const size_t parts = ( listed && ( count >= m_minBlocksPerDevice * m_gpus.size() ) ) ? m_gpus.size() : 1;
+        /* (a prefetch, which only exists with one device, has been joined above: the contexts are this thread's) */
         std::vector<Batch> decoded( parts );
         if ( parts == 1 ) {
             decoded[0].buffer = takeBuffer( 0, count * 1000000ULL + 65536ULL );
@@ -306,6 +323,9 @@ public:
                 && ( ( m_batches.size() > MAX_CACHED_BATCHES ) || ( m_cachedBytes > m_cacheBudget )
                      || ( largeBatches() > MAX_LARGE_BATCHES * parts ) ) ) {
             evictOldest();
+        }
+        if ( listed && ( parts == 1 ) && ( m_sequentialFetches > 0 ) ) {
+            startPrefetch();
         }
         return checked( *inserted, wantedEntry.second );
     }
@@ -380,6 +400,86 @@ private:
             throwForStatus( r );
         }
         return Block{ &r, static_cast<const uint8_t*>( batch.buffer.data ) + r.out_offset, batch.decoder };
+    }
+
+    /**
+     * Consecutive access with large batches: the batch behind the last one is decoded by a second host thread while the
+     * caller consumes the current one (its bytes leave through the copy stream and the staging buffers, which the decode
+     * does not touch).  One device only; like the reference's prefetches it is dropped when the access pattern changes.
+     */
+    void
+    startPrefetch()
+    {
+        if ( ( m_gpus.size() != 1 ) || m_prefetchPending || ( m_prefetchMinBlocks == 0 ) ) {
+            return;
+        }
+        const auto& offsets = finderOffsets();
+        const size_t limit = finderCount();
+        const size_t first = m_nextSequentialBlock;
+        if ( first >= limit ) {
+            return;
+        }
+        const size_t largest = std::min<size_t>( MAX_BATCH_BLOCKS, std::max<size_t>( 256, roundUpToPowerOfTwo( limit / 8U ) ) );
+        size_t count = std::min( largest, limit - first );
+        for ( size_t i = 0; i < count; ++i ) {
+            if ( m_byOffset.count( offsets[first + i] ) != 0 ) {
+                count = i;
+                break;
+            }
+        }
+        if ( count < std::min( m_prefetchMinBlocks, limit - first ) ) {
+            return;
+        }
+        m_prefetched = Batch{};
+        m_prefetched.buffer = takeBuffer( 0, count * 1000000ULL + 65536ULL );
+        m_prefetchFailure = nullptr;
+        m_prefetchFirst = first;
+        m_prefetchCount = count;
+        m_prefetchPending = true;
+        GpuDecoder* const decoder = &gpu();
+        const uint64_t* const batchOffsets = offsets.data() + first;
+        m_prefetchThread = std::thread( [this, decoder, batchOffsets, count] () {
+            try {
+                decoder->decode( batchOffsets, count, m_prefetched.results, m_prefetched.buffer );
+            } catch ( ... ) {
+                m_prefetchFailure = std::current_exception();
+            }
+        } );
+    }
+
+    /** Waits for a running prefetch; @p keep: its batch enters the cache.  @return whether one did. */
+    bool
+    joinPrefetch( bool keep )
+    {
+        if ( !m_prefetchPending ) {
+            return false;
+        }
+        m_prefetchThread.join();
+        m_prefetchPending = false;
+        if ( !keep || m_prefetchFailure ) {
+            /* a failed prefetch is simply forgotten: the blocks are decoded again when they are asked for, and then the
+             * failure surfaces where the reference's would */
+            if ( m_prefetched.buffer.data != nullptr ) {
+                m_freeBuffers.emplace_back( 0, m_prefetched.buffer );
+            }
+            m_prefetched = Batch{};
+            return false;
+        }
+        m_prefetched.bytes = m_prefetched.buffer.capacity;
+        m_batches.push_front( std::move( m_prefetched ) );
+        m_prefetched = Batch{};
+        const auto inserted = m_batches.begin();
+        for ( size_t i = 0; i < inserted->results.size(); ++i ) {
+            m_byOffset[inserted->results[i].enc_offset_bits] = { inserted, i };
+        }
+        m_cachedBytes += inserted->bytes;
+        m_nextSequentialBlock = m_prefetchFirst + m_prefetchCount;
+        while ( ( m_batches.size() > 1 )
+                && ( ( m_batches.size() > MAX_CACHED_BATCHES ) || ( m_cachedBytes > m_cacheBudget )
+                     || ( largeBatches() > MAX_LARGE_BATCHES ) ) ) {
+            evictOldest();
+        }
+        return true;
     }
 
     [[nodiscard]] static size_t
@@ -468,5 +568,14 @@ private:
     size_t m_expected{ 0 };
     size_t m_hits{ 0 };
     size_t m_misses{ 0 };
+    size_t m_prefetchHits{ 0 };
+
+    std::thread m_prefetchThread;
+    Batch m_prefetched;
+    std::exception_ptr m_prefetchFailure;
+    size_t m_prefetchFirst{ 0 };
+    size_t m_prefetchCount{ 0 };
+    size_t m_prefetchMinBlocks{ 256 };   /* batches smaller than this are not prefetched; $IBZ2_PREFETCH_MIN_BLOCKS, 0 = never */
+    bool m_prefetchPending{ false };
 };
 }  // namespace ibz2host

@@ -9,7 +9,8 @@
  * host then lays out what the reference's ChunkData carries for bzip2:
  *   encodedOffsetInBits / encodedSizeInBits   where the chunk really starts and how far it reaches
  *   decodedSizeInBytes + the bytes            (the bytes stay in HBM; deliver() hands them out)
- *   blockBoundaries                           ( encoded offset, decoded offset ) of every block but the first
+ *   blockBoundaries                           ( encoded offset, decoded offset ) of every block, end-of-stream blocks
+ *                                             included, in front of which the chunk already holds data
  *                                             (ChunkData::appendDeflateBlockBoundary, Bzip2Chunk.hpp:119-121)
  *   footers                                   ( bit position behind an end-of-stream block, decoded offset )
  *                                             (Bzip2Chunk.hpp:125-131)
@@ -73,12 +74,17 @@ public:
         /* the data blocks that start inside the range; the reference tries chunkOffset itself and then looks for the
          * next magic (Bzip2Chunk.hpp:225-258), which comes to the same list */
         Bzip2ChunkData result;
-        /* end-of-stream blocks and stream headers from @p position on belong to the chunk (Bzip2Chunk.hpp:123-138) */
+        /* end-of-stream blocks and stream headers from @p position on belong to the chunk (Bzip2Chunk.hpp:123-138),
+         * but nothing that starts exactly at untilOffset does (the second half of the stop condition,
+         * Bzip2Chunk.hpp:112-114): an end-of-stream block there opens the next chunk */
         const auto skipStreamEnds = [&] ( uint64_t position, uint64_t decodedSoFar ) {
-            while ( position + 48U + 32U <= fileSize * 8ULL ) {
+            while ( ( position + 48U + 32U <= fileSize * 8ULL ) && ( ( position != untilOffset ) || ( position == chunkOffset ) ) ) {
                 const auto header = GpuDecoder::probeHeader( fileData, fileSize, position );
                 if ( ( header.status != IBZ2_ST_OK ) || ( header.is_eos == 0 ) ) {
                     break;
+                }
+                if ( decodedSoFar > 0 ) {
+                    result.blockBoundaries.push_back( { position, decodedSoFar } );
                 }
                 position = header.enc_offset_bits + header.enc_size_bits;
                 result.footers.push_back( { position, decodedSoFar } );
@@ -139,7 +145,7 @@ public:
                 decoder.freeDevice( result.data );
                 throwForStatus( r );
             }
-            if ( i > 0 ) {
+            if ( decoded > 0 ) {
                 result.blockBoundaries.push_back( { r.enc_offset_bits, decoded } );
             }
             decoded += r.out_size;

@@ -106,3 +106,30 @@ def test_config5_multistream_random_access(tmp_path):
         assert second.read(1 << 20) == raw[offset:offset + (1 << 20)].tobytes()
     assert second.seek(raw.size - 10) == raw.size - 10 and second.read() == raw[-10:].tobytes()
     second.close()
+
+
+def test_sequential_read_with_prefetch_thread(tmp_path, monkeypatch):
+    """Consecutive reads: once a batch has been decoded on demand, the next one is decoded by a second host thread while the
+    caller consumes the current one (host/BlockSource.hpp startPrefetch; the reference's FetchNextAdaptive,
+    core/Prefetcher.hpp:159-176).  Here the threshold is lowered so that a 64 MB file already gets there; bytes, block map
+    and a seek back into an evicted region must be what they are without it."""
+    w = benchdata.build_single_stream("mixed", 7, 64 << 20, 1, 9)
+    path = tmp_path / "stream.bz2"
+    w.compressed.tofile(path)
+    raw = w.raw_base.tobytes()
+    maps = []
+    for min_blocks in ("1", "0"):
+        monkeypatch.setenv("IBZ2_PREFETCH_MIN_BLOCKS", min_blocks)
+        f = ibz2.open(str(path), parallelization=4)
+        got = bytearray()
+        while True:
+            piece = f.read(3_000_000)
+            if not piece:
+                break
+            got += piece
+        assert bytes(got) == raw
+        maps.append(f.block_offsets())
+        f.seek(1_000_000)
+        assert f.read(100) == raw[1_000_000:1_000_100]
+        f.close()
+    assert maps[0] == maps[1] and len(maps[0]) == w.blocks + 2
