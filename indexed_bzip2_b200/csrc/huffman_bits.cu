@@ -508,6 +508,338 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
     }
 }
 
+/*
+ * K2b for launches with few blocks -- one CTA per bzip2 block, the bit positions of a whole group of 50 symbols looked up at
+ * once.
+ *
+ * One lane per block is as fast as a single dependent chain of ~12 instructions per symbol gets (71 cycles per symbol on
+ * an otherwise idle SM: 33 ms for a block of 900 k symbols however few blocks there are to decode -- the latency of a random
+ * read, and all of a 100 MB file).  With SMs to spare the chain itself is shortened instead:
+ *   A  thread r of 512 looks at bit offset r behind the (word-aligned) start of the group AS IF a symbol started there:
+ *      nine bits -> code length -> ring1[r] = { offset of the symbol behind it, 1 symbol }; a bit pattern that is not a plain
+ *      symbol of at most nine bits (longer code, end-of-block symbol, no code) points at itself with 0 symbols;
+ *   B..D  pointer doubling: ring2[r] = ring1 o ring1, ring4 = ring2 o ring2, ring8 = ring4 o ring4, counts added;
+ *   the chain: one warp follows ring8 six times and ring2 once from the group's first bit: 50 symbols in 7 dependent
+ *      shared-memory loads instead of 50 x ( load + shift + address ).  The counts tell whether all hops were whole; if not
+ *      (an exceptional symbol, the end of the block) the group is walked one symbol at a time through ring1 and
+ *      decodeOneSymbol, which is also what a table switch in the middle of the ring amounts to;
+ *   output: thread s < 50 walks from the chain's stop before symbol s & ~7 to symbol s through ring4/ring2/ring1 and stores
+ *      the entry of the offset it arrives at, while the chain warp is already busy with the next group (the rings are
+ *      double buffered).
+ * The group is the unit because the table switches every 50 symbols at a bit position only the chain knows
+ * (bzip2.hpp:710-721): 512 offsets cover 31 + 50 x 9 bits.  Same entries, same exits to the careful decoder as the
+ * lane-per-block kernel above; ~20 instructions per symbol instead of 12, so it only pays while SMs would otherwise idle.
+ */
+constexpr int GRP_THREADS = 512;
+constexpr uint32_t GRP_RING = GRP_THREADS;       /* bit offsets per group */
+constexpr uint32_t GRP_LEVELS = 4;               /* hops of 1, 2, 4, 8 symbols */
+constexpr uint32_t GRP_WORDS = 256;              /* staged big-endian words of the file (a ring) */
+constexpr uint32_t GRP_REFILL = 64;
+constexpr uint32_t GRP_POS_MASK = 2U * GRP_RING - 1U;   /* an entry = byte offset of the target's entry | symbols << 10 */
+constexpr uint32_t GRP_COUNT_SHIFT = 10;
+constexpr uint32_t GRP_CAREFUL_STOP = GRP_RING - 32U;
+constexpr uint32_t GRP_BLOCKS_PER_SM = 8;         /* launches with up to this many blocks per SM take this kernel */   /* the careful walk re-bases the ring behind this offset */
+static_assert( 31U + GROUP_SIZE * HUFF_LUT_BITS < GRP_RING, "a group of plain symbols must fit the ring" );
+static_assert( GRP_CAREFUL_STOP + HUFF_LUT_BITS <= GRP_RING, "no plain symbol in front of the stop leaves the ring" );
+
+struct GroupShared
+{
+    alignas( 16 ) uint8_t dec[DEC_STRIDE];
+    uint32_t words[GRP_WORDS];
+    uint16_t ring[2][GRP_LEVELS][GRP_RING];
+    uint16_t idx[2][GRP_RING];
+    uint16_t coarse[2][8];
+    unsigned long long nextBit;
+    uint32_t left;       /* symbols the current selector still covers */
+    uint32_t outcome;    /* 0 = go on, 1 = end-of-block symbol seen, 2 = careful decoder */
+    uint32_t nsym;
+    uint32_t fast;       /* the group just finished took the fast path: its entries are still to be stored */
+    uint32_t block;
+};
+
+__device__ __forceinline__ uint32_t
+ringLoad( const uint16_t* ring, uint32_t byteOffset )
+{
+    return *reinterpret_cast<const uint16_t*>( reinterpret_cast<const uint8_t*>( ring ) + byteOffset );
+}
+
+/* entries of a group that took the fast path; called by 64 threads with s = 0..63 */
+__device__ __forceinline__ void
+storeGroupEntries( const GroupShared& sh, uint32_t set, uint32_t s, uint32_t table, uint16_t* __restrict__ out )
+{
+    if ( s >= GROUP_SIZE ) {
+        return;
+    }
+    const uint32_t hop = s < 48U ? ( s >> 3 ) : 6U;
+    const uint32_t within = s < 48U ? ( s & 7U ) : s - 48U;
+    uint32_t p2 = sh.coarse[set][hop];
+    if ( ( within & 4U ) != 0 ) {
+        p2 = ringLoad( sh.ring[set][2], p2 ) & GRP_POS_MASK;
+    }
+    if ( ( within & 2U ) != 0 ) {
+        p2 = ringLoad( sh.ring[set][1], p2 ) & GRP_POS_MASK;
+    }
+    if ( ( within & 1U ) != 0 ) {
+        p2 = ringLoad( sh.ring[set][0], p2 ) & GRP_POS_MASK;
+    }
+    out[s] = static_cast<uint16_t>( ( table << HUFF_LUT_BITS ) | ringLoad( sh.idx[set], p2 ) );
+}
+
+__global__ void __launch_bounds__( GRP_THREADS, 2 )
+huffmanGroupsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta* __restrict__ meta, uint32_t nblocks,
+                     const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
+                     uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, const uint32_t* __restrict__ order )
+{
+    __shared__ GroupShared sh;
+    const uint32_t t = threadIdx.x;
+    const uint32_t decAddr = static_cast<uint32_t>( __cvta_generic_to_shared( sh.dec ) );
+    const uint64_t nbits = nbytes * 8U;
+
+    while ( true ) {
+        __syncthreads();   /* everybody is done with the previous block's shared state */
+        if ( t == 0 ) {
+            sh.block = atomicAdd( counter, 1U );
+        }
+        __syncthreads();
+        uint32_t block = sh.block;
+        if ( block >= nblocks ) {
+            break;
+        }
+        if ( order != nullptr ) {
+            block = order[block];
+        }
+        BlockMeta& bm = meta[block];
+        const BlockTables* const bt = tablesAll + block;
+        {
+            /* one thread looks and tells: what it writes below must not split the CTA */
+            if ( t == 0 ) {
+                uint32_t skip = ( ( bm.status != IBZ2_ST_OK ) || ( bm.isEos != 0 ) ) ? 1U : 0U;
+                if ( ( skip == 0 ) && ( bt->symbolCount == 0 ) ) {
+                    bm.status = ST_INTERNAL_CAREFUL;   /* see huffmanBitsKernel */
+                    skip = 1;
+                }
+                sh.outcome = skip;
+            }
+            __syncthreads();
+            if ( sh.outcome != 0 ) {
+                continue;
+            }
+        }
+        const uint32_t symbolCount = bt->symbolCount;
+        const uint32_t groupCount = bt->groupCount;
+        const uint32_t selectorsCount = bt->selectorsCount;
+        const uint8_t* const selectors = selectorsAll + static_cast<uint64_t>( block ) * SEL_STRIDE;
+        uint16_t* const symOut = reinterpret_cast<uint16_t*>( reinterpret_cast<uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE )
+                                                              + K2_SYM16_OFFSET );
+        {
+            /* the same tables as one decoder of huffmanBitsKernel keeps, built by all threads */
+            const uint4* const src = reinterpret_cast<const uint4*>( &bt->lut[0][0] );
+            uint32_t* const dst = reinterpret_cast<uint32_t*>( sh.dec );
+            for ( uint32_t q = t; q < groupCount * ( HUFF_LUT_SIZE / 8U ); q += GRP_THREADS ) {
+                const uint4 v = __ldg( src + q );
+                const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+                uint32_t lens[2] = { 0, 0 };
+#pragma unroll
+                for ( uint32_t i = 0; i < 4U; ++i ) {
+                    const uint32_t a = ( ( w[i] & 0xFFFFU ) >> 5 ) > symbolCount ? 0U : ( w[i] & 31U );
+                    const uint32_t b = ( w[i] >> 21 ) > symbolCount ? 0U : ( ( w[i] >> 16 ) & 31U );
+                    lens[i >> 1] |= ( a | ( b << 8 ) ) << ( 16U * ( i & 1U ) );
+                }
+                dst[2U * q] = lens[0];
+                dst[2U * q + 1U] = lens[1];
+            }
+            for ( uint32_t i = t; i < groupCount * LONG_LIMITS; i += GRP_THREADS ) {
+                const uint32_t g = i / LONG_LIMITS;
+                const uint64_t limit = bt->limit[g][LONG_FIRST_LEN + i % LONG_LIMITS];
+                *reinterpret_cast<uint32_t*>( sh.dec + DEC_LIM_OFFSET + i * 4U ) = static_cast<uint32_t>( limit >> 12 );
+            }
+            for ( uint32_t i = t; i < groupCount * LONG_OFFSETS; i += GRP_THREADS ) {
+                const uint32_t g = i / LONG_OFFSETS;
+                *reinterpret_cast<uint16_t*>( sh.dec + DEC_OFF_OFFSET + i * 2U ) = bt->offset[g][LONG_FIRST_LEN + 1U + i % LONG_OFFSETS];
+            }
+            if ( t < groupCount ) {
+                *reinterpret_cast<uint16_t*>( sh.dec + DEC_EOB_OFFSET + t * 2U ) = bt->eobPerm[t];
+            }
+        }
+        const uint64_t startBit = bt->dataStartBit;
+        uint64_t loadedUpTo = ( startBit >> 5 ) + GRP_WORDS;   /* words in front of this one are staged */
+        for ( uint32_t i = t; i < GRP_WORDS; i += GRP_THREADS ) {
+            const uint64_t w = ( startBit >> 5 ) + i;
+            sh.words[w & ( GRP_WORDS - 1U )] = bswap( loadWordRaw( data, nbytes, w ) );
+        }
+        if ( t == 0 ) {
+            sh.nextBit = startBit;
+            sh.left = GROUP_SIZE;
+            sh.outcome = 0;
+            sh.nsym = 0;
+            sh.fast = 0;
+        }
+        uint32_t selIdx = 0;
+        uint32_t tableAhead = selectorsCount > 0 ? selectors[0] : 0U;   /* the selector of the next fresh group, loaded early */
+        uint32_t table = 0;
+        uint32_t set = 0;
+        uint32_t prevFast = 0;
+        uint32_t prevTable = 0;
+        uint32_t prevNsym = 0;
+        uint32_t outcome = 0;
+        uint32_t nsym = 0;
+        uint64_t X = startBit;
+        bool pending = false;
+        uint32_t pendingRaw = 0;
+        __syncthreads();
+
+        while ( true ) {
+            X = sh.nextBit;
+            const uint32_t left = sh.left;
+            outcome = sh.outcome;
+            nsym = sh.nsym;
+            if ( outcome != 0 ) {
+                break;
+            }
+            if ( left == GROUP_SIZE ) {
+                /* next group of 50 symbols: switch the table (bzip2.hpp:710-721) */
+                if ( ( selIdx >= selectorsCount ) || ( nsym >= SYM_LIMIT ) || ( X > nbits ) ) {
+                    outcome = 2;
+                    break;
+                }
+                table = tableAhead;
+                ++selIdx;
+                tableAhead = selIdx < selectorsCount ? selectors[selIdx] : 0U;
+            }
+            const uint64_t baseWord = X >> 5;
+            const uint32_t r0 = static_cast<uint32_t>( X & 31U );
+
+            /* the staged words run GRP_REFILL at a time, loaded in one iteration and stored in the next; the slots they
+             * overwrite hold words in front of baseWord (fewer than 160 are staged ahead when a load is issued) */
+            if ( pending ) {
+                if ( t < GRP_REFILL ) {
+                    sh.words[( loadedUpTo + t ) & ( GRP_WORDS - 1U )] = bswap( pendingRaw );
+                }
+                loadedUpTo += GRP_REFILL;
+                pending = false;
+            }
+            if ( loadedUpTo - baseWord < 160U ) {
+                if ( t < GRP_REFILL ) {
+                    pendingRaw = loadWordRaw( data, nbytes, loadedUpTo + t );
+                } else if ( ( t < GRP_REFILL + 2U ) && ( ( loadedUpTo + 2U * GRP_REFILL ) * 4U < nbytes ) ) {
+                    asm volatile( "prefetch.global.L2 [%0];" ::"l"( data + ( loadedUpTo + GRP_REFILL + ( t - GRP_REFILL ) * 32U ) * 4U ) );
+                }
+                pending = true;
+            }
+
+            /* A: every bit offset of the ring as a symbol start */
+            uint32_t e;
+            {
+                const uint32_t w = t >> 5;
+                const uint32_t wa = sh.words[( baseWord + w ) & ( GRP_WORDS - 1U )];
+                const uint32_t wb = sh.words[( baseWord + w + 1U ) & ( GRP_WORDS - 1U )];
+                const uint32_t hi = __funnelshift_l( wb, wa, t & 31U );
+                const uint32_t idx = hi >> ( 32 - HUFF_LUT_BITS );
+                const uint32_t len = sh.dec[table * HUFF_LUT_SIZE + idx];
+                const uint32_t target = t + len;
+                e = ( ( len != 0 ) && ( target < GRP_RING ) ) ? ( ( target * 2U ) | ( 1U << GRP_COUNT_SHIFT ) ) : t * 2U;
+                sh.ring[set][0][t] = static_cast<uint16_t>( e );
+                sh.idx[set][t] = static_cast<uint16_t>( idx );
+            }
+            __syncthreads();
+            /* B..D: hops of 2, 4, 8 symbols */
+#pragma unroll
+            for ( uint32_t level = 1; level < GRP_LEVELS; ++level ) {
+                const uint32_t f = ringLoad( sh.ring[set][level - 1U], e & GRP_POS_MASK );
+                e = f + ( e & ~GRP_POS_MASK );
+                sh.ring[set][level][t] = static_cast<uint16_t>( e );
+                __syncthreads();
+            }
+
+            if ( t < 32U ) {
+                /* the chain */
+                uint32_t p2 = r0 * 2U;
+                uint32_t count = 0;
+                if ( left == GROUP_SIZE ) {
+#pragma unroll
+                    for ( uint32_t hop = 0; hop < 6U; ++hop ) {
+                        if ( t == 0 ) {
+                            sh.coarse[set][hop] = static_cast<uint16_t>( p2 );
+                        }
+                        const uint32_t f = ringLoad( sh.ring[set][3], p2 );
+                        count += f >> GRP_COUNT_SHIFT;
+                        p2 = f & GRP_POS_MASK;
+                    }
+                    if ( t == 0 ) {
+                        sh.coarse[set][6] = static_cast<uint16_t>( p2 );
+                    }
+                    const uint32_t f = ringLoad( sh.ring[set][1], p2 );
+                    count += f >> GRP_COUNT_SHIFT;
+                    p2 = f & GRP_POS_MASK;
+                }
+                if ( count == GROUP_SIZE ) {
+                    if ( t == 0 ) {
+                        sh.nextBit = baseWord * 32U + ( p2 >> 1 );
+                        sh.nsym = nsym + GROUP_SIZE;
+                        sh.fast = 1;
+                    }
+                } else {
+                    /* one symbol at a time: plain ones through ring1, the others through decodeOneSymbol */
+                    uint32_t p = r0;
+                    uint32_t done = 0;
+                    uint32_t what = SYM_PLAIN;
+                    uint16_t* const out = symOut + nsym;
+                    while ( ( done < left ) && ( p < GRP_CAREFUL_STOP ) ) {
+                        const uint32_t f = sh.ring[set][0][p];
+                        if ( ( f >> GRP_COUNT_SHIFT ) != 0 ) {
+                            if ( t == 0 ) {
+                                out[done] = static_cast<uint16_t>( ( table << HUFF_LUT_BITS ) | sh.idx[set][p] );
+                            }
+                            p = ( f & GRP_POS_MASK ) >> 1;
+                            ++done;
+                            continue;
+                        }
+                        const uint32_t w = p >> 5;
+                        uint32_t pos = p & 31U;
+                        uint32_t entry = 0;
+                        what = decodeOneSymbol( sh.words[( baseWord + w ) & ( GRP_WORDS - 1U )],
+                                                sh.words[( baseWord + w + 1U ) & ( GRP_WORDS - 1U )], pos, decAddr, table, bt, &entry );
+                        p = ( p & ~31U ) + pos;
+                        if ( what != SYM_PLAIN ) {
+                            break;
+                        }
+                        if ( t == 0 ) {
+                            out[done] = static_cast<uint16_t>( entry );
+                        }
+                        ++done;
+                    }
+                    if ( t == 0 ) {
+                        sh.nextBit = baseWord * 32U + p;
+                        sh.nsym = nsym + done;
+                        sh.fast = 0;
+                        sh.outcome = what == SYM_PLAIN ? 0U : ( what == SYM_EOB ? 1U : 2U );
+                        sh.left = done < left ? left - done : GROUP_SIZE;
+                    }
+                }
+            } else if ( ( t < 96U ) && ( prevFast != 0 ) ) {
+                storeGroupEntries( sh, set ^ 1U, t - 32U, prevTable, symOut + prevNsym );
+            }
+            __syncthreads();
+            prevFast = sh.fast;
+            prevTable = table;
+            prevNsym = nsym;
+            set ^= 1U;
+        }
+
+        if ( ( prevFast != 0 ) && ( t >= 32U ) && ( t < 96U ) ) {
+            storeGroupEntries( sh, set ^ 1U, t - 32U, prevTable, symOut + prevNsym );
+        }
+        if ( t == 0 ) {
+            if ( ( outcome == 1 ) && ( X <= nbits ) ) {
+                bm.nCoded = nsym;
+                bm.endBit = X;
+            } else {
+                bm.status = ST_INTERNAL_CAREFUL;
+            }
+        }
+    }
+}
+
 /* What K2b stored per symbol -> the symbol itself: ( table << 9 ) | index goes through K2a's 9-bit table, 0x8000 | table <<
  * 9 | rank through perm (HuffmanCodingSymbolsPerLength.hpp:105-124).  One pass over the symbol arrays with 16-byte
  * accesses; the 9 KB of tables of a block stay in L1. */
@@ -564,6 +896,24 @@ void
 launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32_t nblocks, const uint8_t* selectors,
                    const BlockTables* tables, uint32_t* scratch, uint32_t* counter, bool ordered, cudaStream_t stream )
 {
+    /* few blocks per SM: a CTA per block (huffmanGroupsKernel); many: a lane per block.  IBZ2_K2B_KERNEL = lanes | groups
+     * forces one of them (the tests run both), IBZ2_K2B_GROUPS_PER_SM moves the switch. */
+    {
+        const char* const which = std::getenv( "IBZ2_K2B_KERNEL" );
+        const char* const perSm = std::getenv( "IBZ2_K2B_GROUPS_PER_SM" );
+        const uint32_t limit = static_cast<uint32_t>( smCount() ) * ( perSm != nullptr ? std::strtoul( perSm, nullptr, 10 ) : GRP_BLOCKS_PER_SM );
+        const bool groups = ( which != nullptr ) && ( which[0] == 'g' ) ? true
+                            : ( which != nullptr ) && ( which[0] == 'l' ) ? false : nblocks <= limit;
+        if ( groups ) {
+            cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
+            const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() * 2 ), nblocks ) );
+            huffmanGroupsKernel<<<ctas, GRP_THREADS, 0, stream>>>( data, nbytes, meta, nblocks, selectors, tables, scratch, counter,
+                                                                 ordered ? counter + K2B_ORDER_OFFSET : nullptr );
+            const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
+            resolveSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
+            return;
+        }
+    }
     const size_t shared = SH_TOTAL_BYTES;
     static const int lanes = [] () {
         const char* const env = std::getenv( "IBZ2_K2B_LANES" );

@@ -5,6 +5,7 @@ compiled reference (tests/golden/golden.json).  Bit-exact: all of this is intege
 Run on the B200 box: python -m pytest tests -m gpu
 """
 import hashlib
+import os
 import json
 
 import numpy as np
@@ -27,14 +28,18 @@ def case(name):
     return (orc.ROOT / "tests" / "golden" / "cases" / f"{name}.bz2").read_bytes()
 
 
-@pytest.fixture(scope="module")
-def ctx():
+# K2b has two kernels, a lane per block for launches with many blocks and a CTA per block for launches with few
+# (csrc/huffman_bits.cu); the launches of this file are all small, so each kernel is forced in turn
+@pytest.fixture(scope="module", params=["lanes", "groups"])
+def ctx(request):
+    os.environ["IBZ2_K2B_KERNEL"] = request.param
     c = _capi.Context(0)
     # these tests compare block by block with the oracle's decode_block, which knows nothing about streams: the library's
     # stream CRC verdict (IBZ2_ST_STREAM_CRC on the last block of a stream) is switched on where it is the subject
     c.set_verify_stream_crc(False)
     yield c
     c.close()
+    os.environ.pop("IBZ2_K2B_KERNEL", None)
 
 
 def split_found(found):
