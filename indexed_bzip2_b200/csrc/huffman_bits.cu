@@ -537,8 +537,10 @@ constexpr uint32_t GRP_WORDS = 256;              /* staged big-endian words of t
 constexpr uint32_t GRP_REFILL = 64;
 constexpr uint32_t GRP_POS_MASK = 2U * GRP_RING - 1U;   /* an entry = byte offset of the target's entry | symbols << 10 */
 constexpr uint32_t GRP_COUNT_SHIFT = 10;
-constexpr uint32_t GRP_CAREFUL_STOP = GRP_RING - 32U;
-constexpr uint32_t GRP_BLOCKS_PER_SM = 8;         /* launches with up to this many blocks per SM take this kernel */   /* the careful walk re-bases the ring behind this offset */
+constexpr uint32_t GRP_CAREFUL_STOP = GRP_RING - 32U;   /* the careful walk re-bases the ring behind this offset */
+/* launches with up to this many blocks per SM take this kernel.  Measured on config 3's blocks: 1133 blocks (7.7 per SM)
+ * 74.0 ms here against 37.4 ms a lane per block, 2266 blocks 134 against 43.9; 112 blocks (config 1) 12.3 against 33.0 */
+constexpr uint32_t GRP_BLOCKS_PER_SM = 2;
 static_assert( 31U + GROUP_SIZE * HUFF_LUT_BITS < GRP_RING, "a group of plain symbols must fit the ring" );
 static_assert( GRP_CAREFUL_STOP + HUFF_LUT_BITS <= GRP_RING, "no plain symbol in front of the stop leaves the ring" );
 
