@@ -172,6 +172,26 @@ int ibz2_copy_synchronize( ibz2_ctx* ctx );
 int ibz2_find_magics( ibz2_ctx* ctx, const void* data, uint64_t nbytes, int data_mem, uint64_t base_bit_offset,
                       uint32_t which, uint64_t* offsets, uint64_t capacity, uint64_t* count );
 
+/* ---- K1 without allocation ----
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same kernel and the
+ * same result as ibz2_find_magics, without a context: the match list and its counter live in a device array of fixed
+ * size that is part of the library image (512.25 KB on every GPU that loads the library, until the process exits), so the
+ * call allocates nothing, neither on the device nor through a library.
+ *   device        CUDA device that holds device_data (made current for the call, the caller's device is restored)
+ *   stream        a cudaStream_t of that device, or NULL for the default stream; the call waits for it before returning
+ *   device_data   DEVICE memory only (the call stages nothing); nbytes bytes
+ *   offsets       HOST array of `capacity` entries, capacity <= IBZ2_NOALLOC_MAX_MATCHES: a larger capacity is refused
+ *                 with IBZ2_E_CAPACITY before anything runs (an 8 GB `bzip2 -9` file has ~9100 magics)
+ *   *count        the number of magics found; IBZ2_E_CAPACITY if it is larger than capacity (offsets then holds
+ *                 `capacity` of them in ascending order, not necessarily the first ones)
+ * All calls on one device share the array: calls that overlap on the GPU (two streams, two threads) race and must be
+ * serialised by the caller.  The first call on a device resolves the array's address (cudaGetSymbolAddress); make it
+ * outside a stream capture.  ibz2_last_error( NULL ) describes a failure on the calling thread. */
+#define IBZ2_NOALLOC_MAX_MATCHES 65536U
+int ibz2_find_magics_noalloc( int device, void* stream, const void* device_data, uint64_t nbytes, uint64_t base_bit_offset,
+                              uint32_t which, uint64_t* offsets, uint64_t capacity, uint64_t* count );
+
 /* ---- K2..K6: decode a batch of blocks ----
  * data/nbytes: the compressed file (or a window of it); block_bit_offsets: HOST array of nblocks bit offsets into
  * data at which a block (or EOS) magic is expected.  Decoded bytes of block i go to out + results[i].out_offset;

@@ -79,6 +79,7 @@ EXPORTS = [
     "ibz2_stream_crc_fold", "ibz2_set_verify_stream_crc", "ibz2_fold_stream_crcs",
     "ibz2_upload_pageable", "ibz2_memcpy_d2h_async", "ibz2_copy_synchronize", "ibz2_multi_create", "ibz2_multi_destroy", "ibz2_multi_last_error", "ibz2_multi_device_count",
     "ibz2_multi_host_alloc_pinned", "ibz2_multi_host_free_pinned", "ibz2_multi_decode_buffer", "ibz2_multi_get_timings",
+    "ibz2_find_magics_noalloc",
 ]
 
 _lib = None
@@ -123,6 +124,8 @@ def load_library() -> C.CDLL:
     L.ibz2_synchronize.argtypes = [vp]
     L.ibz2_find_magics.restype = i32
     L.ibz2_find_magics.argtypes = [vp, vp, u64, i32, u64, u32, vp, u64, C.POINTER(u64)]
+    L.ibz2_find_magics_noalloc.restype = i32
+    L.ibz2_find_magics_noalloc.argtypes = [i32, vp, vp, u64, u64, u32, vp, u64, C.POINTER(u64)]
     L.ibz2_decode_blocks.restype = i32
     L.ibz2_decode_blocks.argtypes = [vp, vp, u64, i32, vp, u64, vp, u64, i32, vp, C.POINTER(u64)]
     L.ibz2_decode_buffer.restype = i32
@@ -448,6 +451,23 @@ class MultiContext:
         self._check(self.lib.ibz2_multi_get_timings(self.handle, C.byref(t), per, len(self.devices)))
         return {"decode_ms": t.decode_ms, "copy_ms": t.copy_ms, "total_ms": t.total_ms,
                 "stream_crc_mismatches": int(t.stream_crc_mismatches), "devices": [p.as_dict() for p in per]}
+
+
+NOALLOC_MAX_MATCHES = 65536
+
+
+def find_magics_noalloc(device: int, dptr: int, nbytes: int, *, which: int = FIND_BLOCK | FIND_EOS, base_bit_offset: int = 0,
+                        capacity: int = NOALLOC_MAX_MATCHES, stream: int = 0) -> np.ndarray:
+    """ibz2_find_magics_noalloc: K1 over DEVICE memory with the scratch in a static device array; no context, no
+    allocation inside the call.  Sorted bit offsets like Context.find_magics."""
+    lib = load_library()
+    out = np.empty(max(capacity, 1), dtype=np.uint64)
+    count = C.c_uint64()
+    rc = lib.ibz2_find_magics_noalloc(device, stream or None, dptr or None, nbytes, base_bit_offset, which,
+                                      out.ctypes.data if capacity else None, capacity, C.byref(count))
+    if rc != 0:
+        raise Ibz2Error(rc, (lib.ibz2_last_error(None) or b"").decode())
+    return out[:count.value].copy()
 
 
 def fold_stream_crcs(results: np.ndarray, verify: bool = True) -> int:

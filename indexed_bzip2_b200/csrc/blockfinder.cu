@@ -18,6 +18,10 @@
  */
 #include "common.cuh"
 
+#include <algorithm>
+#include <cstdio>
+#include <mutex>
+
 namespace ibz2
 {
 namespace
@@ -180,3 +184,173 @@ launchFindMagics( const uint8_t* data, uint64_t nbytes, uint32_t which, uint64_t
     findMagicsKernel<<<blocks, FINDER_THREADS, 0, stream>>>( data, nbytes, which, found, foundCount, capacity );
 }
 }  // namespace ibz2
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * ibz2_find_magics_noalloc -- K1 for callers that must not allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The match list and its counter, which ibz2_find_magics keeps in cudaMalloc'ed memory of its context,
+ * live in a file-scope device array of fixed size instead: every GPU that loads the library holds these 512.25 KB
+ * until the process exits.  All calls on one device share the array, so calls that overlap on the GPU race; the
+ * counter is cleared at the start of every call, the match slots keep the last call's contents behind the new count.
+ * --------------------------------------------------------------------------------------------------------------- */
+namespace ibz2
+{
+namespace
+{
+constexpr uint32_t NOALLOC_COUNTER_BYTES = 256;   /* the counter gets an aligned slot of its own */
+constexpr uint64_t NOALLOC_SCRATCH_BYTES = NOALLOC_COUNTER_BYTES + static_cast<uint64_t>( IBZ2_NOALLOC_MAX_MATCHES ) * sizeof( uint64_t );
+constexpr int NOALLOC_MAX_DEVICES = 64;
+
+static __device__ __align__( 256 ) uint8_t g_noallocScratch[NOALLOC_SCRATCH_BYTES];
+
+/* In host code g_noallocScratch is a stand-in, not a device address: what a kernel gets is what cudaGetSymbolAddress
+ * returned on that device, resolved once per device with that device current. */
+struct NoallocDevice
+{
+    uint8_t* scratch{ nullptr };
+    int sms{ 0 };
+    bool ready{ false };
+};
+NoallocDevice g_noallocDevices[NOALLOC_MAX_DEVICES];
+std::mutex g_noallocMutex;
+thread_local char g_noallocMessage[320];
+
+int
+noallocFail( int rc, const char* what, const char* detail )
+{
+    std::snprintf( g_noallocMessage, sizeof( g_noallocMessage ), "ibz2_find_magics_noalloc: %s%s%s", what,
+                   detail != nullptr ? ": " : "", detail != nullptr ? detail : "" );
+    setContextFreeError( g_noallocMessage );
+    return rc;
+}
+
+/* the caller's current device is put back when the call returns */
+struct NoallocDeviceGuard
+{
+    int previous{ -1 };
+    bool switched{ false };
+    ~NoallocDeviceGuard()
+    {
+        if ( switched ) {
+            cudaSetDevice( previous );
+        }
+    }
+};
+
+int
+noallocSetUp( int device, NoallocDevice** out )
+{
+    const std::lock_guard<std::mutex> lock( g_noallocMutex );
+    NoallocDevice& d = g_noallocDevices[device];
+    if ( !d.ready ) {
+        void* address = nullptr;
+        cudaError_t err = cudaGetSymbolAddress( &address, g_noallocScratch );
+        if ( ( err != cudaSuccess ) || ( address == nullptr ) ) {
+            cudaGetLastError();
+            return noallocFail( IBZ2_E_CUDA, "cudaGetSymbolAddress of the scratch array failed", cudaGetErrorString( err ) );
+        }
+        int sms = 0;
+        err = cudaDeviceGetAttribute( &sms, cudaDevAttrMultiProcessorCount, device );
+        if ( ( err != cudaSuccess ) || ( sms <= 0 ) ) {
+            cudaGetLastError();
+            return noallocFail( IBZ2_E_CUDA, "cannot read the SM count", cudaGetErrorString( err ) );
+        }
+        d.scratch = static_cast<uint8_t*>( address );
+        d.sms = sms;
+        d.ready = true;
+    }
+    *out = &d;
+    return IBZ2_OK;
+}
+}  // namespace
+}  // namespace ibz2
+
+extern "C" int
+ibz2_find_magics_noalloc( int device, void* stream, const void* device_data, uint64_t nbytes, uint64_t base_bit_offset,
+                          uint32_t which, uint64_t* offsets, uint64_t capacity, uint64_t* count )
+{
+    using namespace ibz2;
+    if ( ( count == nullptr ) || ( ( device_data == nullptr ) && ( nbytes > 0 ) )
+         || ( ( which & ( IBZ2_FIND_BLOCK | IBZ2_FIND_EOS ) ) == 0 ) || ( ( offsets == nullptr ) && ( capacity > 0 ) ) ) {
+        return noallocFail( IBZ2_E_INVALID_ARGUMENT, "invalid argument", nullptr );
+    }
+    *count = 0;
+    if ( capacity > IBZ2_NOALLOC_MAX_MATCHES ) {
+        char detail[160];
+        std::snprintf( detail, sizeof( detail ), "%llu entries asked for, the static scratch array holds IBZ2_NOALLOC_MAX_MATCHES = %u "
+                       "(use ibz2_find_magics for more)", static_cast<unsigned long long>( capacity ), IBZ2_NOALLOC_MAX_MATCHES );
+        return noallocFail( IBZ2_E_CAPACITY, "capacity beyond the maximum", detail );
+    }
+    if ( ( device < 0 ) || ( device >= NOALLOC_MAX_DEVICES ) ) {
+        return noallocFail( IBZ2_E_INVALID_ARGUMENT, "device index out of range", nullptr );
+    }
+    NoallocDeviceGuard guard;
+    cudaError_t err = cudaGetDevice( &guard.previous );
+    if ( ( err == cudaSuccess ) && ( guard.previous != device ) ) {
+        err = cudaSetDevice( device );
+        guard.switched = err == cudaSuccess;
+    }
+    if ( err != cudaSuccess ) {
+        cudaGetLastError();
+        return noallocFail( IBZ2_E_NO_DEVICE, "cannot make the device current (there is no CPU fallback)", cudaGetErrorString( err ) );
+    }
+    if ( nbytes < 6 ) {
+        return IBZ2_OK;
+    }
+    {
+        /* a host pointer would make the kernel fault (and the context unusable): look before launching */
+        cudaPointerAttributes attributes{};
+        err = cudaPointerGetAttributes( &attributes, device_data );
+        if ( ( err != cudaSuccess ) || ( ( attributes.type != cudaMemoryTypeDevice ) && ( attributes.type != cudaMemoryTypeManaged ) ) ) {
+            cudaGetLastError();
+            return noallocFail( IBZ2_E_INVALID_ARGUMENT, "device_data is not device memory (this entry point stages nothing)", nullptr );
+        }
+    }
+    NoallocDevice* d = nullptr;
+    const int rc = noallocSetUp( device, &d );
+    if ( rc != IBZ2_OK ) {
+        return rc;
+    }
+    const cudaStream_t s = static_cast<cudaStream_t>( stream );
+    uint32_t* const dCount = reinterpret_cast<uint32_t*>( d->scratch );
+    uint64_t* const dFound = reinterpret_cast<uint64_t*>( d->scratch + NOALLOC_COUNTER_BYTES );
+    const uint32_t slots = static_cast<uint32_t>( capacity );
+
+    /* the array keeps the last call's contents: the counter must start at zero */
+    if ( ( err = cudaMemsetAsync( dCount, 0, sizeof( uint32_t ), s ) ) != cudaSuccess ) {
+        return noallocFail( IBZ2_E_CUDA, "cudaMemsetAsync", cudaGetErrorString( err ) );
+    }
+    const uint64_t nVectors = nbytes / 16U;
+    const uint64_t wanted = ( nVectors + FINDER_THREADS * FINDER_UNROLL - 1 ) / ( FINDER_THREADS * FINDER_UNROLL );
+    const uint64_t maxBlocks = static_cast<uint64_t>( d->sms ) * 8U;
+    const uint32_t blocks = static_cast<uint32_t>( wanted < 1 ? 1 : ( wanted > maxBlocks ? maxBlocks : wanted ) );
+    findMagicsKernel<<<blocks, FINDER_THREADS, 0, s>>>( static_cast<const uint8_t*>( device_data ), nbytes, which, dFound,
+                                                        dCount, slots );
+    if ( ( err = cudaGetLastError() ) != cudaSuccess ) {
+        return noallocFail( IBZ2_E_CUDA, "kernel launch", cudaGetErrorString( err ) );
+    }
+    uint32_t found = 0;
+    if ( ( ( err = cudaMemcpyAsync( &found, dCount, sizeof( uint32_t ), cudaMemcpyDeviceToHost, s ) ) != cudaSuccess )
+         || ( ( err = cudaStreamSynchronize( s ) ) != cudaSuccess ) ) {
+        return noallocFail( IBZ2_E_CUDA, "reading the match count", cudaGetErrorString( err ) );
+    }
+    *count = found;
+    const uint64_t n = std::min<uint64_t>( found, capacity );
+    if ( n > 0 ) {
+        if ( ( ( err = cudaMemcpyAsync( offsets, dFound, n * sizeof( uint64_t ), cudaMemcpyDeviceToHost, s ) ) != cudaSuccess )
+             || ( ( err = cudaStreamSynchronize( s ) ) != cudaSuccess ) ) {
+            return noallocFail( IBZ2_E_CUDA, "reading the matches", cudaGetErrorString( err ) );
+        }
+        /* ascending by bit offset like ibz2_find_magics (in place: std::sort allocates nothing) */
+        std::sort( offsets, offsets + n, [] ( uint64_t a, uint64_t b ) {
+            return ( a & ~IBZ2_OFFSET_EOS_FLAG ) < ( b & ~IBZ2_OFFSET_EOS_FLAG );
+        } );
+        for ( uint64_t i = 0; i < n; ++i ) {
+            offsets[i] = ( ( offsets[i] & ~IBZ2_OFFSET_EOS_FLAG ) + base_bit_offset ) | ( offsets[i] & IBZ2_OFFSET_EOS_FLAG );
+        }
+    }
+    if ( found > capacity ) {
+        return noallocFail( IBZ2_E_CAPACITY, "more matches than capacity (offsets holds `capacity` of them, not necessarily the first)", nullptr );
+    }
+    return IBZ2_OK;
+}

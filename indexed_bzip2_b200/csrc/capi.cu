@@ -283,6 +283,13 @@ smCount()
 {
     return g_smCount;
 }
+
+/* what ibz2_last_error( NULL ) returns on this thread, for entry points that have no context (blockfinder.cu) */
+void
+setContextFreeError( const char* message )
+{
+    g_createError = message;
+}
 }  // namespace ibz2
 
 extern "C" {

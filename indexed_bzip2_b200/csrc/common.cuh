@@ -223,4 +223,5 @@ constexpr uint32_t CRC_PIECE_BYTES = 131072;
 void initCrcConstants();
 
 int smCount();
+void setContextFreeError( const char* message );
 }  // namespace ibz2
