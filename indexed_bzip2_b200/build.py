@@ -47,8 +47,14 @@ def _stale(target: Path, deps: list[Path]) -> bool:
 
 def build_native(force: bool = False, verbose: bool = False) -> Path:
     BUILD.mkdir(exist_ok=True)
-    headers = list(CSRC.glob("*.cuh")) + list((PKG.parent / "include").glob("*.h")) + [Path(__file__)]
+    headers = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inl")) + list((PKG.parent / "include").glob("*.h")) + [Path(__file__)]
     cc = nvcc()
+    # objects built with other experiment flags ($IBZ2_NVCC_EXTRA) are stale whatever their age
+    stamp = BUILD / "nvcc_extra.txt"
+    extra = os.environ.get("IBZ2_NVCC_EXTRA", "")
+    if (stamp.read_text() if stamp.exists() else "") != extra:
+        force = True
+        stamp.write_text(extra)
     jobs = []
     for name in CUDA_SOURCES:
         src = CSRC / name

@@ -179,12 +179,18 @@ void launchBwtPrepare( const uint8_t* lbytes, uint32_t* dbuf, BlockMeta* meta, u
  * segment its length and successor segment (one uint2: the ranking follows chains of them, one load per hop; kept
  * apart from the slots so that a block's 56 250 links are 450 KB that stay in L2), the position at which a walk longer
  * than the slot goes on (u32) and, after ranking, its output offset (u32).  The buffer starts with a TRAV_STAGE_HEADER holding the walk kernel's work counter. */
-constexpr uint32_t TRAV_SPACING_SHIFT = 4;
+#ifndef IBZ2_TRAV_SPACING_SHIFT
+#define IBZ2_TRAV_SPACING_SHIFT 4
+#endif
+#ifndef IBZ2_TRAV_SLOT_SHIFT
+#define IBZ2_TRAV_SLOT_SHIFT 6
+#endif
+constexpr uint32_t TRAV_SPACING_SHIFT = IBZ2_TRAV_SPACING_SHIFT;
 constexpr uint32_t TRAV_SPACING = 1U << TRAV_SPACING_SHIFT;                    /* a splitter every 16 positions */
 constexpr uint32_t TRAV_COARSE_SHIFT = 6;                                      /* every 64: the ones that get ranked */
 constexpr uint32_t TRAV_MAX_SEGMENTS = ( DBUF_SIZE + TRAV_SPACING - 1U ) / TRAV_SPACING;   /* 56250 */
 constexpr uint32_t TRAV_SEG_CAP = ( TRAV_MAX_SEGMENTS + 63U ) & ~63U;          /* 56256 */
-constexpr uint32_t TRAV_SLOT_SHIFT = 6;
+constexpr uint32_t TRAV_SLOT_SHIFT = IBZ2_TRAV_SLOT_SHIFT;
 constexpr uint32_t TRAV_SLOT_BYTES = 1U << TRAV_SLOT_SHIFT;                    /* 4 x the mean segment length: two slots per line */
 constexpr uint32_t TRAV_SLOT2_SHIFT = 7;                                       /* where the 1.8 % of longer segments go on */
 constexpr uint32_t TRAV_SLOT2_BYTES = 1U << TRAV_SLOT2_SHIFT;
