@@ -340,16 +340,28 @@ KERNELS = {"find_ms": "K1 findMagicsKernel", "huffman_bits_ms": "K2b huffmanBits
 # this same command on one B200 (`--metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum`); only
 # valid for the default workload at N=1, and only as fresh as the list
 TRAFFIC_CSV = ROOT / "profiles" / "r2_launches.csv"
-TRAFFIC_KERNELS = {"find_ms": ["findMagicsKernel"], "huffman_bits_ms": ["huffmanBitsKernel", "resolveSymbolsKernel"],
+TRAFFIC_CSV_CONFIG1 = ROOT / "profiles" / "r2_launches_cfg1.csv"
+TRAFFIC_KERNELS = {"find_ms": ["findMagicsKernel"],
+                   "huffman_bits_ms": ["huffmanBitsKernel", "huffmanGroupsKernel", "resolveSymbolsKernel"],
                    "mtf_chunk_ms": ["mtfChunkKernel"],
                    "bwt_prepare_ms": ["bwtPrepareKernel"], "bwt_walk_ms": ["bwtWalkKernel"], "rle_scan_ms": ["rleScanKernel"],
                    "rle_write_ms": ["rleWriteKernel"], "crc_ms": ["crcKernel"]}
 
 
-def ncu_traffic(stage: str):
+def k2b_kernel_name(blocks: int, sms: int = 148) -> str:
+    """which of the two Huffman bit kernels a launch of `blocks` blocks takes (launchHuffmanBits, csrc/huffman_bits.cu)"""
+    forced = os.environ.get("IBZ2_K2B_KERNEL", "")[:1]
+    per_sm = int(os.environ.get("IBZ2_K2B_GROUPS_PER_SM", "2"))
+    groups = forced == "g" or (forced != "l" and blocks <= sms * per_sm)
+    return ("K2b huffmanGroupsKernel (a CTA per block)" if groups else "K2b huffmanBitsKernel (a lane per block)") \
+        + " + resolveSymbolsKernel"
+
+
+def ncu_traffic(stage: str, csv_path: Path = TRAFFIC_CSV):
     """(bytes per step, source) from the launch list: the launches between two findMagicsKernel launches are one step"""
     import csv
 
+    TRAFFIC_CSV = csv_path
     if not TRAFFIC_CSV.exists():
         return None, "no launch list committed"
     rows = list(csv.reader(TRAFFIC_CSV.read_text().splitlines()))
@@ -594,9 +606,14 @@ def run_ours(args):
         alg = algorithmic_bytes(dominant, my_c, n_symbols, int(total), n_coded)
         default_workload = (world == 1 and args.config == 3 and args.kind == "mixed" and args.copies == 8
                             and args.base_bytes == 1_000_000_000 and args.level == 9)
-        traffic, traffic_src = ncu_traffic(dominant) if default_workload else (None, "no capture for this workload")
+        config1_workload = (world == 1 and args.config == 1 and args.kind == "base64" and args.copies == 1
+                            and args.base_bytes == 100_000_000 and args.level == 9)
+        traffic, traffic_src = (ncu_traffic(dominant) if default_workload
+                                else ncu_traffic(dominant, TRAFFIC_CSV_CONFIG1) if config1_workload
+                                else (None, "no capture for this workload"))
         achieved = alg / (per_step[dominant] * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": KERNELS[dominant], "achieved": round(achieved, 2), "peak": peak,
+        kernel_name = KERNELS[dominant] if dominant != "huffman_bits_ms" else k2b_kernel_name(-(-len(results) // waves))
+        roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": round(achieved, 2), "peak": peak,
                     "unit": "GB/s", "frac": round(achieved / peak, 5),
                     "traffic": traffic, "traffic_source": traffic_src,
                     "peak_source": peak_src,

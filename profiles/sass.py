@@ -18,7 +18,7 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 LIB = ROOT / "indexed_bzip2_b200" / "libibz2_cuda.so"
 OUT = ROOT / "profiles" / "sass"
-KERNELS = ["findMagicsKernel", "huffmanHeaderKernel", "huffmanBitsKernelILi4E", "resolveSymbolsKernel", "mtfChunkKernel",
+KERNELS = ["findMagicsKernel", "huffmanHeaderKernel", "huffmanBitsKernelILi4E", "huffmanGroupsKernel", "resolveSymbolsKernel", "mtfChunkKernel",
            "mtfExpandKernel", "bwtPrepareKernel", "bwtWalkKernel", "bwtRankKernel", "bwtPlaceKernel", "rleScanKernel",
            "rleWriteKernel", "crcKernel"]
 
@@ -75,6 +75,11 @@ def main() -> None:
             continue
         pretty = short.replace("ILi4E", "_lanes4")
         prof = next((p for k, p in profiles.items() if pretty.split("_")[0] in k), None)
+        target = OUT / f"{pretty}.sass"
+        if prof is None and target.exists() and "share of the stall samples" in target.read_text():
+            # an annotated listing from an earlier capture is worth more than a bare one: leave it
+            print(f"{pretty}: kept (annotated by an earlier capture)")
+            continue
         # loops: a branch to a lower address closes one
         loops = []
         for line in lines:
