@@ -662,13 +662,17 @@ def run_ours(args):
     if world > 1:
         # the same job through the product's own multi-GPU call (ibz2_multi_decode_buffer: ONE process, one host thread
         # and one context per GPU, one pinned output buffer); the other ranks have released their GPUs and wait
+        # (a CPU-side barrier: an NCCL barrier would keep a kernel spinning on the waiting ranks' GPUs, which are the
+        # GPUs rank 0's call is using -- measured: 508 ms per call with it, 325 ms without)
         dist.barrier()
+        torch.cuda.synchronize()
+        waiting = dist.new_group(backend="gloo")
         if rank == 0 and os.environ.get("IBZ2_BENCH_MULTI", "1") != "0":
             try:
                 line["multi_api"] = multi_api_run(w, world, args.steps)
             except Exception as e:
                 line["multi_api"] = {"value": None, "note": f"failed: {e}"}
-        dist.barrier()
+        dist.barrier(group=waiting)
         dist.destroy_process_group()
     if line is not None:
         print(json.dumps(line), flush=True)
