@@ -842,6 +842,8 @@ huffmanGroupsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
     }
 }
 
+#include "huffman_pipeline.inl"
+
 /* What K2b stored per symbol -> the symbol itself: ( table << 9 ) | index goes through K2a's 9-bit table, 0x8000 | table <<
  * 9 | rank through perm (HuffmanCodingSymbolsPerLength.hpp:105-124).  One pass over the symbol arrays with 16-byte
  * accesses; the 9 KB of tables of a block stay in L1. */
@@ -904,8 +906,18 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
         const char* const which = std::getenv( "IBZ2_K2B_KERNEL" );
         const char* const perSm = std::getenv( "IBZ2_K2B_GROUPS_PER_SM" );
         const uint32_t limit = static_cast<uint32_t>( smCount() ) * ( perSm != nullptr ? std::strtoul( perSm, nullptr, 10 ) : GRP_BLOCKS_PER_SM );
-        const bool groups = ( which != nullptr ) && ( which[0] == 'g' ) ? true
+        const bool groups = ( which != nullptr ) && ( ( which[0] == 'g' ) || ( which[0] == 'p' ) ) ? true
                             : ( which != nullptr ) && ( which[0] == 'l' ) ? false : nblocks <= limit;
+        if ( groups && ( ( which == nullptr ) || ( which[0] != 'g' ) ) ) {
+            /* the pipelined version; IBZ2_K2B_KERNEL=groups runs the first one */
+            cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
+            const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() * 2 ), nblocks ) );
+            huffmanPipelineKernel<<<ctas, PIPE_THREADS, 0, stream>>>( data, nbytes, meta, nblocks, selectors, tables, scratch, counter,
+                                                                     ordered ? counter + K2B_ORDER_OFFSET : nullptr );
+            const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
+            resolveSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );
+            return;
+        }
         if ( groups ) {
             cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
             const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() * 2 ), nblocks ) );

@@ -30,7 +30,7 @@ def case(name):
 
 # K2b has two kernels, a lane per block for launches with many blocks and a CTA per block for launches with few
 # (csrc/huffman_bits.cu); the launches of this file are all small, so each kernel is forced in turn
-@pytest.fixture(scope="module", params=["lanes", "groups"])
+@pytest.fixture(scope="module", params=["lanes", "groups", "pipeline"])
 def ctx(request):
     os.environ["IBZ2_K2B_KERNEL"] = request.param
     c = _capi.Context(0)
