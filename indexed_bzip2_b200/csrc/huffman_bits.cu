@@ -29,7 +29,9 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 
 namespace ibz2
 {
@@ -908,11 +910,13 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
         const uint32_t limit = static_cast<uint32_t>( smCount() ) * ( perSm != nullptr ? std::strtoul( perSm, nullptr, 10 ) : GRP_BLOCKS_PER_SM );
         const bool groups = ( which != nullptr ) && ( ( which[0] == 'g' ) || ( which[0] == 'p' ) ) ? true
                             : ( which != nullptr ) && ( which[0] == 'l' ) ? false : nblocks <= limit;
-        if ( groups && ( ( which == nullptr ) || ( which[0] != 'g' ) ) ) {
-            /* the pipelined version; IBZ2_K2B_KERNEL=groups runs the first one */
+        if ( groups && ( which != nullptr ) && ( which[0] == 'p' ) ) {
+            /* the pipelined version (IBZ2_K2B_KERNEL=pipeline): an experiment, not the default */
             cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
             const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() * 2 ), nblocks ) );
-            huffmanPipelineKernel<<<ctas, PIPE_THREADS, 0, stream>>>( data, nbytes, meta, nblocks, selectors, tables, scratch, counter,
+            cudaFuncSetAttribute( huffmanPipelineKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  static_cast<int>( sizeof( PipeShared ) ) );
+            huffmanPipelineKernel<<<ctas, PIPE_THREADS, sizeof( PipeShared ), stream>>>( data, nbytes, meta, nblocks, selectors, tables, scratch, counter,
                                                                      ordered ? counter + K2B_ORDER_OFFSET : nullptr );
             const dim3 grid( ( DBUF_SIZE + RESOLVE_PER_CTA - 1U ) / RESOLVE_PER_CTA, nblocks );
             resolveSymbolsKernel<<<grid, RESOLVE_THREADS, 0, stream>>>( meta, tables, scratch );

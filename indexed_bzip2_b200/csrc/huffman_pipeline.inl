@@ -6,7 +6,7 @@
  * not on where the groups start.  The table of every group is known in advance (the selectors), and the next group starts
  * between 50 and 450 bits behind the current one.  So while warp 16 follows the chain of group g through ring set g % 3,
  * the 16 builder warps look up all 1024 bit offsets from ( start of g + 50 ) & ~31 on with the table of group g + 1 and
- * double them to hops of 2, 4, 8, 16 symbols into set ( g + 1 ) % 3, and warps 17-18 store the entries of group g - 1 out
+ * double them to hops of 2, 4, 8 symbols into set ( g + 1 ) % 3, and warps 17-18 store the entries of group g - 1 out
  * of set ( g - 1 ) % 3.  One CTA barrier per group; the builders use a barrier of their own between the doubling rounds.
  * A group that is not 50 plain symbols of at most 9 bits (long code, end of block) is walked one symbol at a time by the
  * chain warp; if it ends outside the range that was looked up for its successor, one round goes to looking up again.
@@ -17,9 +17,14 @@ constexpr uint32_t PIPE_CHAIN_WARP = PIPE_BUILD_THREADS / 32;
 constexpr uint32_t PIPE_OUT_WARP = PIPE_CHAIN_WARP + 1U;   /* and the one behind it */
 constexpr int PIPE_THREADS = PIPE_BUILD_THREADS + 3 * 32;
 constexpr uint32_t PIPE_RING = 1024;             /* bit offsets per set */
-constexpr uint32_t PIPE_LEVELS = 5;              /* hops of 1, 2, 4, 8, 16 symbols */
+#ifndef IBZ2_PIPE_LEVELS
+#define IBZ2_PIPE_LEVELS 4
+#endif
+constexpr uint32_t PIPE_LEVELS = IBZ2_PIPE_LEVELS;            /* 4: hops of 1, 2, 4, 8 symbols; 3: up to 4 */
+constexpr uint32_t PIPE_HOP = 1U << ( PIPE_LEVELS - 1U );     /* symbols of the longest hop */
+constexpr uint32_t PIPE_HOPS = ( GROUP_SIZE - 2U ) / PIPE_HOP; /* long hops per group; one hop of 2 behind them */
+static_assert( PIPE_HOPS * PIPE_HOP + 2U == GROUP_SIZE, "48 symbols in long hops, 2 in a hop of two" );
 constexpr uint32_t PIPE_SETS = 3;
-constexpr uint32_t PIPE_NO_SET = PIPE_SETS;
 constexpr uint32_t PIPE_FLAG = 0x8000U;          /* the hop is whole: 2^level plain symbols */
 constexpr uint32_t PIPE_TARGET = 0x07FFU;        /* offset behind the hop; >= PIPE_RING: outside the set */
 constexpr uint32_t PIPE_WORDS = 256;             /* staged big-endian words of the file (a ring) */
@@ -30,32 +35,67 @@ constexpr uint32_t PIPE_MAX_START = PIPE_RING - ( GROUP_SIZE - 2U ) * HUFF_LUT_B
 constexpr uint32_t PIPE_SKIP = GROUP_SIZE;       /* the next group starts at least this many bits behind the current one */
 static_assert( ( GROUP_SIZE * HUFF_LUT_BITS - PIPE_SKIP ) + 31U <= PIPE_MAX_START, "the successor of a plain group is covered" );
 
-struct PipeControl
+/* what the chain warp tells the others at the end of a round: one 16-byte store, one 16-byte load */
+constexpr uint32_t PIPE_OUTCOME = 3U;            /* 0 = go on, 1 = end-of-block symbol seen, 2 = careful decoder */
+constexpr uint32_t PIPE_REBUILD = 4U;            /* group g has no usable set: look it up from its first bit, no chain this round */
+constexpr uint32_t PIPE_STORE = 8U;              /* group g - 1 was 50 plain symbols: their entries are still to be stored */
+/* The bit offsets of a set that are worth looking up.  A group of 50 plain symbols takes between 50 x the shortest and
+ * 50 x the longest code that the block's 9-bit tables hold, so the first bit of the next group and its last one lie in a
+ * range that is the same for every group of the block (about 700 of the 1024 offsets for data whose codes are all of
+ * similar length); it is worked out once per block.  A group with an exceptional symbol may end anywhere: the chain warp
+ * checks that the next group's first bit is inside the range and has it looked up again from that bit if it is not. */
+struct PipeWindow
 {
-    unsigned long long buildBase;   /* bit position (a multiple of 32) of offset 0 of the set to build */
-    unsigned long long endBit;      /* first bit behind the groups chained so far */
-    uint32_t outcome;               /* 0 = go on, 1 = end-of-block symbol seen, 2 = careful decoder */
-    uint32_t buildSet;              /* PIPE_NO_SET: nothing to build */
-    uint32_t buildLut;              /* table * HUFF_LUT_SIZE of the set to build */
-    uint32_t outFast;               /* the group chained last is 50 plain symbols whose entries are still to be stored */
-    uint32_t outSet;
-    uint32_t outLut;
-    uint32_t outNsym;               /* symbols in front of that group */
-    uint32_t nsym;                  /* symbols of the groups chained so far */
+    uint32_t lo;   /* multiples of 32 */
+    uint32_t hi;
+};
+
+struct PipeLengths
+{
+    uint32_t shortest;   /* over all tables of the block: codes of at most 9 bits, without the end-of-block symbol */
+    uint32_t longest;
+};
+
+__device__ __forceinline__ PipeWindow
+pipeWindow( const PipeLengths lengths, bool fromFirstBit )
+{
+    PipeWindow w;
+    w.lo = 0;
+    w.hi = PIPE_RING;
+    if ( lengths.shortest <= lengths.longest ) {
+        if ( fromFirstBit ) {
+            /* a group from the word its first bit is in */
+            w.hi = min( PIPE_RING, ( 31U + GROUP_SIZE * lengths.longest + 63U ) & ~31U );
+        } else {
+            /* a group from 50 bits behind the first bit of the group in front of it */
+            w.lo = ( GROUP_SIZE * lengths.shortest - PIPE_SKIP ) & ~31U;
+            w.hi = min( PIPE_RING, ( 31U + GROUP_SIZE * lengths.longest - PIPE_SKIP + GROUP_SIZE * lengths.longest + 63U ) & ~31U );
+        }
+    }
+    return w;
+}
+
+struct PipeState
+{
+    unsigned long long X;   /* first bit of group g */
+    uint32_t g;             /* the group to chain next */
+    uint32_t flags;
 };
 
 struct PipeShared
 {
     alignas( 16 ) uint8_t dec[( DEC_STRIDE + 15U ) & ~15U];
-    alignas( 16 ) PipeControl ctrl[2];
+    alignas( 16 ) PipeState state[2];
     uint32_t block;
     uint32_t skip;
+    uint32_t nsym;          /* symbols in front of state.X, written when the block ends */
+    PipeLengths lengths;
     uint32_t words[PIPE_WORDS];
     uint16_t ring[PIPE_SETS][PIPE_LEVELS][PIPE_RING];
     uint16_t idx[PIPE_SETS][PIPE_RING];
-    uint16_t coarse[PIPE_SETS][4];
+    uint16_t coarse[PIPE_SETS][16];
+    alignas( 16 ) uint8_t selectors[MAX_SELECTORS + 64U];
 };
-static_assert( sizeof( PipeShared ) <= 48U * 1024U, "static shared memory" );
 
 __device__ __forceinline__ void
 pipeBuilderBarrier()
@@ -68,7 +108,8 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
                        const uint8_t* __restrict__ selectorsAll, const BlockTables* __restrict__ tablesAll,
                        uint32_t* __restrict__ scratchAll, uint32_t* __restrict__ counter, const uint32_t* __restrict__ order )
 {
-    __shared__ PipeShared sh;
+    extern __shared__ __align__( 16 ) uint8_t pipeSharedRaw[];
+    PipeShared& sh = *reinterpret_cast<PipeShared*>( pipeSharedRaw );
     const uint32_t t = threadIdx.x;
     const uint32_t warp = t >> 5;
     const uint32_t lane = t & 31U;
@@ -109,6 +150,11 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
         const uint8_t* const selectors = selectorsAll + static_cast<uint64_t>( block ) * SEL_STRIDE;
         uint16_t* const symOut = reinterpret_cast<uint16_t*>( reinterpret_cast<uint8_t*>( scratchAll + static_cast<uint64_t>( block ) * DBUF_STRIDE )
                                                               + K2_SYM16_OFFSET );
+        if ( t == 0 ) {
+            sh.lengths.shortest = 0xFFU;
+            sh.lengths.longest = 0;
+        }
+        __syncthreads();
         {
             /* the same tables as one decoder of huffmanBitsKernel keeps, built by all threads */
             const uint4* const src = reinterpret_cast<const uint4*>( &bt->lut[0][0] );
@@ -125,6 +171,16 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
                 }
                 dst[2U * q] = lens[0];
                 dst[2U * q + 1U] = lens[1];
+                uint32_t shortest = 0xFFU;
+                uint32_t longest = 0;
+#pragma unroll
+                for ( uint32_t i = 0; i < 8U; ++i ) {
+                    const uint32_t len = ( lens[i >> 2] >> ( 8U * ( i & 3U ) ) ) & 0xFFU;
+                    shortest = len != 0 ? min( shortest, len ) : shortest;
+                    longest = max( longest, len );
+                }
+                atomicMin( &sh.lengths.shortest, shortest );
+                atomicMax( &sh.lengths.longest, longest );
             }
             for ( uint32_t i = t; i < groupCount * LONG_LIMITS; i += PIPE_THREADS ) {
                 const uint64_t limit = bt->limit[i / LONG_LIMITS][LONG_FIRST_LEN + i % LONG_LIMITS];
@@ -138,42 +194,53 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
                 *reinterpret_cast<uint16_t*>( sh.dec + DEC_EOB_OFFSET + t * 2U ) = bt->eobPerm[t];
             }
         }
+        /* the table of every group (bzip2.hpp:710-721), so that nobody waits for global memory to learn it */
+        for ( uint32_t i = t; i < ( selectorsCount + 15U ) / 16U; i += PIPE_THREADS ) {
+            reinterpret_cast<uint4*>( sh.selectors )[i] = __ldg( reinterpret_cast<const uint4*>( selectors ) + i );
+        }
         const uint64_t startBit = bt->dataStartBit;
         for ( uint32_t i = t; i < PIPE_WORDS; i += PIPE_THREADS ) {
             const uint64_t w = ( startBit >> 5 ) + i;
             sh.words[w & ( PIPE_WORDS - 1U )] = bswap( loadWordRaw( data, nbytes, w ) );
         }
         if ( t == 0 ) {
-            /* the first round only looks up: group 0 from the word its first bit is in */
-            PipeControl c{};
-            c.buildBase = startBit & ~static_cast<uint64_t>( 31U );
-            c.endBit = startBit;
-            c.buildSet = 0;
-            c.buildLut = ( selectorsCount > 0 ? selectors[0] : 0U ) * HUFF_LUT_SIZE;
-            sh.ctrl[0] = c;
+            /* the first round only looks up: group 0, from the word its first bit is in */
+            PipeState first;
+            first.X = startBit;
+            first.g = 0;
+            first.flags = PIPE_REBUILD;
+            sh.state[0] = first;
         }
         /* ---- what the roles keep between the rounds ---- */
         /* builders: file words in front of loadedUpTo are staged; a refill is loaded in one round and stored in the next */
         uint64_t loadedUpTo = ( startBit >> 5 ) + PIPE_WORDS;
         bool pending = false;
         uint32_t pendingRaw = 0;
-        /* chain warp: the next group to chain, where it starts, and which group each set holds, looked up from where */
-        uint64_t X = startBit;
-        uint32_t g = 0;
+        /* chain warp: offset 0 of the set of the group to chain, and the symbols in front of that group */
+        uint64_t baseOfG = startBit & ~static_cast<uint64_t>( 31U );
+        PipeWindow windowOfG{ 0, PIPE_RING };   /* set when the lengths are known, below */
         uint32_t nsym = 0;
-        constexpr uint32_t NO_GROUP = 0xFFFFFFFFU;
-        uint32_t setGroup0 = 0, setGroup1 = NO_GROUP, setGroup2 = NO_GROUP;
-        uint64_t setBase0 = startBit & ~static_cast<uint64_t>( 31U ), setBase1 = 0, setBase2 = 0;
         uint32_t round = 0;
         __syncthreads();
+        const PipeWindow windowFirst = pipeWindow( sh.lengths, true );
+        const PipeWindow windowBehind = pipeWindow( sh.lengths, false );
+        windowOfG = windowFirst;
 
         while ( true ) {
-            const PipeControl ctrl = sh.ctrl[round & 1U];
-            if ( ctrl.outcome != 0 ) {
+            const uint4 stateRaw = *reinterpret_cast<const uint4*>( &sh.state[round & 1U] );
+            const uint64_t X = ( static_cast<uint64_t>( stateRaw.y ) << 32 ) | stateRaw.x;
+            const uint32_t g = stateRaw.z;
+            const uint32_t flags = stateRaw.w;
+            if ( ( flags & PIPE_OUTCOME ) != 0 ) {
                 break;
             }
+            const bool rebuild = ( flags & PIPE_REBUILD ) != 0;
             if ( warp < PIPE_CHAIN_WARP ) {
-                /* ================= builders ================= */
+                /* ================= builders: group g from its first bit, or group g + 1 from 50 bits behind it ================= */
+                const uint32_t group = rebuild ? g : g + 1U;
+                const uint32_t set = group % PIPE_SETS;
+                const uint64_t baseWord = ( rebuild ? X : X + PIPE_SKIP ) >> 5;
+                const uint32_t lut = ( group < selectorsCount ? sh.selectors[group] : 0U ) * HUFF_LUT_SIZE;
                 if ( pending ) {
                     if ( t < PIPE_REFILL ) {
                         /* these slots hold words more than 190 in front of the newest: nobody reads them any more */
@@ -182,125 +249,149 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
                     loadedUpTo += PIPE_REFILL;
                     pending = false;
                 }
-                if ( ctrl.buildSet != PIPE_NO_SET ) {
-                    const uint64_t baseWord = ctrl.buildBase >> 5;
-                    if ( loadedUpTo < baseWord + PIPE_AHEAD ) {
-                        if ( t < PIPE_REFILL ) {
-                            pendingRaw = loadWordRaw( data, nbytes, loadedUpTo + t );
-                        }
-                        pending = true;
+                if ( loadedUpTo < baseWord + PIPE_AHEAD ) {
+                    if ( t < PIPE_REFILL ) {
+                        pendingRaw = loadWordRaw( data, nbytes, loadedUpTo + t );
                     }
-                    const uint32_t set = ctrl.buildSet;
-                    const uint32_t slot = static_cast<uint32_t>( baseWord );
-                    uint32_t e[2];
+                    pending = true;
+                }
+                const uint32_t slot = static_cast<uint32_t>( baseWord );
+                const PipeWindow window = rebuild ? windowFirst : windowBehind;
+                /* a thread looks at offsets first and first + 512 of the window, as far as they are inside; both limits are
+                 * multiples of 32, so a warp takes one of three ways as a whole, and within a way the two offsets are
+                 * independent instruction streams (a warp outside the window only keeps the others company at the barriers) */
+                const uint32_t first = window.lo + t;
+                const uint32_t count = first + PIPE_BUILD_THREADS < window.hi ? 2U : ( first < window.hi ? 1U : 0U );
+                uint32_t e[2] = { 0, 0 };
+                const auto lookUp = [&] ( auto n ) {
+                    constexpr uint32_t N = decltype( n )::value;
+                    uint32_t index[N];
 #pragma unroll
-                    for ( uint32_t j = 0; j < 2U; ++j ) {
-                        const uint32_t r = t + j * PIPE_BUILD_THREADS;
+                    for ( uint32_t j = 0; j < N; ++j ) {
+                        const uint32_t r = first + j * PIPE_BUILD_THREADS;
                         const uint32_t w = slot + ( r >> 5 );
                         const uint32_t wa = sh.words[w & ( PIPE_WORDS - 1U )];
                         const uint32_t wb = sh.words[( w + 1U ) & ( PIPE_WORDS - 1U )];
-                        const uint32_t index = __funnelshift_l( wb, wa, r & 31U ) >> ( 32 - HUFF_LUT_BITS );
-                        const uint32_t len = sh.dec[ctrl.buildLut + index];
-                        e[j] = len != 0 ? ( ( r + len ) | PIPE_FLAG ) : r;
-                        sh.ring[set][0][r] = static_cast<uint16_t>( e[j] );
-                        sh.idx[set][r] = static_cast<uint16_t>( index );
+                        index[j] = __funnelshift_l( wb, wa, r & 31U ) >> ( 32 - HUFF_LUT_BITS );
                     }
 #pragma unroll
-                    for ( uint32_t level = 1; level < PIPE_LEVELS; ++level ) {
-                        pipeBuilderBarrier();
+                    for ( uint32_t j = 0; j < N; ++j ) {
+                        const uint32_t r = first + j * PIPE_BUILD_THREADS;
+                        const uint32_t len = sh.dec[lut + index[j]];
+                        e[j] = len != 0 ? ( ( r + len ) | PIPE_FLAG ) : r;
+                        sh.ring[set][0][r] = static_cast<uint16_t>( e[j] );
+                        sh.idx[set][r] = static_cast<uint16_t>( index[j] );
+                    }
+                };
+                const auto doubleUp = [&] ( auto n, uint32_t level ) {
+                    constexpr uint32_t N = decltype( n )::value;
+                    uint32_t f[N];
 #pragma unroll
-                        for ( uint32_t j = 0; j < 2U; ++j ) {
-                            const uint32_t target = e[j] & PIPE_TARGET;
-                            const uint32_t f = sh.ring[set][level - 1U][target & ( PIPE_RING - 1U )];
-                            const bool whole = ( ( e[j] & PIPE_FLAG ) != 0 ) && ( target < PIPE_RING );
-                            e[j] = whole ? f : ( e[j] & ~PIPE_FLAG );
-                            sh.ring[set][level][t + j * PIPE_BUILD_THREADS] = static_cast<uint16_t>( e[j] );
-                        }
+                    for ( uint32_t j = 0; j < N; ++j ) {
+                        f[j] = sh.ring[set][level - 1U][e[j] & ( PIPE_RING - 1U )];
+                    }
+#pragma unroll
+                    for ( uint32_t j = 0; j < N; ++j ) {
+                        /* what lies behind the window was looked up for an earlier group */
+                        const bool whole = ( ( e[j] & PIPE_FLAG ) != 0 ) && ( ( e[j] & PIPE_TARGET ) < window.hi );
+                        e[j] = whole ? f[j] : ( e[j] & ~PIPE_FLAG );
+                        sh.ring[set][level][first + j * PIPE_BUILD_THREADS] = static_cast<uint16_t>( e[j] );
+                    }
+                };
+                if ( count == 2U ) {
+                    lookUp( std::integral_constant<uint32_t, 2>{} );
+                } else if ( count == 1U ) {
+                    lookUp( std::integral_constant<uint32_t, 1>{} );
+                }
+#pragma unroll
+                for ( uint32_t level = 1; level < PIPE_LEVELS; ++level ) {
+                    pipeBuilderBarrier();
+                    if ( count == 2U ) {
+                        doubleUp( std::integral_constant<uint32_t, 2>{}, level );
+                    } else if ( count == 1U ) {
+                        doubleUp( std::integral_constant<uint32_t, 1>{}, level );
                     }
                 }
             } else if ( warp > PIPE_CHAIN_WARP ) {
-                /* ================= output: the entries of the group chained in the round before ================= */
+                /* ================= output: the entries of group g - 1, chained in the round before ================= */
                 const uint32_t s = lane + 32U * ( warp - PIPE_OUT_WARP );
-                if ( ( ctrl.outFast != 0 ) && ( s < GROUP_SIZE ) ) {
-                    const uint32_t set = ctrl.outSet;
-                    uint32_t q = sh.coarse[set][s >> 4];
-                    if ( ( s & 8U ) != 0 ) {
-                        q = sh.ring[set][3][q] & PIPE_TARGET;
+                if ( ( ( flags & PIPE_STORE ) != 0 ) && ( s < GROUP_SIZE ) ) {
+                    const uint32_t set = ( g - 1U ) % PIPE_SETS;
+                    uint32_t q = sh.coarse[set][s / PIPE_HOP];
+#pragma unroll
+                    for ( uint32_t level = PIPE_LEVELS - 1U; level-- > 0; ) {
+                        if ( ( s & ( 1U << level ) ) != 0 ) {
+                            q = sh.ring[set][level][q] & PIPE_TARGET;
+                        }
                     }
-                    if ( ( s & 4U ) != 0 ) {
-                        q = sh.ring[set][2][q] & PIPE_TARGET;
-                    }
-                    if ( ( s & 2U ) != 0 ) {
-                        q = sh.ring[set][1][q] & PIPE_TARGET;
-                    }
-                    if ( ( s & 1U ) != 0 ) {
-                        q = sh.ring[set][0][q] & PIPE_TARGET;
-                    }
-                    symOut[ctrl.outNsym + s] = static_cast<uint16_t>( ctrl.outLut | sh.idx[set][q] );
+                    /* every group in front of this one had 50 symbols */
+                    symOut[( g - 1U ) * GROUP_SIZE + s]
+                        = static_cast<uint16_t>( sh.selectors[g - 1U] * HUFF_LUT_SIZE | sh.idx[set][q] );
                 }
             } else {
                 /* ================= the chain ================= */
-                const uint32_t set = g % PIPE_SETS;
-                const uint32_t heldGroup = set == 0 ? setGroup0 : ( set == 1 ? setGroup1 : setGroup2 );
-                const uint64_t base = set == 0 ? setBase0 : ( set == 1 ? setBase1 : setBase2 );
-                /* the set of group g is usable if it has been looked up (not in this very round) from a place that covers it */
-                const bool ready = ( heldGroup == g ) && ( set != ctrl.buildSet ) && ( X >= base ) && ( X - base <= PIPE_MAX_START );
-                const uint32_t tableNow = g < selectorsCount ? selectors[g] : 0U;
-                const uint32_t tableNext = g + 1U < selectorsCount ? selectors[g + 1U] : 0U;
-                const uint32_t tableAfter = g + 2U < selectorsCount ? selectors[g + 2U] : 0U;
-                PipeControl next{};
-                next.outcome = 0;
-                next.outFast = 0;
-                if ( ready ) {
+                uint64_t nextX = X;
+                uint32_t nextG = g;
+                uint32_t nextFlags = 0;
+                if ( !rebuild ) {
+                    const uint32_t set = g % PIPE_SETS;
                     /* next group of 50 symbols: the exits the lane kernel has at this place (bzip2.hpp:710-721) */
                     if ( ( g >= selectorsCount ) || ( nsym >= SYM_LIMIT ) || ( X > nbits ) ) {
-                        next.outcome = 2;
+                        nextFlags = 2;
                     } else {
-                        const uint32_t p0 = static_cast<uint32_t>( X - base );
-                        const uint16_t* const hop16 = sh.ring[set][4];
-                        const uint32_t f1 = hop16[p0];
-                        const uint32_t t1 = f1 & PIPE_TARGET;
-                        const uint32_t f2 = hop16[t1 & ( PIPE_RING - 1U )];
-                        const uint32_t t2 = f2 & PIPE_TARGET;
-                        const uint32_t f3 = hop16[t2 & ( PIPE_RING - 1U )];
-                        const uint32_t t3 = f3 & PIPE_TARGET;
-                        const uint32_t f4 = sh.ring[set][1][t3 & ( PIPE_RING - 1U )];
-                        const bool whole = ( ( f1 & f2 & f3 & f4 & PIPE_FLAG ) != 0 ) && ( ( t1 | t2 | t3 ) < PIPE_RING );
-                        if ( whole ) {
-                            if ( lane < 4U ) {
-                                sh.coarse[set][lane] = static_cast<uint16_t>( lane == 0 ? p0 : ( lane == 1 ? t1 : ( lane == 2 ? t2 : t3 ) ) );
+                        const uint32_t p0 = static_cast<uint32_t>( X - baseOfG );
+                        const uint16_t* const hop8 = sh.ring[set][PIPE_LEVELS - 1U];
+                        uint32_t p = p0;
+                        uint32_t mine = 0;   /* lane k: where hop k starts */
+                        uint32_t all = PIPE_FLAG;
+                        uint32_t reach = 0;
+#pragma unroll
+                        for ( uint32_t hop = 0; hop < PIPE_HOPS; ++hop ) {
+                            mine = lane == hop ? p : mine;
+                            const uint32_t f = hop8[p & ( PIPE_RING - 1U )];
+                            all &= f;
+                            reach = max( reach, p );
+                            p = f & PIPE_TARGET;
+                        }
+                        mine = lane == PIPE_HOPS ? p : mine;
+                        reach = max( reach, p );
+                        const uint32_t last = sh.ring[set][1][p & ( PIPE_RING - 1U )];
+                        all &= last;
+                        /* (the builders end a hop at the window's end, so a whole hop has only read entries of this group;
+                         * where a hop STARTS is the chain's to check) */
+                        if ( ( all != 0 ) && ( reach < windowOfG.hi ) ) {
+                            if ( lane <= PIPE_HOPS ) {
+                                sh.coarse[set][lane] = static_cast<uint16_t>( mine );
                             }
-                            next.outFast = 1;
-                            next.outSet = set;
-                            next.outLut = tableNow * HUFF_LUT_SIZE;
-                            next.outNsym = nsym;
-                            X = base + ( f4 & PIPE_TARGET );
+                            nextX = baseOfG + ( last & PIPE_TARGET );
+                            nextG = g + 1U;
+                            nextFlags = PIPE_STORE;
                             nsym += GROUP_SIZE;
-                            ++g;
                         } else {
                             /* one symbol at a time: plain ones through the single hops, the others through decodeOneSymbol */
-                            uint32_t p = p0;
+                            const uint32_t table = sh.selectors[g];
+                            uint32_t q = p0;
                             uint32_t done = 0;
                             uint32_t what = SYM_PLAIN;
                             uint16_t* const out = symOut + nsym;
                             while ( done < GROUP_SIZE ) {
-                                if ( p < PIPE_RING ) {
-                                    const uint32_t f = sh.ring[set][0][p];
+                                if ( ( q >= windowOfG.lo ) && ( q < windowOfG.hi ) ) {
+                                    const uint32_t f = sh.ring[set][0][q];
                                     if ( ( f & PIPE_FLAG ) != 0 ) {
                                         if ( lane == 0 ) {
-                                            out[done] = static_cast<uint16_t>( tableNow * HUFF_LUT_SIZE | sh.idx[set][p] );
+                                            out[done] = static_cast<uint16_t>( table * HUFF_LUT_SIZE | sh.idx[set][q] );
                                         }
-                                        p = f & PIPE_TARGET;
+                                        q = f & PIPE_TARGET;
                                         ++done;
                                         continue;
                                     }
                                 }
-                                const uint32_t w = static_cast<uint32_t>( base >> 5 ) + ( p >> 5 );
-                                uint32_t pos = p & 31U;
+                                const uint32_t w = static_cast<uint32_t>( baseOfG >> 5 ) + ( q >> 5 );
+                                uint32_t pos = q & 31U;
                                 uint32_t entry = 0;
                                 what = decodeOneSymbol( sh.words[w & ( PIPE_WORDS - 1U )], sh.words[( w + 1U ) & ( PIPE_WORDS - 1U )], pos,
-                                                        decAddr, tableNow, bt, &entry );
-                                p = ( p & ~31U ) + pos;
+                                                        decAddr, table, bt, &entry );
+                                q = ( q & ~31U ) + pos;
                                 if ( what != SYM_PLAIN ) {
                                     break;
                                 }
@@ -309,58 +400,36 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
                                 }
                                 ++done;
                             }
-                            X = base + p;
+                            nextX = baseOfG + q;
                             nsym += done;
-                            next.outcome = what == SYM_PLAIN ? 0U : ( what == SYM_EOB ? 1U : 2U );
-                            if ( what == SYM_PLAIN ) {
-                                ++g;
-                            }
+                            nextFlags = what == SYM_PLAIN ? 0U : ( what == SYM_EOB ? 1U : 2U );
+                            nextG = what == SYM_PLAIN ? g + 1U : g;
                         }
                     }
-                }
-                /* ---- what the others do in the next round ---- */
-                const bool advanced = ready && ( next.outcome == 0 );
-                const uint32_t tableComing = advanced ? tableNext : tableNow;     /* of group g as it is now */
-                const uint32_t tableBehind = advanced ? tableAfter : tableNext;   /* of group g + 1 */
-                const uint32_t comingSet = g % PIPE_SETS;
-                const uint32_t comingHeld = comingSet == 0 ? setGroup0 : ( comingSet == 1 ? setGroup1 : setGroup2 );
-                const uint64_t comingBase = comingSet == 0 ? setBase0 : ( comingSet == 1 ? setBase1 : setBase2 );
-                /* (the set being looked up in this round is complete when the next one starts) */
-                const bool comingReady = ( comingHeld == g ) && ( X >= comingBase ) && ( X - comingBase <= PIPE_MAX_START );
-                uint32_t buildSet = PIPE_NO_SET;
-                uint32_t buildGroup = 0;
-                uint64_t buildBase = 0;
-                uint32_t buildTable = 0;
-                if ( !comingReady ) {
-                    buildSet = comingSet;
-                    buildGroup = g;
-                    buildBase = X & ~static_cast<uint64_t>( 31U );
-                    buildTable = tableComing;
-                } else {
-                    const uint32_t behindSet = ( g + 1U ) % PIPE_SETS;
-                    const uint32_t behindHeld = behindSet == 0 ? setGroup0 : ( behindSet == 1 ? setGroup1 : setGroup2 );
-                    if ( behindHeld != g + 1U ) {
-                        buildSet = behindSet;
-                        buildGroup = g + 1U;
-                        buildBase = ( X + PIPE_SKIP ) & ~static_cast<uint64_t>( 31U );
-                        buildTable = tableBehind;
+                    /* the set of the next group is being looked up from 50 bits behind this group's first bit; a group with
+                     * long codes may end behind what that covers */
+                    const uint64_t baseOfNext = ( X + PIPE_SKIP ) & ~static_cast<uint64_t>( 31U );
+                    const PipeWindow windowOfNext = windowBehind;
+                    if ( ( nextX < baseOfNext + windowOfNext.lo ) || ( nextX - baseOfNext > PIPE_MAX_START )
+                         || ( nextX - baseOfNext >= windowOfNext.hi ) ) {
+                        nextFlags |= PIPE_REBUILD;
+                        baseOfG = nextX & ~static_cast<uint64_t>( 31U );
+                        windowOfG = windowFirst;
+                    } else {
+                        baseOfG = baseOfNext;
+                        windowOfG = windowOfNext;
                     }
                 }
-                if ( buildSet != PIPE_NO_SET ) {
-                    setGroup0 = buildSet == 0 ? buildGroup : setGroup0;
-                    setGroup1 = buildSet == 1 ? buildGroup : setGroup1;
-                    setGroup2 = buildSet == 2 ? buildGroup : setGroup2;
-                    setBase0 = buildSet == 0 ? buildBase : setBase0;
-                    setBase1 = buildSet == 1 ? buildBase : setBase1;
-                    setBase2 = buildSet == 2 ? buildBase : setBase2;
-                }
-                next.buildSet = buildSet;
-                next.buildBase = buildBase;
-                next.buildLut = buildTable * HUFF_LUT_SIZE;
-                next.endBit = X;
-                next.nsym = nsym;
                 if ( lane == 0 ) {
-                    sh.ctrl[( round + 1U ) & 1U] = next;
+                    uint4 raw;
+                    raw.x = static_cast<uint32_t>( nextX );
+                    raw.y = static_cast<uint32_t>( nextX >> 32 );
+                    raw.z = nextG;
+                    raw.w = nextFlags;
+                    *reinterpret_cast<uint4*>( &sh.state[( round + 1U ) & 1U] ) = raw;
+                    if ( ( nextFlags & PIPE_OUTCOME ) != 0 ) {
+                        sh.nsym = nsym;
+                    }
                 }
             }
             __syncthreads();
@@ -368,10 +437,10 @@ huffmanPipelineKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockM
         }
 
         if ( t == 0 ) {
-            const PipeControl last = sh.ctrl[round & 1U];
-            if ( ( last.outcome == 1 ) && ( last.endBit <= nbits ) ) {
-                bm.nCoded = last.nsym;
-                bm.endBit = last.endBit;
+            const PipeState last = sh.state[round & 1U];
+            if ( ( ( last.flags & PIPE_OUTCOME ) == 1 ) && ( last.X <= nbits ) ) {
+                bm.nCoded = sh.nsym;
+                bm.endBit = last.X;
             } else {
                 bm.status = ST_INTERNAL_CAREFUL;
             }
