@@ -342,7 +342,7 @@ KERNELS = {"find_ms": "K1 findMagicsKernel", "huffman_bits_ms": "K2b huffmanBits
 TRAFFIC_CSV = ROOT / "profiles" / "r2_launches.csv"
 TRAFFIC_CSV_CONFIG1 = ROOT / "profiles" / "r2_launches_cfg1.csv"
 TRAFFIC_KERNELS = {"find_ms": ["findMagicsKernel"],
-                   "huffman_bits_ms": ["huffmanBitsKernel", "huffmanGroupsKernel", "resolveSymbolsKernel"],
+                   "huffman_bits_ms": ["huffmanBitsKernel", "huffmanGroupsKernel", "huffmanPipelineKernel", "resolveSymbolsKernel"],
                    "mtf_chunk_ms": ["mtfChunkKernel"],
                    "bwt_prepare_ms": ["bwtPrepareKernel"], "bwt_walk_ms": ["bwtWalkKernel"], "rle_scan_ms": ["rleScanKernel"],
                    "rle_write_ms": ["rleWriteKernel"], "crc_ms": ["crcKernel"]}
@@ -352,8 +352,10 @@ def k2b_kernel_name(blocks: int, sms: int = 148) -> str:
     """which of the two Huffman bit kernels a launch of `blocks` blocks takes (launchHuffmanBits, csrc/huffman_bits.cu)"""
     forced = os.environ.get("IBZ2_K2B_KERNEL", "")[:1]
     per_sm = int(os.environ.get("IBZ2_K2B_GROUPS_PER_SM", "2"))
-    groups = forced == "g" or (forced != "l" and blocks <= sms * per_sm)
-    return ("K2b huffmanGroupsKernel (a CTA per block)" if groups else "K2b huffmanBitsKernel (a lane per block)") \
+    groups = forced in ("g", "p") or (forced != "l" and blocks <= sms * per_sm)
+    first = forced == "g"
+    return (("K2b huffmanGroupsKernel (a CTA per block)" if first else "K2b huffmanPipelineKernel (a CTA per block, pipelined)")
+            if groups else "K2b huffmanBitsKernel (a lane per block)") \
         + " + resolveSymbolsKernel"
 
 

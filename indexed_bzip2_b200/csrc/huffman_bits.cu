@@ -910,8 +910,9 @@ launchHuffmanBits( const uint8_t* data, uint64_t nbytes, BlockMeta* meta, uint32
         const uint32_t limit = static_cast<uint32_t>( smCount() ) * ( perSm != nullptr ? std::strtoul( perSm, nullptr, 10 ) : GRP_BLOCKS_PER_SM );
         const bool groups = ( which != nullptr ) && ( ( which[0] == 'g' ) || ( which[0] == 'p' ) ) ? true
                             : ( which != nullptr ) && ( which[0] == 'l' ) ? false : nblocks <= limit;
-        if ( groups && ( which != nullptr ) && ( which[0] == 'p' ) ) {
-            /* the pipelined version (IBZ2_K2B_KERNEL=pipeline): an experiment, not the default */
+        if ( groups && ( ( which == nullptr ) || ( which[0] != 'g' ) ) ) {
+            /* the pipelined version (config 1: 11.5 ms against 12.3, random reads 22.5 ms against 24.3);
+             * IBZ2_K2B_KERNEL=groups runs the first one */
             cudaMemsetAsync( counter, 0, sizeof( uint32_t ), stream );
             const uint32_t ctas = std::max( 1U, std::min( static_cast<uint32_t>( smCount() * 2 ), nblocks ) );
             cudaFuncSetAttribute( huffmanPipelineKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

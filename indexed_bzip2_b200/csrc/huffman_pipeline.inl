@@ -17,6 +17,9 @@ constexpr uint32_t PIPE_CHAIN_WARP = PIPE_BUILD_THREADS / 32;
 constexpr uint32_t PIPE_OUT_WARP = PIPE_CHAIN_WARP + 1U;   /* and the one behind it */
 constexpr int PIPE_THREADS = PIPE_BUILD_THREADS + 3 * 32;
 constexpr uint32_t PIPE_RING = 1024;             /* bit offsets per set */
+#ifndef IBZ2_PIPE_WINDOW
+#define IBZ2_PIPE_WINDOW 0
+#endif
 #ifndef IBZ2_PIPE_LEVELS
 #define IBZ2_PIPE_LEVELS 4
 #endif
@@ -62,7 +65,10 @@ pipeWindow( const PipeLengths lengths, bool fromFirstBit )
     PipeWindow w;
     w.lo = 0;
     w.hi = PIPE_RING;
-    if ( lengths.shortest <= lengths.longest ) {
+    /* Measured on config 1 (windows of ~740 offsets): 13.5 ms with the window, 11.9 ms with all 1024 offsets -- a builder warp
+     * with two rows of offsets takes as long as before and the warps with one row wait for it, so a window only pays once
+     * it is at most 512 offsets wide.  Kept for that case; off by default. */
+    if ( ( IBZ2_PIPE_WINDOW != 0 ) && ( lengths.shortest <= lengths.longest ) ) {
         if ( fromFirstBit ) {
             /* a group from the word its first bit is in */
             w.hi = min( PIPE_RING, ( 31U + GROUP_SIZE * lengths.longest + 63U ) & ~31U );

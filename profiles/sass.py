@@ -18,7 +18,7 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 LIB = ROOT / "indexed_bzip2_b200" / "libibz2_cuda.so"
 OUT = ROOT / "profiles" / "sass"
-KERNELS = ["findMagicsKernel", "huffmanHeaderKernel", "huffmanBitsKernelILi4E", "huffmanGroupsKernel", "resolveSymbolsKernel", "mtfChunkKernel",
+KERNELS = ["findMagicsKernel", "huffmanHeaderKernel", "huffmanBitsKernelILi4E", "huffmanGroupsKernel", "huffmanPipelineKernel", "resolveSymbolsKernel", "mtfChunkKernel",
            "mtfExpandKernel", "bwtPrepareKernel", "bwtWalkKernel", "bwtRankKernel", "bwtPlaceKernel", "rleScanKernel",
            "rleWriteKernel", "crcKernel"]
 
