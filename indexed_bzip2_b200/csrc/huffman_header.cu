@@ -119,6 +119,138 @@ struct WarpBits
     }
 };
 
+/* ---- readSelectors (bzip2.hpp:574-637) by the whole warp ----
+ * A selector is j one bits and a zero bit (j < groupCount <= 6), then move-to-front over six table numbers.  Read one after
+ * the other that is 160 dependent instructions per selector and 94 % of this kernel's time (18 000 selectors per block).
+ * But every zero bit ends a selector: lane l takes 32 bits of the stream, counts its zeros, a prefix sum over the lanes
+ * numbers them, and j is the distance to the zero in front (the ones at the end of the lane in front carry over).  The
+ * move-to-front over the j values is a composition of permutations of six positions: every lane works out the permutation
+ * of its share of the selectors, a scan over the lanes composes them, and a second pass over the share writes the table
+ * numbers.  Anything unexpected -- a selector with groupCount or more ones -- returns false, and the caller reads the
+ * selectors one at a time as before, which reports what the reference would report at the bit where it would. */
+__device__ __forceinline__ uint32_t
+selectorMtfStep( uint32_t& list, uint32_t j )
+{
+    const uint32_t uc = ( list >> ( 4U * j ) ) & 15U;
+    const uint32_t low = list & ( ( 1U << ( 4U * j ) ) - 1U );
+    const uint32_t high = ( j >= 5U ) ? 0U : ( list >> ( 4U * j + 4U ) ) << ( 4U * j + 4U );
+    list = high | ( low << 4 ) | uc;
+    return uc;
+}
+
+/* ( a then b ): the list that b makes of the list that a made of the identity */
+__device__ __forceinline__ uint32_t
+selectorCompose( uint32_t a, uint32_t b )
+{
+    uint32_t r = 0;
+#pragma unroll
+    for ( uint32_t i = 0; i < MAX_GROUPS; ++i ) {
+        r |= ( ( a >> ( 4U * ( ( b >> ( 4U * i ) ) & 15U ) ) ) & 15U ) << ( 4U * i );
+    }
+    return r;
+}
+
+__device__ __forceinline__ bool
+readSelectorsByWarp( const uint8_t* __restrict__ data, uint64_t nbytes, uint64_t startBit, uint32_t count, uint32_t groupCount,
+                     uint8_t* __restrict__ selectors, uint32_t lane, uint64_t* endBit )
+{
+    /* ---- the unary part: selectors[i] = j ---- */
+    uint32_t found = 0;   /* zeros seen in the chunks before this one */
+    uint32_t carry = 0;   /* ones at the end of the chunk before this one */
+    uint64_t end = 0;
+    for ( uint64_t pos = startBit; found < count; pos += 1024U ) {
+        const uint64_t bit = pos + 32U * lane;
+        const uint32_t bits = __funnelshift_l( loadWordBE( data, nbytes, ( bit >> 5 ) + 1U ), loadWordBE( data, nbytes, bit >> 5 ),
+                                               static_cast<uint32_t>( bit ) & 31U );
+        const uint32_t zeros = ~bits;   /* bit 31 = the first bit */
+        const uint32_t mine = static_cast<uint32_t>( __popc( zeros ) );
+        uint32_t inclusive = mine;
+#pragma unroll
+        for ( int d = 1; d < 32; d <<= 1 ) {
+            const uint32_t up = __shfl_up_sync( FULL, inclusive, d );
+            if ( lane >= static_cast<uint32_t>( d ) ) {
+                inclusive += up;
+            }
+        }
+        const uint32_t total = __shfl_sync( FULL, inclusive, 31 );
+        const uint32_t firstIndex = found + inclusive - mine;   /* number of this lane's first zero */
+        /* ones behind the lane's last zero */
+        const uint32_t trailing = zeros != 0 ? static_cast<uint32_t>( __ffs( static_cast<int>( zeros ) ) ) - 1U : 32U;
+        uint32_t carryIn = __shfl_up_sync( FULL, trailing, 1 );
+        carryIn = lane == 0 ? carry : carryIn;
+        /* 32 ones in a row inside the selectors: not a selector */
+        bool bad = ( zeros == 0 ) && ( firstIndex < count );
+        uint64_t endHere = 0;
+        uint32_t rest = zeros;
+        uint32_t previous = 0;
+        uint32_t index = firstIndex;
+        bool first = true;
+        while ( ( rest != 0 ) && ( index < count ) ) {
+            const uint32_t b = static_cast<uint32_t>( __clz( static_cast<int>( rest ) ) );
+            rest &= ~( 0x80000000U >> b );
+            const uint32_t j = first ? b + carryIn : b - previous - 1U;
+            bad = bad || ( j >= groupCount );
+            selectors[index] = static_cast<uint8_t>( j );
+            if ( index + 1U == count ) {
+                endHere = bit + b + 1U;
+            }
+            previous = b;
+            first = false;
+            ++index;
+        }
+        if ( __any_sync( FULL, bad ) ) {
+            return false;
+        }
+        const uint32_t holder = __ballot_sync( FULL, endHere != 0 );
+        if ( holder != 0 ) {
+            end = __shfl_sync( FULL, endHere, __ffs( static_cast<int>( holder ) ) - 1 );
+        }
+        found += total;
+        carry = __shfl_sync( FULL, trailing, 31 );
+    }
+    *endBit = end;
+    __syncwarp();   /* the j values are read back by other lanes */
+
+    /* ---- move-to-front: lane l has selectors [l * share, (l + 1) * share), share a multiple of 4 ---- */
+    const uint32_t share = ( ( count + 31U ) / 32U + 3U ) & ~3U;
+    const uint32_t lo = min( count, lane * share );
+    const uint32_t hi = min( count, lo + share );
+    uint32_t* const words = reinterpret_cast<uint32_t*>( selectors );   /* 16-byte aligned; bytes behind `count` are nobody's */
+    uint32_t list = 0x543210U;   /* six 4-bit entries, entry i at bits [4i, 4i + 4) */
+    for ( uint32_t i = lo; i < hi; i += 4U ) {
+        const uint32_t four = words[i >> 2];
+#pragma unroll
+        for ( uint32_t k = 0; k < 4U; ++k ) {
+            if ( i + k < hi ) {
+                selectorMtfStep( list, ( four >> ( 8U * k ) ) & 0xFFU );
+            }
+        }
+    }
+    uint32_t scanned = list;
+#pragma unroll
+    for ( int d = 1; d < 32; d <<= 1 ) {
+        const uint32_t up = __shfl_up_sync( FULL, scanned, d );
+        if ( lane >= static_cast<uint32_t>( d ) ) {
+            scanned = selectorCompose( up, scanned );
+        }
+    }
+    list = __shfl_up_sync( FULL, scanned, 1 );
+    list = lane == 0 ? 0x543210U : list;
+    for ( uint32_t i = lo; i < hi; i += 4U ) {
+        const uint32_t four = words[i >> 2];
+        uint32_t tables = 0;
+#pragma unroll
+        for ( uint32_t k = 0; k < 4U; ++k ) {
+            if ( i + k < hi ) {
+                tables |= selectorMtfStep( list, ( four >> ( 8U * k ) ) & 0xFFU ) << ( 8U * k );
+            }
+        }
+        words[i >> 2] = tables;
+    }
+    __syncwarp();
+    return true;
+}
+
 /* Canonical code of one table from its lengths in ws.lens[0..nsym) (bzip2.hpp:680-683 -> HuffmanCodingBase.hpp:165-187).
  * Returns false for an over-subscribed length set (Error::INVALID_CODE_LENGTHS); incomplete sets are accepted. */
 __device__ __forceinline__ bool
@@ -322,7 +454,15 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
             status = IBZ2_ST_SELECTOR_COUNT;
             break;
         }
-        {
+        uint64_t behindSelectors = 0;
+        if ( readSelectorsByWarp( data, nbytes, br.tell(), selectorsCount, groupCount, selectors, lane, &behindSelectors ) ) {
+            br.init( data, nbytes, behindSelectors, lane );
+            if ( br.tell() > nbits ) {
+                status = IBZ2_ST_EOF;
+                break;
+            }
+        } else {
+            /* one at a time, from the same place: reports the selector that is wrong where the reference would */
             uint32_t mtfSel = 0x543210U;  /* six 4-bit entries, entry i at bits [4i, 4i + 4) */
             uint32_t mine = 0;
             for ( uint32_t i = 0; i < selectorsCount; ++i ) {
