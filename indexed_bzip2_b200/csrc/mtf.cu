@@ -329,9 +329,16 @@ mtfListsKernel( BlockMeta* __restrict__ meta, uint32_t nblocks, const BlockTable
     curWords[lane] = reinterpret_cast<const uint2*>( tablesAll[block].s2b )[lane];
     __syncwarp();
 
+    /* what the loop needs of chunk j + 1 is loaded while chunk j is composed: the chain from one chunk to the next is the
+     * shared-memory gather alone (the checkpoint's load used to sit on it: 1030 cycles per chunk) */
     uint2 perm = chunks > 0 ? lists[lane] : make_uint2( 0, 0 );
+    ChunkCheckpoint ckNext = chunks > 0 ? ckpt[0] : ChunkCheckpoint{ 0, 0 };
     for ( uint32_t j = 0; j < chunks; ++j ) {
         const uint2 nextPerm = ( j + 1U < chunks ) ? lists[static_cast<uint64_t>( j + 1U ) * 32U + lane] : make_uint2( 0, 0 );
+        const ChunkCheckpoint ck = ckNext;
+        if ( j + 1U < chunks ) {
+            ckNext = ckpt[j + 1U];
+        }
         const uint2 mine = curWords[lane];
         uint2 composed;
         composed.x = static_cast<uint32_t>( cur[perm.x & 0xFFU] ) | ( static_cast<uint32_t>( cur[( perm.x >> 8 ) & 0xFFU] ) << 8 )
@@ -343,7 +350,6 @@ mtfListsKernel( BlockMeta* __restrict__ meta, uint32_t nblocks, const BlockTable
         lists[static_cast<uint64_t>( j ) * 32U + lane] = mine;   /* the chunk's start list replaces its permutation */
         {
             /* chunk byte counts -> where each chunk's bytes start in L (every lane keeps the same running sum) */
-            const ChunkCheckpoint ck = ckpt[j];
             flags |= ck.runShift;
             if ( lane == 0 ) {
                 ckpt[j] = ChunkCheckpoint{ static_cast<uint32_t>( min( produced, static_cast<uint64_t>( 0xFFFFFFFFU ) ) ),
