@@ -246,6 +246,7 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
     uint32_t nsym = 0;
     uint32_t selIdx = 0;
     uint32_t selWord = 0;
+    uint32_t selNext = 0;   /* the four selectors behind selWord's, loaded when selWord's come into use */
     uint32_t sink = 0;   /* keeps the touch() loads alive */
 
     while ( true ) {
@@ -316,6 +317,7 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             d.pos = static_cast<uint32_t>( startBit & 31U );
             nsym = 0;
             selIdx = 0;
+            selNext = *reinterpret_cast<const uint32_t*>( selectors );
             haveBlock = true;
         }
 
@@ -327,7 +329,9 @@ huffmanBitsKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMeta*
             outcome = 2;
         } else {
             if ( ( selIdx & 3U ) == 0 ) {
-                selWord = *reinterpret_cast<const uint32_t*>( selectors + selIdx );
+                /* SEL_STRIDE leaves room behind the last selector: the load needs no bounds check */
+                selWord = selNext;
+                selNext = *reinterpret_cast<const uint32_t*>( selectors + selIdx + 4U );
             }
             const uint32_t table = ( selWord >> ( 8U * ( selIdx & 3U ) ) ) & 0xFFU;
             ++selIdx;
