@@ -1,5 +1,9 @@
+"""Per-call and per-device timings of ibz2_multi_decode_buffer on the config-3 workload, outside torchrun:
+    python profiles/multi_api_timing.py [devices]        (profiles/r2_multi_api_n2_standalone.log is its output at 2)
+"""
 import sys, time, json
-sys.path.insert(0, '.')
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np
 import benchdata, bench
 from indexed_bzip2_b200 import _capi
