@@ -356,6 +356,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
     uint32_t origPtr = 0;
     uint32_t isEos = 0;
     uint32_t isEof = 0;
+    uint32_t reported = 0;   /* IBZ2_ST_SELECTOR_UNARY: the group count, which the reference's message quotes (bzip2.hpp:625-629) */
     uint64_t endBit = startBit;
 
     WarpBits br;
@@ -472,6 +473,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
                 br.skip( static_cast<int>( j < 6U ? j + 1U : 6U ) );
                 if ( j >= groupCount ) {
                     status = IBZ2_ST_SELECTOR_UNARY;
+                    reported = groupCount;
                     break;
                 }
                 const uint32_t uc = ( mtfSel >> ( 4U * j ) ) & 15U;
@@ -583,7 +585,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         bm.status = status;
         bm.headerCrc = headerCrc;
         bm.origPtr = origPtr;
-        bm.n = 0;
+        bm.n = status == IBZ2_ST_SELECTOR_UNARY ? reported : 0U;
         bm.nCoded = 0;
         bm.endBit = endBit;
         bm.isEos = isEos;

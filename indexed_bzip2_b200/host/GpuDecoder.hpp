@@ -56,7 +56,9 @@ throwForStatus( const ibz2_block_result& r )
     case IBZ2_ST_SELECTOR_COUNT:
         throw std::logic_error( "[BZip2 block header] the number of selectors is invalid" );
     case IBZ2_ST_SELECTOR_UNARY:
-        throw std::domain_error( "[BZip2 block header] could not find zero termination after group count bits" );
+        /* n_symbols carries the block's group count for this status (bzip2.hpp:625-629) */
+        msg << "[BZip2 block header] Could not find zero termination after " << r.n_symbols << " bits";
+        throw std::domain_error( msg.str() );
     case IBZ2_ST_CODE_LENGTH:
         throw std::logic_error( "[BZip2 block header] start_huffman_length is larger than the maximum code length" );
     case IBZ2_ST_CODE_LENGTHS:

@@ -124,10 +124,13 @@ def skewed_lengths(alphabet: int, order: list[int] | None = None, longest: int =
 
 
 def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, selectors_of=None,
-               raw_symbols: list[int] | None = None) -> int:
+               raw_symbols: list[int] | None = None, total_selectors: int | None = None,
+               bad_selector: int | None = None) -> int:
     """Appends one block; returns its CRC.  tables: code lengths per group over the alphabet (len(used) + 2 symbols),
     None = two tables of balanced codes.  selectors_of(group index) -> table.  raw_symbols: write these symbols
-    under an EMPTY symbol map (alphabet RUNA, RUNB) instead of what `data` transforms to."""
+    under an EMPTY symbol map (alphabet RUNA, RUNB) instead of what `data` transforms to.  total_selectors: write
+    this many selectors (at most 32767, the 15-bit field), more than the block's groups need.  bad_selector: selector
+    number whose unary code has as many ones as there are tables (one too many)."""
     crc = crc32_bzip2(data)
     packed = rle1(data)
     last, orig = bwt(packed)
@@ -141,7 +144,9 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
         tables = [skewed_lengths(alphabet, longest=0), skewed_lengths(alphabet, longest=0)]   # balanced
     assert 2 <= len(tables) <= 6 and all(len(t) == alphabet for t in tables)
     ngroups = (len(symbols) + 49) // 50
-    selectors = [(selectors_of(g) if selectors_of else g % len(tables)) for g in range(ngroups)]
+    nselectors = ngroups if total_selectors is None else total_selectors
+    assert ngroups <= nselectors <= 32767
+    selectors = [(selectors_of(g) if selectors_of else g % len(tables)) for g in range(nselectors)]
 
     w.put(MAGIC_BLOCK, 48)
     w.put(crc, 32)
@@ -164,9 +169,11 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
     w.put(len(tables), 3)
     w.put(len(selectors), 15)
     order = list(range(len(tables)))
-    for s in selectors:
+    for i, s in enumerate(selectors):
         k = order.index(s)
         order.insert(0, order.pop(k))
+        if i == bad_selector:
+            k = len(tables)
         w.put((1 << (k + 1)) - 2, k + 1)   # k ones and a zero
     for lengths in tables:
         cur = lengths[0]

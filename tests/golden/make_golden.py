@@ -137,6 +137,18 @@ def generated_cases() -> dict[str, bytes]:
     second = bytearray(bz2.compress(text_like(rng2, 30_000), 1))
     second[-3] ^= 0x40
     cases["err-stream-crc-multistream"] = ref["base64-32KiB"] + bytes(second) + ref["1B"]
+    # as many selectors as the 15-bit field holds (bzip2.hpp:574-637 reads them all; libbz2 writes 18002 at most), with
+    # every move-to-front distance among them; and a long list whose selector 19000 has one 1 bit too many
+    sel_text = text_like(rng2, 5_000)
+    cases["selectors-32767"] = craft.stream([dict(data=sel_text, tables=None, total_selectors=32767,
+                                                  selectors_of=lambda g: (g * 7 + g // 5) % 2)])
+    sel_tables6 = [[8] * 254 + [9] * 4 for _ in range(6)]   # 254 / 256 + 4 / 512 = 1
+    every_byte = bytes(range(256)) * 40
+    cases["selectors-20001-six-tables"] = craft.stream([dict(data=every_byte, tables=sel_tables6, total_selectors=20001,
+                                                             selectors_of=lambda g: (g * g + g // 3) % 6)])
+    cases["err-selector-unary-late"] = craft.stream([dict(data=every_byte, tables=sel_tables6, total_selectors=20001,
+                                                          selectors_of=lambda g: (g * g + g // 3) % 6,
+                                                          bad_selector=19000)])
     return cases
 
 

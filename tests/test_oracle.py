@@ -15,7 +15,7 @@ ALL = sorted(GOLDEN)
 
 # reference error text -> status of the restatement
 ERROR_STATUS = {"err-bitflip": 13, "err-truncated": 14, "err-empty-symbol-map-runb": 9, "err-empty-symbol-map-runs": 9,
-                "err-stream-crc": 17, "err-stream-crc-multistream": 17}
+                "err-stream-crc": 17, "err-stream-crc-multistream": 17, "err-selector-unary-late": 6}
 
 
 def case(name):
