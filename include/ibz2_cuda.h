@@ -97,8 +97,9 @@ typedef struct ibz2_block_result {
     uint32_t status;          /* enum ibz2_block_status */
     uint32_t is_eos;          /* BlockHeaderData::isEndOfStreamBlock */
     uint32_t is_eof;          /* BlockHeaderData::isEndOfFile (EOS blocks only) */
-    uint32_t n_symbols;       /* entries of the BWT vector (dbufCount, bzip2.hpp:793); for IBZ2_ST_SELECTOR_UNARY the block's
-                               * group count (bzip2.hpp:625-629 quotes it); for IBZ2_ST_SELECTOR_OVERRUN the
+    uint32_t n_symbols;       /* entries of the BWT vector (dbufCount, bzip2.hpp:793); for a rejected header field (IBZ2_ST_GROUP_COUNT,
+                               * _SELECTOR_COUNT, _SELECTOR_UNARY, _CODE_LENGTH) the value the reference's message quotes
+                               * (bzip2.hpp:581, 595, 627, 659); for IBZ2_ST_SELECTOR_OVERRUN the
                                * block's selector count, which the reference's message quotes (bzip2.hpp:714-718) */
     uint32_t orig_ptr;        /* bzip2.hpp:514 */
     uint32_t stream_flags;    /* IBZ2_STREAM_*: where the streams of the file begin and end among the blocks of the call */

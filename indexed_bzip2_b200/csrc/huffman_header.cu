@@ -356,7 +356,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
     uint32_t origPtr = 0;
     uint32_t isEos = 0;
     uint32_t isEof = 0;
-    uint32_t reported = 0;   /* IBZ2_ST_SELECTOR_UNARY: the group count, which the reference's message quotes (bzip2.hpp:625-629) */
+    uint32_t reported = 0;   /* the value the reference's message quotes for a header field it rejects (bzip2.hpp:581, 595, 627, 659) */
     uint64_t endBit = startBit;
 
     WarpBits br;
@@ -444,6 +444,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         }
         if ( ( groupCount < 2U ) || ( groupCount > MAX_GROUPS ) ) {
             status = IBZ2_ST_GROUP_COUNT;
+            reported = groupCount;
             break;
         }
         const uint32_t selectorsCount = br.get( 15 );
@@ -453,6 +454,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         }
         if ( selectorsCount == 0 ) {
             status = IBZ2_ST_SELECTOR_COUNT;
+            reported = selectorsCount;
             break;
         }
         uint64_t behindSelectors = 0;
@@ -504,6 +506,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
                 while ( true ) {
                     if ( hh - 1U > MAX_CODE_LEN - 1U ) {
                         status = IBZ2_ST_CODE_LENGTH;
+                        reported = hh;
                         break;
                     }
                     br.ensure();
@@ -585,7 +588,7 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         bm.status = status;
         bm.headerCrc = headerCrc;
         bm.origPtr = origPtr;
-        bm.n = status == IBZ2_ST_SELECTOR_UNARY ? reported : 0U;
+        bm.n = reported;   /* 0 unless a header field was rejected */
         bm.nCoded = 0;
         bm.endBit = endBit;
         bm.isEos = isEos;

@@ -49,18 +49,22 @@ throwForStatus( const ibz2_block_result& r )
     case IBZ2_ST_RANDOMISED:
         throw std::domain_error( "[BZip2 block header] deprecated isRandomized bit is not supported" );
     case IBZ2_ST_ORIGPTR_RANGE:
-        msg << "[BZip2 block header] origPtr " << r.orig_ptr << " is larger than buffer size";
+        msg << "[BZip2 block header] origPtr " << r.orig_ptr << " is larger than buffer size: " << IBZ2_MAX_BLOCK_SYMBOLS;
         throw std::logic_error( msg.str() );
+    /* for the header fields below n_symbols carries the value that was rejected: the reference's messages quote it
+     * (bzip2.hpp:581, 595, 627, 659) */
     case IBZ2_ST_GROUP_COUNT:
-        throw std::logic_error( "[BZip2 block header] invalid number of Huffman trees" );
+        msg << "[BZip2 block header] Invalid Huffman coding group count " << r.n_symbols;
+        throw std::logic_error( msg.str() );
     case IBZ2_ST_SELECTOR_COUNT:
-        throw std::logic_error( "[BZip2 block header] the number of selectors is invalid" );
+        msg << "[BZip2 block header] The number of selectors " << r.n_symbols << " is invalid";
+        throw std::logic_error( msg.str() );
     case IBZ2_ST_SELECTOR_UNARY:
-        /* n_symbols carries the block's group count for this status (bzip2.hpp:625-629) */
         msg << "[BZip2 block header] Could not find zero termination after " << r.n_symbols << " bits";
         throw std::domain_error( msg.str() );
     case IBZ2_ST_CODE_LENGTH:
-        throw std::logic_error( "[BZip2 block header] start_huffman_length is larger than the maximum code length" );
+        msg << "[BZip2 block header] start_huffman_length " << r.n_symbols << " is larger than 20 or zero\n";
+        throw std::logic_error( msg.str() );
     case IBZ2_ST_CODE_LENGTHS:
         throw std::domain_error( "Constructing a Huffman coding from the given code length sequence failed!" );
     case IBZ2_ST_SELECTOR_OVERRUN:

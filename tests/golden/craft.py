@@ -125,12 +125,15 @@ def skewed_lengths(alphabet: int, order: list[int] | None = None, longest: int =
 
 def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, selectors_of=None,
                raw_symbols: list[int] | None = None, total_selectors: int | None = None,
-               bad_selector: int | None = None) -> int:
+               bad_selector: int | None = None, fields: dict | None = None) -> int:
     """Appends one block; returns its CRC.  tables: code lengths per group over the alphabet (len(used) + 2 symbols),
     None = two tables of balanced codes.  selectors_of(group index) -> table.  raw_symbols: write these symbols
     under an EMPTY symbol map (alphabet RUNA, RUNB) instead of what `data` transforms to.  total_selectors: write
     this many selectors (at most 32767, the 15-bit field), more than the block's groups need.  bad_selector: selector
-    number whose unary code has as many ones as there are tables (one too many)."""
+    number whose unary code has as many ones as there are tables (one too many).  fields: header fields written
+    with the given value instead of the right one: "orig" (24 bits), "ngroups" (3), "nselectors" (15),
+    "first_length" (the 5-bit start length of table 0)."""
+    fields = fields or {}
     crc = crc32_bzip2(data)
     packed = rle1(data)
     last, orig = bwt(packed)
@@ -151,7 +154,7 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
     w.put(MAGIC_BLOCK, 48)
     w.put(crc, 32)
     w.put(0, 1)
-    w.put(orig, 24)
+    w.put(fields.get("orig", orig), 24)
     if empty_symbol_map:
         w.put(0, 16)
     else:
@@ -166,8 +169,8 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
                     if b >> 4 == g:
                         mask |= 1 << (15 - (b & 15))
                 w.put(mask, 16)
-    w.put(len(tables), 3)
-    w.put(len(selectors), 15)
+    w.put(fields.get("ngroups", len(tables)), 3)
+    w.put(fields.get("nselectors", len(selectors)), 15)
     order = list(range(len(tables)))
     for i, s in enumerate(selectors):
         k = order.index(s)
@@ -175,9 +178,9 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
         if i == bad_selector:
             k = len(tables)
         w.put((1 << (k + 1)) - 2, k + 1)   # k ones and a zero
-    for lengths in tables:
+    for number, lengths in enumerate(tables):
         cur = lengths[0]
-        w.put(cur, 5)
+        w.put(fields.get("first_length", cur) if number == 0 else cur, 5)
         for l in lengths:
             while cur != l:
                 w.put(2 if cur < l else 3, 2)

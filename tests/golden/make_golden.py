@@ -149,6 +149,15 @@ def generated_cases() -> dict[str, bytes]:
     cases["err-selector-unary-late"] = craft.stream([dict(data=every_byte, tables=sel_tables6, total_selectors=20001,
                                                           selectors_of=lambda g: (g * g + g // 3) % 6,
                                                           bad_selector=19000)])
+    # one stream per header check of bzip2.hpp:479-685 and :794-798 that no other case reaches: what the reference
+    # throws, and with which words, is part of the interface
+    small = text_like(rng2, 3_000)
+    cases["err-origptr"] = craft.stream([dict(data=small, tables=None, fields={"orig": 0xFFFFF0})])
+    cases["err-group-count-1"] = craft.stream([dict(data=small, tables=None, fields={"ngroups": 1})])
+    cases["err-group-count-7"] = craft.stream([dict(data=small, tables=None, fields={"ngroups": 7})])
+    cases["err-selector-count-0"] = craft.stream([dict(data=small, tables=None, fields={"nselectors": 0})])
+    cases["err-code-length-0"] = craft.stream([dict(data=small, tables=None, fields={"first_length": 0})])
+    cases["err-code-length-21"] = craft.stream([dict(data=small, tables=None, fields={"first_length": 21})])
     return cases
 
 
