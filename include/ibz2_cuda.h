@@ -101,7 +101,8 @@ typedef struct ibz2_block_result {
                                * _SELECTOR_COUNT, _SELECTOR_UNARY, _CODE_LENGTH) the value the reference's message quotes
                                * (bzip2.hpp:581, 595, 627, 659); for IBZ2_ST_SELECTOR_OVERRUN the
                                * block's selector count, which the reference's message quotes (bzip2.hpp:714-718) */
-    uint32_t orig_ptr;        /* bzip2.hpp:514 */
+    uint32_t orig_ptr;        /* bzip2.hpp:514; for IBZ2_ST_BAD_MAGIC the lower 24 of the 48 bits found where the magic
+                               * should be (the upper 24 in n_symbols): the reference's message quotes them */
     uint32_t stream_flags;    /* IBZ2_STREAM_*: where the streams of the file begin and end among the blocks of the call */
     uint32_t stream_crc_expected;   /* last block of a stream: BlockHeader::headerCRC() of the EOS block behind it */
     uint32_t stream_crc_calculated; /* last block of a stream whose first block is part of the same call and whose blocks

@@ -1503,6 +1503,8 @@ ibz2_read_block_header( const uint8_t* data, uint64_t nbytes, uint64_t bit_offse
     }
     if ( magic != IBZ2_MAGIC_BLOCK ) {
         result->status = IBZ2_ST_BAD_MAGIC;
+        result->n_symbols = static_cast<uint32_t>( magic >> 24 );   /* what was there instead, for the message */
+        result->orig_ptr = static_cast<uint32_t>( magic & 0xFFFFFFU );
     }
     return IBZ2_OK;
 }

@@ -394,6 +394,8 @@ huffmanHeaderKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMet
         }
         if ( magic != MAGIC_BLOCK ) {
             status = IBZ2_ST_BAD_MAGIC;
+            reported = static_cast<uint32_t>( magicHi );   /* the reference's message quotes the 48 bits (bzip2.hpp:502-507) */
+            origPtr = static_cast<uint32_t>( magicLo );
             break;
         }
         const uint32_t randomised = br.get( 1 );

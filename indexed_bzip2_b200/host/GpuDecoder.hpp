@@ -44,7 +44,10 @@ throwForStatus( const ibz2_block_result& r )
     std::stringstream msg;
     switch ( r.status ) {
     case IBZ2_ST_BAD_MAGIC:
-        msg << "[BZip2 block header] invalid compressed magic at offset " << r.enc_offset_bits << " b";
+        /* n_symbols and orig_ptr carry the upper and lower 24 of the 48 bits that were there (bzip2.hpp:502-507) */
+        msg << "[BZip2 block header] invalid compressed magic 0x" << std::hex
+            << ( ( static_cast<uint64_t>( r.n_symbols ) << 24 ) | r.orig_ptr ) << std::dec
+            << " at offset " << r.enc_offset_bits / 8U << " B " << r.enc_offset_bits % 8U << " b";
         throw std::domain_error( msg.str() );
     case IBZ2_ST_RANDOMISED:
         throw std::domain_error( "[BZip2 block header] deprecated isRandomized bit is not supported" );

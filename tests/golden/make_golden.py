@@ -158,6 +158,8 @@ def generated_cases() -> dict[str, bytes]:
     cases["err-selector-count-0"] = craft.stream([dict(data=small, tables=None, fields={"nselectors": 0})])
     cases["err-code-length-0"] = craft.stream([dict(data=small, tables=None, fields={"first_length": 0})])
     cases["err-code-length-21"] = craft.stream([dict(data=small, tables=None, fields={"first_length": 21})])
+    # a stream header with something else where the first block's magic should be (bzip2.hpp:502-507)
+    cases["err-bad-magic-after-header"] = b"BZh9" + bytes([0xAB, 0xCD, 0xEF, 0x01, 0x23, 0x45, 0x67, 0x89] * 4)
     return cases
 
 
