@@ -99,7 +99,8 @@ typedef struct ibz2_block_result {
     uint32_t is_eof;          /* BlockHeaderData::isEndOfFile (EOS blocks only) */
     uint32_t n_symbols;       /* entries of the BWT vector (dbufCount, bzip2.hpp:793); for a rejected header field (IBZ2_ST_GROUP_COUNT,
                                * _SELECTOR_COUNT, _SELECTOR_UNARY, _CODE_LENGTH) the value the reference's message quotes
-                               * (bzip2.hpp:581, 595, 627, 659); for IBZ2_ST_SELECTOR_OVERRUN the
+                               * (bzip2.hpp:581, 595, 627, 659); for IBZ2_ST_DBUF_OVERFLOW the count that did not fit
+                               * (bzip2.hpp:751-756, 776-780); for IBZ2_ST_SELECTOR_OVERRUN the
                                * block's selector count, which the reference's message quotes (bzip2.hpp:714-718) */
     uint32_t orig_ptr;        /* bzip2.hpp:514; for IBZ2_ST_BAD_MAGIC the lower 24 of the 48 bits found where the magic
                                * should be (the upper 24 in n_symbols): the reference's message quotes them */

@@ -1405,7 +1405,8 @@ ibz2_debug_decode_block( ibz2_ctx* ctx, const void* data, uint64_t nbytes, uint6
     IBZ2_CUDA_CHECK( ctx, cudaMemcpyAsync( ctx->hMeta, ctx->dMeta, sizeof( ibz2::BlockMeta ), cudaMemcpyDeviceToHost, s ) );
     IBZ2_CUDA_CHECK( ctx, cudaStreamSynchronize( s ) );
     IBZ2_CUDA_CHECK( ctx, cudaGetLastError() );
-    const uint32_t n = ctx->hMeta[0].n;
+    /* (for a block that failed, n carries what the reference's message quotes, not a symbol count) */
+    const uint32_t n = ctx->hMeta[0].status == IBZ2_ST_OK ? ctx->hMeta[0].n : 0U;
     if ( ( lbytes != nullptr ) && ( n > 0 ) ) {
         IBZ2_CUDA_CHECK( ctx, cudaMemcpy( lbytes, ctx->dLbytes, n, cudaMemcpyDeviceToHost ) );
     }

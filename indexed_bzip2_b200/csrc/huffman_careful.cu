@@ -258,6 +258,7 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
 
     uint32_t status = IBZ2_ST_OK;
     uint32_t selectorsSeen = 0;   /* the selector count, for the message of a selector overrun */
+    uint32_t overflowAt = 0;      /* the count that did not fit the block any more, for the message of an overflow */
     uint32_t headerCrc = 0;
     uint32_t origPtr = 0;
     uint32_t cnt = 0;       /* dbufCount */
@@ -514,6 +515,7 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
                 runPos = 0;
                 if ( static_cast<uint64_t>( cnt ) + hh > DBUF_SIZE ) {
                     status = IBZ2_ST_DBUF_OVERFLOW;
+                    overflowAt = static_cast<uint32_t>( cnt + hh );   /* what the reference's message quotes (bzip2.hpp:751-756: the sum in 32 bits) */
                     break;
                 }
                 const uint32_t uc = __shfl_sync( FULL, m[0], 0 );
@@ -543,6 +545,7 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
             }
             if ( cnt >= DBUF_SIZE ) {
                 status = IBZ2_ST_DBUF_OVERFLOW;
+                overflowAt = cnt;        /* bzip2.hpp:776-780 */
                 break;
             }
             const uint32_t uc = moveToFront( m, sym - 1U, lane );
@@ -582,7 +585,8 @@ huffmanCarefulKernel( const uint8_t* __restrict__ data, uint64_t nbytes, BlockMe
         bm.headerCrc = headerCrc;
         bm.origPtr = origPtr;
         /* a selector overrun reports the selector count, which the reference puts into its message (bzip2.hpp:714-718) */
-        bm.n = ( status == IBZ2_ST_OK ) ? cnt : ( status == IBZ2_ST_SELECTOR_OVERRUN ? selectorsSeen : 0U );
+        bm.n = ( status == IBZ2_ST_OK ) ? cnt : ( status == IBZ2_ST_SELECTOR_OVERRUN ? selectorsSeen
+                                               : ( status == IBZ2_ST_DBUF_OVERFLOW ? overflowAt : 0U ) );
         bm.endBit = endBit;
         bm.isEos = isEos;
         bm.isEof = isEof;

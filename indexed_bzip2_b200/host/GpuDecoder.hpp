@@ -75,7 +75,11 @@ throwForStatus( const ibz2_block_result& r )
         msg << "[BZip2 block data] selector " << r.n_symbols << " out of maximum range " << r.n_symbols;
         throw std::domain_error( msg.str() );
     case IBZ2_ST_DBUF_OVERFLOW:
-        throw std::domain_error( "[BZip2 block data] dbufCount exceeds dbufSize" );
+        /* n_symbols carries the count that did not fit: behind a run the sum the reference prints (bzip2.hpp:751-756),
+         * in front of a literal the count itself, which is the buffer size then (bzip2.hpp:776-780) */
+        msg << "[BZip2 block data] dbufCount " << ( r.n_symbols > IBZ2_MAX_BLOCK_SYMBOLS ? "+ hh " : "" ) << r.n_symbols
+            << " > " << IBZ2_MAX_BLOCK_SYMBOLS << " dbufSize";
+        throw std::domain_error( msg.str() );
     case IBZ2_ST_INVALID_CODE:
         throw std::bad_optional_access();
     case IBZ2_ST_ORIGPTR:

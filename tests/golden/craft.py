@@ -132,7 +132,8 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
     this many selectors (at most 32767, the 15-bit field), more than the block's groups need.  bad_selector: selector
     number whose unary code has as many ones as there are tables (one too many).  fields: header fields written
     with the given value instead of the right one: "orig" (24 bits), "ngroups" (3), "nselectors" (15),
-    "first_length" (the 5-bit start length of table 0)."""
+    "first_length" (the 5-bit start length of table 0); "used": with raw_symbols, the byte values of the symbol map
+    (default none); "skip_data": nothing behind the code lengths (for tables no code can be made of)."""
     fields = fields or {}
     crc = crc32_bzip2(data)
     packed = rle1(data)
@@ -141,7 +142,8 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
     symbols = mtf_rle2(last, used)
     empty_symbol_map = raw_symbols is not None
     if empty_symbol_map:
-        used, symbols, orig = [], list(raw_symbols), 0
+        used, symbols, orig = list(fields.get("used", [])), list(raw_symbols), 0
+        empty_symbol_map = not used
     alphabet = len(used) + 2
     if tables is None:
         tables = [skewed_lengths(alphabet, longest=0), skewed_lengths(alphabet, longest=0)]   # balanced
@@ -186,6 +188,8 @@ def block_bits(w: BitWriter, data: bytes, tables: list[list[int]] | None, select
                 w.put(2 if cur < l else 3, 2)
                 cur += 1 if cur < l else -1
             w.put(0, 1)
+    if fields.get("skip_data"):
+        return crc
     codes = [canonical_codes(t) for t in tables]
     for i, s in enumerate(symbols):
         t = selectors[i // 50]

@@ -160,6 +160,14 @@ def generated_cases() -> dict[str, bytes]:
     cases["err-code-length-21"] = craft.stream([dict(data=small, tables=None, fields={"first_length": 21})])
     # a stream header with something else where the first block's magic should be (bzip2.hpp:502-507)
     cases["err-bad-magic-after-header"] = b"BZh9" + bytes([0xAB, 0xCD, 0xEF, 0x01, 0x23, 0x45, 0x67, 0x89] * 4)
+    # what readBlockData itself rejects (bzip2.hpp:748-756, 794-798) and what the table construction rejects (:680-683)
+    cases["err-origptr-error"] = craft.stream([dict(data=small, tables=None, fields={"orig": 5000})])
+    alphabet_small = len(set(craft.rle1(small))) + 2
+    cases["err-code-lengths-oversubscribed"] = craft.stream([dict(data=small, tables=[[1] * alphabet_small] * 2,
+                                                                  fields={"skip_data": True})])
+    # one byte value, then RUNB twenty-one times: a run of 2^22 - 2 bytes, more than a block holds
+    cases["err-run-longer-than-block"] = craft.stream([dict(data=b"x", tables=[[1, 2, 2], [1, 2, 2]],
+                                                            raw_symbols=[1] * 21 + [2], fields={"used": [120]})])
     return cases
 
 

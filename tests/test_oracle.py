@@ -17,7 +17,8 @@ ALL = sorted(GOLDEN)
 ERROR_STATUS = {"err-bitflip": 13, "err-truncated": 14, "err-empty-symbol-map-runb": 9, "err-empty-symbol-map-runs": 9,
                 "err-stream-crc": 17, "err-stream-crc-multistream": 17, "err-selector-unary-late": 6,
                 "err-origptr": 3, "err-group-count-1": 4, "err-group-count-7": 4, "err-selector-count-0": 5,
-                "err-code-length-0": 7, "err-code-length-21": 7}
+                "err-code-length-0": 7, "err-code-length-21": 7, "err-origptr-error": 12,
+                "err-code-lengths-oversubscribed": 8, "err-run-longer-than-block": 10}
 
 
 def case(name):
